@@ -1,0 +1,62 @@
+/*
+ * jpeggpu_b200.h — additive entry points of libjpeggpu_b200.so (C99).  None of these exist in
+ * the reference; the eight jpeggpu_* symbols + is_css_444 of <jpeggpu/jpeggpu.h> are the drop-in
+ * boundary and keep working without them.  They expose what the reference keeps private so that
+ * parity can be checked through the C ABI:
+ *   - the quantised coefficient planes (reference: d_image_qdct inside its scratch,
+ *     src/decoder.cpp:230-246, the bit-exact comparison target of SURVEY §9.2),
+ *   - per-scan statistics and the scratch offsets of the intermediate buffers (reference:
+ *     d_scan_destuffed / s_info at the offsets of SURVEY §9.3).
+ */
+#ifndef JPEGGPU_B200_H_
+#define JPEGGPU_B200_H_
+
+#include <jpeggpu/jpeggpu.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Size in int16 elements of each component's coefficient plane: width[c] x height[c], both
+ * rounded up to whole MCUs of the scan that codes the component (reference scan_component::
+ * data_size, src/reader.cpp:395-405). */
+enum jpeggpu_status jpeggpu_b200_get_coefficient_size(
+    jpeggpu_decoder_t decoder, int width[JPEGGPU_MAX_COMP], int height[JPEGGPU_MAX_COMP]);
+
+/* Like jpeggpu_decoder_decode, but stops after DC un-differencing and writes the quantised
+ * coefficients (not dequantised, DC absolute) as planar raster int16 into d_planes[c] (device,
+ * 16-byte aligned, width[c]*height[c] elements, row length width[c]): the output of the
+ * reference's decode_transpose (src/decode_transpose.cu:136-215). */
+enum jpeggpu_status jpeggpu_b200_decode_coefficients(
+    jpeggpu_decoder_t decoder,
+    int16_t* d_planes[JPEGGPU_MAX_COMP],
+    void* d_tmp,
+    size_t tmp_size,
+    cudaStream_t stream);
+
+struct jpeggpu_b200_scan_stats {
+    int num_components;
+    int num_segments;          /* restart segments */
+    int dus_per_mcu;
+    int total_mcus;
+    unsigned scan_bytes;       /* Sb: stuffed entropy-coded bytes */
+    unsigned destuffed_bytes;  /* Sd: data bytes after unstuffing */
+    unsigned num_subsequences; /* N */
+    unsigned num_data_units;   /* D */
+    int subsequence_bytes;
+    int kernel_launches;       /* launches jpeggpu_decoder_decode issues for this scan */
+    /* byte offsets inside d_tmp of the intermediate buffers (valid after decode + sync) */
+    size_t off_control, off_destuffed, off_coefficients, off_sync_records, off_slot_prefix;
+};
+
+/* Statistics of scan `scan` of the last parsed image; *num_scans (optional) gets the count. */
+enum jpeggpu_status jpeggpu_b200_get_scan_stats(
+    jpeggpu_decoder_t decoder, int scan, struct jpeggpu_b200_scan_stats* stats, int* num_scans);
+
+/* Bytes jpeggpu_decoder_transfer copies host-to-device for the last parsed image. */
+enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, size_t* bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,148 @@
+// common.hpp — types shared by the host planner and the sm_100a kernels.
+//
+// Vocabulary (reference glossary: src/decoder.cpp:46-63):
+//   scan        one SOS worth of entropy-coded data
+//   segment     the part of a scan between two restart markers (independent bit stream)
+//   subsequence kSubBytes destuffed bytes handled by one thread; never straddles a segment
+//   data unit   one 8x8 block of 64 coefficients (DU)
+//   slot        one coefficient position in coded order: slot = du * 64 + zigzag index
+#ifndef JB2_COMMON_HPP_
+#define JB2_COMMON_HPP_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define JB2_HD __host__ __device__ __forceinline__
+#else
+#define JB2_HD inline
+#endif
+
+namespace jb2 {
+
+constexpr int kMaxComp = 4;       // JPEGGPU_MAX_COMP (include/jpeggpu/jpeggpu.h:33)
+constexpr int kMaxScans = 4;      // one component may be coded once (src/defs.hpp:84)
+constexpr int kMaxDuPerMcu = 10;  // T.81 B.2.3
+constexpr int kMaxTables = 8;     // 4 DC + 4 AC (src/defs.hpp:91)
+
+// Subsequence size. The reference fixes 128 B (src/decoder_defs.hpp:32); we default to 64 B so a
+// 12 MP scan exposes 2x the threads.  Must be a multiple of 4.
+#ifndef JB2_SUB_BYTES
+#define JB2_SUB_BYTES 64
+#endif
+constexpr int kSubBytes = JB2_SUB_BYTES;
+constexpr int kSubBits = kSubBytes * 8;
+constexpr int kSubWords = kSubBytes / 4;
+// Run-in: a thread cold-starts this many subsequences before its own to guess its entry state.
+#ifndef JB2_RUNIN_SUBS
+#define JB2_RUNIN_SUBS 6
+#endif
+constexpr int kRunInSubs = JB2_RUNIN_SUBS;
+
+// ---- Huffman lookup tables -------------------------------------------------------------------
+// One table = header (8 u16) + primary LUT (2^kLutBits u16, indexed by the next kLutBits bits)
+// + secondary LUT (lut2_size u16, indexed by peek16 - base16) for codes longer than kLutBits
+// + slow-path arrays for pathological tables whose long-code region exceeds kLut2Max.
+// Entry: bits 0-4 total bits to skip (code length + magnitude bits, >= 1),
+//        bits 5-8 magnitude size, bits 9-15 slot advance (run + 1; 64 = end of block).
+constexpr int kLutBits = 10;
+constexpr int kLut1Size = 1 << kLutBits;
+constexpr int kLut2Max = 4096;
+constexpr uint16_t kEntryLong = 0xffffu; // primary miss: go to the secondary LUT
+constexpr uint16_t kEntrySlow = 0xfffeu; // secondary miss: canonical length search
+
+struct HuffSlow {       // canonical decode data (T.81 F.2.2.3), used by the slow path only
+    uint32_t limit[17]; // limit[l] = (maxcode[l] + 1) << (16 - l), l = 1..16; 0 if no codes
+    int32_t valoff[17]; // huffval index of first code of length l, minus its code
+    uint8_t huffval[256];
+    uint8_t is_dc;
+    uint8_t pad[3];
+};
+
+JB2_HD uint16_t make_entry(unsigned symbol, int code_len, bool is_dc)
+{
+    unsigned size, adv;
+    if (is_dc) {
+        size = symbol & 15u; // valid streams: 0..11
+        adv = 1;
+    } else {
+        const unsigned run = symbol >> 4;
+        size = symbol & 15u;
+        // src/decode_huffman.cu:236-242: size 0 is ZRL when run == 15, otherwise end of block
+        adv = size ? run + 1 : (run == 15 ? 16u : 64u);
+    }
+    unsigned skip = (unsigned)code_len + size; // <= 16 + 15
+    return (uint16_t)(skip | (size << 5) | (adv << 9));
+}
+
+// ---- device-visible descriptors ---------------------------------------------------------------
+
+struct SegDesc {          // one per restart segment, built by the host walk
+    uint32_t sub_off;     // first subsequence of the segment
+    uint32_t nbytes;      // destuffed data bytes in the segment
+    uint32_t kept_before; // destuffed data bytes in all earlier segments of the scan
+    uint32_t src_begin;   // stuffed offset (relative to scan start) of the first byte
+};
+
+struct SubEntry { // per-subsequence sync record, stored as one 8-byte word
+    uint16_t g;   // packed entry state
+    uint16_t x;   // packed exit state given g
+    uint32_t n;   // slots advanced inside the subsequence given g
+};
+
+// packed state: overflow bits past the boundary (5) | DU index in MCU (4) | zig-zag index (6)
+JB2_HD uint16_t pack_state(unsigned o, unsigned c, unsigned z)
+{
+    return (uint16_t)(o | (c << 5) | (z << 9));
+}
+
+struct ScanGeom { // by-value kernel parameter describing one scan
+    int num_comp;         // components in the scan
+    int dus_per_mcu;      // K
+    int mcus_x, mcus_y;
+    int total_mcus;
+    int restart_interval; // MCUs per segment; == total_mcus when no DRI
+    int num_segments;
+    uint32_t num_subs;    // N
+    uint32_t scan_bytes;  // stuffed bytes Sb
+    int num_tables;
+    // per DU slot of the MCU
+    uint8_t slot_dc[kMaxDuPerMcu]; // table slot of the DC table
+    uint8_t slot_ac[kMaxDuPerMcu];
+    uint8_t slot_comp[kMaxDuPerMcu]; // scan component of the slot
+    // per scan component
+    int frame_comp[kMaxComp];
+    int ssx[kMaxComp], ssy[kMaxComp]; // DUs per MCU in x / y (1 for non-interleaved)
+    int du_off[kMaxComp];             // first slot of the component inside the MCU
+    int blocks_x[kMaxComp], blocks_y[kMaxComp]; // coded plane size in DUs (MCU padded)
+    int size_x[kMaxComp], size_y[kMaxComp];     // output plane size in samples
+    uint32_t du_prefix[kMaxComp + 1];           // prefix sum of blocks_x*blocks_y
+    uint16_t table_off[kMaxTables];             // u16 offset of each table in the LUT pool
+    uint32_t lut_pool_u16;                      // total u16 in the pool
+};
+
+struct OutPlanes {
+    uint8_t* ptr[kMaxComp]; // indexed by scan component
+    int pitch[kMaxComp];
+    uint8_t q[kMaxComp][64]; // natural-order quantisation table per scan component
+};
+
+struct CoefPlanes {
+    int16_t* ptr[kMaxComp]; // indexed by scan component
+    int stride[kMaxComp];   // in int16 elements
+};
+
+// Control block at the front of the per-scan work area (zeroed every decode).
+struct Control {
+    uint32_t repairs[8]; // repairs made by sync-repair pass i
+    uint32_t pad[8];
+};
+
+// zig-zag -> natural order (T.81 Figure A.6; same table as src/defs.hpp:94-102)
+#define JB2_NATURAL_ORDER                                                                      \
+    0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, \
+        20, 13, 6, 7, 14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44,  \
+        51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63
+
+} // namespace jb2
+#endif

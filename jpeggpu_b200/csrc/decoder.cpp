@@ -1,0 +1,438 @@
+// decoder.cpp — scratch planner, staging and stage orchestration behind the C ABI.
+// Replaces src/decoder.{hpp,cpp} + src/jpeggpu.cpp of the reference.  Differences by design:
+//  * the scratch plan is computed once in parse_header (sizes are pure functions of the parsed
+//    geometry), not by walking the pipeline twice with do_it=false/true;
+//  * one packed staging block + one copy per scan (entropy-coded bytes only) instead of the
+//    whole file plus 9+ table copies (src/decoder.cpp:175-208, quirk Q9);
+//  * one memset per scan; 12 launches per scan instead of ~40 stream operations;
+//  * cumulative scratch-size check (reference quirk Q7).
+#include "huff_lut.hpp"
+#include "kernels.hpp"
+#include "parser.hpp"
+
+#include <jpeggpu/jpeggpu.h>
+#include <jpeggpu_b200.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+using namespace jb2;
+
+namespace {
+
+size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+struct ScanLayout {
+    // upload block (offsets inside the staging block == inside d_tmp)
+    size_t off_lut = 0, off_slow = 0, off_segs = 0;
+    // uploaded entropy-coded bytes
+    size_t off_bytes = 0;
+    // work area (shared by all scans of the image; scans run back to back on one stream)
+    size_t off_ctrl = 0, off_destuffed = 0, off_coef = 0, zero_bytes = 0;
+    size_t off_tile_agg = 0, off_entries = 0, off_qpos = 0, off_seg_idx = 0, off_dc_agg = 0;
+    uint32_t destuffed_bytes = 0;
+    uint32_t num_dus = 0;
+};
+
+} // namespace
+
+struct jpeggpu_decoder {
+    Logger log;
+    ImagePlan plan;
+    bool parsed = false;
+    ScanLayout layout[kMaxScans];
+    size_t upload_bytes = 0; // staging block size
+    size_t total_bytes = 0;  // scratch requirement
+    size_t transfer_bytes = 0;
+    uint8_t* staging = nullptr;
+    size_t staging_cap = 0;
+    bool staging_pinned = false;
+    std::vector<uint16_t> lut_scratch;
+
+    ~jpeggpu_decoder() { release_staging(); }
+
+    void release_staging()
+    {
+        if (staging) {
+            if (staging_pinned) cudaFreeHost(staging);
+            else free(staging);
+        }
+        staging = nullptr;
+        staging_cap = 0;
+    }
+
+    jpeggpu_status reserve_staging(size_t bytes)
+    {
+        if (bytes <= staging_cap) return JPEGGPU_SUCCESS;
+        release_staging();
+        const size_t cap = align256(bytes + bytes / 2 + 65536);
+        void* p = nullptr;
+        if (cudaHostAlloc(&p, cap, cudaHostAllocDefault) == cudaSuccess) {
+            staging_pinned = true;
+        } else {
+            (void)cudaGetLastError(); // no device (CPU-only parse): pageable staging still works
+            p = malloc(cap);
+            staging_pinned = false;
+            if (!p) return JPEGGPU_OUT_OF_HOST_MEMORY;
+        }
+        staging = static_cast<uint8_t*>(p);
+        staging_cap = cap;
+        return JPEGGPU_SUCCESS;
+    }
+
+    jpeggpu_status plan_scratch();
+    ScanBufs bufs(int s, void* d_tmp) const;
+    jpeggpu_status run(jpeggpu_img* img, int16_t* const* coef_planes, void* d_tmp, size_t tmp_size,
+                       cudaStream_t stream);
+};
+
+// Lay out staging + scratch and fill the staging block (LUTs, slow tables, segment directory).
+jpeggpu_status jpeggpu_decoder::plan_scratch()
+{
+    size_t off = 0;
+    // pass 1: sizes of the upload block
+    std::vector<uint16_t>& pool = lut_scratch;
+    HuffSlow slow[kMaxScans][kMaxTables];
+    std::vector<size_t> pool_begin(plan.num_scans + 1, 0);
+    pool.clear();
+    for (int s = 0; s < plan.num_scans; ++s) {
+        ScanPlan& sp = plan.scans[s];
+        pool_begin[s] = pool.size();
+        for (int t = 0; t < sp.geom.num_tables; ++t) {
+            const uint32_t at = build_lut(sp.tables[t], pool, slow[s][t]);
+            sp.geom.table_off[t] = (uint16_t)(at - pool_begin[s]);
+        }
+        if (pool.size() & 1) pool.push_back(0);
+        sp.geom.lut_pool_u16 = (uint32_t)(pool.size() - pool_begin[s]);
+        if (sp.geom.lut_pool_u16 > 47 * 1024) return JPEGGPU_NOT_SUPPORTED; // > 94 KiB of LUTs
+    }
+    pool_begin[plan.num_scans] = pool.size();
+    for (int s = 0; s < plan.num_scans; ++s) {
+        ScanLayout& L = layout[s];
+        const ScanGeom& g = plan.scans[s].geom;
+        L.off_lut = off;
+        off += align256((size_t)g.lut_pool_u16 * 2);
+        L.off_slow = off;
+        off += align256(sizeof(HuffSlow) * kMaxTables);
+        L.off_segs = off;
+        off += align256(sizeof(SegDesc) * (size_t)g.num_segments);
+    }
+    upload_bytes = off;
+    transfer_bytes = upload_bytes;
+    for (int s = 0; s < plan.num_scans; ++s) {
+        layout[s].off_bytes = off;
+        off += align256((size_t)plan.scans[s].geom.scan_bytes + 16);
+        transfer_bytes += plan.scans[s].geom.scan_bytes;
+    }
+    // work area: sized for the largest scan
+    const size_t work_begin = off;
+    size_t work_end = off;
+    for (int s = 0; s < plan.num_scans; ++s) {
+        ScanLayout& L = layout[s];
+        const ScanGeom& g = plan.scans[s].geom;
+        const ScanPlan& sp = plan.scans[s];
+        size_t o = work_begin;
+        L.num_dus = (uint32_t)g.total_mcus * (uint32_t)g.dus_per_mcu;
+        L.destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
+        L.off_ctrl = o;
+        o += align256(sizeof(Control));
+        L.off_destuffed = o;
+        o += align256((size_t)g.num_subs * kSubBytes + 64);
+        L.off_coef = o;
+        o += align256((size_t)L.num_dus * 128);
+        L.zero_bytes = o - L.off_ctrl;
+        L.off_tile_agg = o;
+        o += align256(((size_t)g.scan_bytes / kDestuffTile + 1) * 8);
+        L.off_entries = o;
+        o += align256((size_t)g.num_subs * sizeof(SubEntry));
+        L.off_qpos = o;
+        o += align256(((size_t)g.num_subs + 1) * 4);
+        L.off_seg_idx = o;
+        o += align256((size_t)g.num_subs * 4);
+        L.off_dc_agg = o;
+        o += align256(((size_t)g.total_mcus / kDcTile + 1) * kMaxComp * sizeof(int));
+        if (o > work_end) work_end = o;
+    }
+    total_bytes = work_end;
+
+    jpeggpu_status st = reserve_staging(upload_bytes);
+    if (st != JPEGGPU_SUCCESS) return st;
+    memset(staging, 0, upload_bytes);
+    for (int s = 0; s < plan.num_scans; ++s) {
+        const ScanLayout& L = layout[s];
+        const ScanPlan& sp = plan.scans[s];
+        memcpy(staging + L.off_lut, pool.data() + pool_begin[s], (size_t)sp.geom.lut_pool_u16 * 2);
+        memcpy(staging + L.off_slow, slow[s], sizeof(HuffSlow) * (size_t)sp.geom.num_tables);
+        if (!sp.segs.empty())
+            memcpy(staging + L.off_segs, sp.segs.data(), sizeof(SegDesc) * sp.segs.size());
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
+{
+    uint8_t* base = static_cast<uint8_t*>(d_tmp);
+    const ScanLayout& L = layout[s];
+    ScanBufs b;
+    b.scan_bytes = base + L.off_bytes;
+    b.segs = reinterpret_cast<const SegDesc*>(base + L.off_segs);
+    b.lut_pool = reinterpret_cast<const uint16_t*>(base + L.off_lut);
+    b.slow = reinterpret_cast<const HuffSlow*>(base + L.off_slow);
+    b.ctrl = reinterpret_cast<Control*>(base + L.off_ctrl);
+    b.destuffed = reinterpret_cast<uint32_t*>(base + L.off_destuffed);
+    b.coef = reinterpret_cast<int16_t*>(base + L.off_coef);
+    b.tile_agg = reinterpret_cast<unsigned long long*>(base + L.off_tile_agg);
+    b.entries = reinterpret_cast<SubEntry*>(base + L.off_entries);
+    b.qpos = reinterpret_cast<uint32_t*>(base + L.off_qpos);
+    b.seg_idx = reinterpret_cast<uint32_t*>(base + L.off_seg_idx);
+    b.dc_agg = reinterpret_cast<int*>(base + L.off_dc_agg);
+    return b;
+}
+
+#define JB2_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess) {                                                         \
+            log.log("CUDA error \"%s\" at %s:%d\n", cudaGetErrorString(e_), __FILE__,    \
+                    __LINE__);                                                           \
+            return JPEGGPU_INTERNAL_ERROR;                                               \
+        }                                                                                \
+    } while (0)
+
+// The stage sequence of one image (reference decode_impl<true>, src/decoder.cpp:216-325).
+jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_planes, void* d_tmp,
+                                    size_t tmp_size, cudaStream_t stream)
+{
+    if (!parsed) return JPEGGPU_INVALID_ARGUMENT;
+    if (!d_tmp || tmp_size < total_bytes) return JPEGGPU_INTERNAL_ERROR; // src/util.hpp:66-68
+    if ((reinterpret_cast<uintptr_t>(d_tmp) & 255u) != 0) return JPEGGPU_INVALID_ARGUMENT;
+    for (int s = 0; s < plan.num_scans; ++s) {
+        const ScanPlan& sp = plan.scans[s];
+        const ScanGeom& g = sp.geom;
+        const ScanLayout& L = layout[s];
+        const ScanBufs b = bufs(s, d_tmp);
+        JB2_CUDA(cudaMemsetAsync(b.ctrl, 0, L.zero_bytes, stream));
+        JB2_CUDA(launch_destuff(g, b, stream));
+        JB2_CUDA(launch_huffman(g, b, stream));
+        JB2_CUDA(launch_dc(g, b, stream));
+        if (img) {
+            OutPlanes out;
+            memset(&out, 0, sizeof(out));
+            for (int a = 0; a < g.num_comp; ++a) {
+                const int ci = g.frame_comp[a];
+                out.ptr[a] = img->image[ci];
+                out.pitch[a] = img->pitch[ci];
+                memcpy(out.q[a], plan.qtables[sp.qidx[a]], 64);
+            }
+            JB2_CUDA(launch_idct(g, b, out, stream));
+        }
+        if (coef_planes) {
+            CoefPlanes cp;
+            memset(&cp, 0, sizeof(cp));
+            for (int a = 0; a < g.num_comp; ++a) {
+                cp.ptr[a] = coef_planes[g.frame_comp[a]];
+                cp.stride[a] = g.blocks_x[a] * 8;
+            }
+            JB2_CUDA(launch_transpose(g, b, cp, stream));
+        }
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+extern "C" {
+
+// src/jpeggpu.cpp:41-60
+const char* jpeggpu_get_status_string(enum jpeggpu_status stat)
+{
+    switch (stat) {
+    case JPEGGPU_SUCCESS: return "success";
+    case JPEGGPU_INVALID_ARGUMENT: return "invalid argument";
+    case JPEGGPU_INVALID_JPEG: return "invalid jpeg";
+    case JPEGGPU_INTERNAL_ERROR: return "internal jpeggpu error";
+    case JPEGGPU_NOT_SUPPORTED: return "jpeg is not supported";
+    case JPEGGPU_OUT_OF_HOST_MEMORY: return "out of host memory";
+    case JPEGGPU_INCOMPLETE_BITSTREAM: return "incomplete bitstream";
+    }
+    return "unknown status";
+}
+
+// src/jpeggpu.cpp:62-75
+enum jpeggpu_status jpeggpu_decoder_startup(jpeggpu_decoder_t* decoder)
+{
+    if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
+    *decoder = new (std::nothrow) jpeggpu_decoder();
+    if (!*decoder) return JPEGGPU_OUT_OF_HOST_MEMORY;
+    return JPEGGPU_SUCCESS;
+}
+
+// src/jpeggpu.cpp:77-86
+enum jpeggpu_status jpeggpu_set_logging(jpeggpu_decoder_t decoder, int do_logging)
+{
+    if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
+    decoder->log.on = do_logging != 0;
+    return JPEGGPU_SUCCESS;
+}
+
+// src/jpeggpu.cpp:88-104
+int is_css_444(struct jpeggpu_subsampling css, int num_components)
+{
+    if (num_components < 1 || num_components > JPEGGPU_MAX_COMP) return 0;
+    for (int c = 0; c < num_components; ++c)
+        if (css.x[c] != 1 || css.y[c] != 1) return 0;
+    return 1;
+}
+
+// src/jpeggpu.cpp:106-114, src/decoder.cpp:83-112
+enum jpeggpu_status jpeggpu_decoder_parse_header(
+    jpeggpu_decoder_t decoder, struct jpeggpu_img_info* img_info, const uint8_t* data, size_t size)
+{
+    if (!decoder || !img_info || !data) return JPEGGPU_INVALID_ARGUMENT;
+    decoder->parsed = false;
+    jpeggpu_status st = parse_jpeg(data, size, decoder->plan, decoder->log);
+    if (st != JPEGGPU_SUCCESS) return st;
+    try {
+        st = decoder->plan_scratch();
+    } catch (const std::bad_alloc&) {
+        st = JPEGGPU_OUT_OF_HOST_MEMORY;
+    }
+    if (st != JPEGGPU_SUCCESS) return st;
+    const ImagePlan& p = decoder->plan;
+    memset(img_info, 0, sizeof(*img_info));
+    img_info->num_components = p.num_comp;
+    for (int c = 0; c < p.num_comp; ++c) {
+        img_info->sizes_x[c] = p.comps[c].size_x;
+        img_info->sizes_y[c] = p.comps[c].size_y;
+        img_info->subsampling.x[c] = p.comps[c].ssx;
+        img_info->subsampling.y[c] = p.comps[c].ssy;
+    }
+    decoder->parsed = true;
+    return JPEGGPU_SUCCESS;
+}
+
+// src/jpeggpu.cpp:116-123
+enum jpeggpu_status jpeggpu_decoder_get_buffer_size(jpeggpu_decoder_t decoder, size_t* tmp_size)
+{
+    if (!decoder || !tmp_size) return JPEGGPU_INVALID_ARGUMENT;
+    if (!decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    *tmp_size = decoder->total_bytes;
+    return JPEGGPU_SUCCESS;
+}
+
+// src/jpeggpu.cpp:125-133, src/decoder.cpp:159-211
+enum jpeggpu_status jpeggpu_decoder_transfer(
+    jpeggpu_decoder_t decoder, void* d_tmp, size_t tmp_size, cudaStream_t stream)
+{
+    if (!decoder || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    if (!d_tmp || tmp_size < decoder->total_bytes) return JPEGGPU_INTERNAL_ERROR;
+    const Logger& log = decoder->log;
+    uint8_t* base = static_cast<uint8_t*>(d_tmp);
+    JB2_CUDA(cudaMemcpyAsync(base, decoder->staging, decoder->upload_bytes,
+                             cudaMemcpyHostToDevice, stream));
+    for (int s = 0; s < decoder->plan.num_scans; ++s) {
+        const ScanPlan& sp = decoder->plan.scans[s];
+        if (sp.geom.scan_bytes == 0) continue;
+        JB2_CUDA(cudaMemcpyAsync(base + decoder->layout[s].off_bytes, decoder->plan.file + sp.begin,
+                                 sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream));
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+// src/jpeggpu.cpp:135-147, src/decoder.cpp:336-354
+enum jpeggpu_status jpeggpu_decoder_decode(
+    jpeggpu_decoder_t decoder, struct jpeggpu_img* img, void* d_tmp, size_t tmp_size,
+    cudaStream_t stream)
+{
+    if (!decoder || !img) return JPEGGPU_INVALID_ARGUMENT;
+    if (!decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    const ImagePlan& p = decoder->plan;
+    for (int c = 0; c < p.num_comp; ++c)
+        if (!img->image[c] || img->pitch[c] < p.comps[c].size_x) return JPEGGPU_INVALID_ARGUMENT;
+    return decoder->run(img, nullptr, d_tmp, tmp_size, stream);
+}
+
+// src/jpeggpu.cpp:149-159
+enum jpeggpu_status jpeggpu_decoder_cleanup(jpeggpu_decoder_t decoder)
+{
+    if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
+    delete decoder;
+    return JPEGGPU_SUCCESS;
+}
+
+// ---- additive entry points (include/jpeggpu_b200.h) --------------------------------------------
+
+static const ScanGeom* coding_scan(const ImagePlan& p, int comp, int* a_out)
+{
+    for (int s = 0; s < p.num_scans; ++s)
+        for (int a = 0; a < p.scans[s].geom.num_comp; ++a)
+            if (p.scans[s].geom.frame_comp[a] == comp) {
+                *a_out = a;
+                return &p.scans[s].geom;
+            }
+    return nullptr;
+}
+
+enum jpeggpu_status jpeggpu_b200_get_coefficient_size(
+    jpeggpu_decoder_t decoder, int width[JPEGGPU_MAX_COMP], int height[JPEGGPU_MAX_COMP])
+{
+    if (!decoder || !width || !height || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    for (int c = 0; c < JPEGGPU_MAX_COMP; ++c) {
+        width[c] = height[c] = 0;
+        int a = 0;
+        const ScanGeom* g = c < decoder->plan.num_comp ? coding_scan(decoder->plan, c, &a) : nullptr;
+        if (g) {
+            width[c] = g->blocks_x[a] * 8;
+            height[c] = g->blocks_y[a] * 8;
+        }
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+enum jpeggpu_status jpeggpu_b200_decode_coefficients(
+    jpeggpu_decoder_t decoder, int16_t* d_planes[JPEGGPU_MAX_COMP], void* d_tmp, size_t tmp_size,
+    cudaStream_t stream)
+{
+    if (!decoder || !d_planes || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    for (int c = 0; c < decoder->plan.num_comp; ++c)
+        if (!d_planes[c] || (reinterpret_cast<uintptr_t>(d_planes[c]) & 15u))
+            return JPEGGPU_INVALID_ARGUMENT;
+    return decoder->run(nullptr, d_planes, d_tmp, tmp_size, stream);
+}
+
+enum jpeggpu_status jpeggpu_b200_get_scan_stats(
+    jpeggpu_decoder_t decoder, int scan, struct jpeggpu_b200_scan_stats* stats, int* num_scans)
+{
+    if (!decoder || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    if (num_scans) *num_scans = decoder->plan.num_scans;
+    if (!stats) return JPEGGPU_SUCCESS;
+    if (scan < 0 || scan >= decoder->plan.num_scans) return JPEGGPU_INVALID_ARGUMENT;
+    const ScanGeom& g = decoder->plan.scans[scan].geom;
+    const ScanLayout& L = decoder->layout[scan];
+    memset(stats, 0, sizeof(*stats));
+    stats->num_components = g.num_comp;
+    stats->num_segments = g.num_segments;
+    stats->dus_per_mcu = g.dus_per_mcu;
+    stats->total_mcus = g.total_mcus;
+    stats->scan_bytes = g.scan_bytes;
+    stats->destuffed_bytes = L.destuffed_bytes;
+    stats->num_subsequences = g.num_subs;
+    stats->num_data_units = L.num_dus;
+    stats->subsequence_bytes = kSubBytes;
+    stats->kernel_launches = count_launches(g, false);
+    stats->off_control = L.off_ctrl;
+    stats->off_destuffed = L.off_destuffed;
+    stats->off_coefficients = L.off_coef;
+    stats->off_sync_records = L.off_entries;
+    stats->off_slot_prefix = L.off_qpos;
+    return JPEGGPU_SUCCESS;
+}
+
+enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, size_t* bytes)
+{
+    if (!decoder || !bytes || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    *bytes = decoder->transfer_bytes;
+    return JPEGGPU_SUCCESS;
+}
+
+} // extern "C"

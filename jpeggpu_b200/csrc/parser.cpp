@@ -1,0 +1,419 @@
+// parser.cpp — host marker parser and scan planner.  See parser.hpp.
+#include "parser.hpp"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+namespace jb2 {
+
+void Logger::log(const char* fmt, ...) const
+{
+    if (!on) return;
+    va_list ap;
+    va_start(ap, fmt);
+    vprintf(fmt, ap);
+    va_end(ap);
+}
+
+namespace {
+
+const uint8_t kNatural[64] = {JB2_NATURAL_ORDER};
+
+struct Cursor {
+    const uint8_t* p;
+    const uint8_t* begin;
+    const uint8_t* end;
+    size_t left() const { return (size_t)(end - p); }
+    unsigned u8() { return *p++; }
+    unsigned u16()
+    {
+        unsigned h = *p++;
+        return (h << 8) | *p++;
+    }
+};
+
+struct ParseState {
+    bool found_sof = false;
+    HuffSpec huff[kMaxTables]; // index = th * 2 + class, persists across scans (T.81 B.2.4.2)
+    bool comp_coded[kMaxComp] = {};
+};
+
+int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+const char* marker_name(unsigned m)
+{
+    switch (m) {
+    case 0xc0: return "SOF0";
+    case 0xc1: return "SOF1";
+    case 0xc2: return "SOF2";
+    case 0xc4: return "DHT";
+    case 0xd8: return "SOI";
+    case 0xd9: return "EOI";
+    case 0xda: return "SOS";
+    case 0xdb: return "DQT";
+    case 0xdd: return "DRI";
+    case 0xfe: return "COM";
+    default: break;
+    }
+    if (m >= 0xe0 && m <= 0xef) return "APPn";
+    if (m >= 0xc3 && m <= 0xcf) return "SOFn";
+    return "marker";
+}
+
+// Frame header. Statuses follow src/reader.cpp:81-184.
+jpeggpu_status read_sof(Cursor& cur, ImagePlan& plan, const Logger& log)
+{
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    const int length = (int)cur.u16();
+    if (length < 2) return JPEGGPU_INVALID_JPEG;
+    if (cur.left() < (size_t)(length - 2)) return JPEGGPU_INCOMPLETE_BITSTREAM;
+    if (length < 8) return JPEGGPU_INVALID_JPEG;
+    const uint8_t* body_end = cur.p + (length - 2);
+    const unsigned precision = cur.u8();
+    if (precision != 8) {
+        log.log("\tunsupported sample precision %u, only 8 is supported\n", precision);
+        return JPEGGPU_NOT_SUPPORTED;
+    }
+    const int lines = (int)cur.u16();
+    const int samples = (int)cur.u16();
+    if (lines == 0 || samples == 0) return JPEGGPU_INVALID_JPEG;
+    plan.width = samples;
+    plan.height = lines;
+    const int nc = (int)cur.u8();
+    if (nc == 0) return JPEGGPU_INVALID_JPEG;
+    if (nc > kMaxComp) return JPEGGPU_NOT_SUPPORTED;
+    if (length - 8 < 3 * nc) return JPEGGPU_INCOMPLETE_BITSTREAM;
+    plan.num_comp = nc;
+    log.log("\tsize_x: %d, size_y: %d, num_components: %d\n", samples, lines, nc);
+    plan.ss_max_x = plan.ss_max_y = 0;
+    for (int c = 0; c < nc; ++c) {
+        FrameComp& fc = plan.comps[c];
+        fc.id = (int)cur.u8();
+        const unsigned sf = cur.u8();
+        int sx = (int)(sf >> 4), sy = (int)(sf & 15);
+        if (sx < 1 || sx > 4 || sy < 1 || sy > 4) return JPEGGPU_INVALID_JPEG;
+        if (nc == 1) sx = sy = 1; // a lone component is always 1x1 (src/reader.cpp:147-157)
+        fc.ssx = sx;
+        fc.ssy = sy;
+        fc.qidx = (int)cur.u8();
+        if (fc.qidx > 3) return JPEGGPU_INVALID_JPEG;
+        log.log("\tc_id: %d, ssx: %d, ssy: %d, qi: %d\n", fc.id, sx, sy, fc.qidx);
+        if (sx > plan.ss_max_x) plan.ss_max_x = sx;
+        if (sy > plan.ss_max_y) plan.ss_max_y = sy;
+    }
+    for (int c = 0; c < nc; ++c) {
+        FrameComp& fc = plan.comps[c];
+        fc.size_x = ceil_div(plan.width * fc.ssx, plan.ss_max_x);
+        fc.size_y = ceil_div(plan.height * fc.ssy, plan.ss_max_y);
+    }
+    cur.p = body_end;
+    return JPEGGPU_SUCCESS;
+}
+
+// Huffman table definitions. Statuses follow src/reader.cpp:226-303.
+jpeggpu_status read_dht(Cursor& cur, ParseState& st, const Logger& log)
+{
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    const int length = (int)cur.u16() - 2;
+    if (length < 0 || cur.left() < (size_t)length) return JPEGGPU_INVALID_JPEG;
+    int rem = length;
+    while (rem > 0) {
+        const unsigned tc_th = cur.u8();
+        --rem;
+        const unsigned cls = tc_th >> 4, th = tc_th & 15;
+        if (cls > 1) return JPEGGPU_INVALID_JPEG;
+        if (th > 3) return JPEGGPU_NOT_SUPPORTED;
+        if (rem < 16) return JPEGGPU_INVALID_JPEG;
+        log.log("\t%s Huffman table index %u\n", cls == 0 ? "DC" : "AC", th);
+        HuffSpec& h = st.huff[th * 2 + cls];
+        h = HuffSpec{};
+        int count = 0;
+        for (int i = 0; i < 16; ++i) {
+            h.counts[i] = (uint8_t)cur.u8();
+            count += h.counts[i];
+        }
+        rem -= 16;
+        if (count > 256 || rem < count) return JPEGGPU_INVALID_JPEG;
+        // the code lengths must fit the code space (Kraft); otherwise no canonical code exists
+        unsigned code = 0;
+        for (int l = 0; l < 16; ++l) {
+            code += h.counts[l];
+            if (code > (1u << (l + 1))) return JPEGGPU_INVALID_JPEG;
+            code <<= 1;
+        }
+        for (int i = 0; i < count; ++i) h.vals[i] = (uint8_t)cur.u8();
+        rem -= count;
+        h.is_dc = cls == 0;
+        h.defined = true;
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+// Quantisation tables, stored de-zigzagged. Statuses follow src/reader.cpp:494-549.
+jpeggpu_status read_dqt(Cursor& cur, ImagePlan& plan, const Logger& log)
+{
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    const int length = (int)cur.u16() - 2;
+    if (length < 0 || cur.left() < (size_t)length) return JPEGGPU_INVALID_JPEG;
+    int rem = length;
+    while (rem > 0) {
+        const unsigned pq_tq = cur.u8();
+        --rem;
+        const unsigned pq = pq_tq >> 4, tq = pq_tq & 15;
+        if (pq > 1 || tq > 3) return JPEGGPU_INVALID_JPEG;
+        if (pq != 0) {
+            log.log("\t16-bit quantization table is not supported\n");
+            return JPEGGPU_NOT_SUPPORTED;
+        }
+        if (rem < 64) return JPEGGPU_INVALID_JPEG;
+        for (int j = 0; j < 64; ++j) plan.qtables[tq][kNatural[j]] = (uint8_t)cur.u8();
+        plan.q_defined[tq] = true;
+        rem -= 64;
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+// Restart interval. Statuses follow src/reader.cpp:551-574.
+jpeggpu_status read_dri(Cursor& cur, ImagePlan& plan, const Logger& log)
+{
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    const int length = (int)cur.u16() - 2;
+    if (length < 2 || cur.left() < (size_t)length) return JPEGGPU_INVALID_JPEG;
+    const int rsti = (int)cur.u16();
+    if (plan.restart_interval != 0 && plan.restart_interval != rsti) {
+        log.log("\tredefined restart interval\n");
+        return JPEGGPU_NOT_SUPPORTED;
+    }
+    plan.restart_interval = rsti;
+    log.log("\trestart_interval: %d\n", rsti);
+    cur.p += length - 2;
+    return JPEGGPU_SUCCESS;
+}
+
+// APPn / COM / anything else with a length. Statuses follow src/reader.cpp:576-594.
+jpeggpu_status skip_segment(Cursor& cur, const Logger& log)
+{
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    const int length = (int)cur.u16();
+    if (length < 2) return JPEGGPU_INVALID_JPEG;
+    if (cur.left() < (size_t)(length - 2)) return JPEGGPU_INCOMPLETE_BITSTREAM;
+    log.log("\twarning: skipping this segment\n");
+    cur.p += length - 2;
+    return JPEGGPU_SUCCESS;
+}
+
+// Walk the entropy-coded data of one scan: find its end and build the restart-segment directory.
+// Replaces the memchr walk of src/reader.cpp:443-489.  The classification is the one the destuff
+// kernel applies per byte (src/decode_destuff.cu:37-44, :64-71): a byte is data unless it is
+// 0xff or follows 0xff; 0xff 0x00 contributes one data byte; 0xff 0xd0..0xd7 closes a segment;
+// 0xff followed by anything else (after optional 0xff fill bytes) ends the scan.
+jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp)
+{
+    const uint8_t* const scan_begin = cur.p;
+    const uint8_t* p = cur.p;
+    const uint8_t* const end = cur.end;
+    uint64_t kept = 0, kept_before = 0, sub_off = 0;
+    uint64_t src_begin = 0;
+    auto close_segment = [&]() {
+        SegDesc d;
+        d.sub_off = (uint32_t)sub_off;
+        d.nbytes = (uint32_t)kept;
+        d.kept_before = (uint32_t)kept_before;
+        d.src_begin = (uint32_t)src_begin;
+        sp.segs.push_back(d);
+        sub_off += (kept + kSubBytes - 1) / kSubBytes;
+        kept_before += kept;
+        kept = 0;
+    };
+    for (;;) {
+        const uint8_t* ff = (const uint8_t*)memchr(p, 0xff, (size_t)(end - p));
+        if (!ff) return JPEGGPU_INVALID_JPEG; // no EOI
+        kept += (uint64_t)(ff - p);
+        const uint8_t* q = ff + 1;
+        while (q < end && *q == 0xff) ++q; // fill bytes
+        if (q >= end) return JPEGGPU_INVALID_JPEG;
+        const unsigned m = *q;
+        if (m == 0) {
+            ++kept;
+            p = q + 1;
+            continue;
+        }
+        if (m >= 0xd0 && m <= 0xd7) {
+            close_segment();
+            p = q + 1;
+            src_begin = (uint64_t)(p - scan_begin);
+            continue;
+        }
+        close_segment();
+        cur.p = q - 1; // the 0xff that introduces the next marker
+        break;
+    }
+    sp.begin = (size_t)(scan_begin - cur.begin);
+    sp.end = (size_t)(cur.p - cur.begin);
+    if (sp.end - sp.begin >= (1ull << 31) || sub_off >= (1ull << 31)) return JPEGGPU_NOT_SUPPORTED;
+    sp.geom.scan_bytes = (uint32_t)(sp.end - sp.begin);
+    sp.geom.num_subs = (uint32_t)sub_off;
+    sp.geom.num_segments = (int)sp.segs.size();
+    return JPEGGPU_SUCCESS;
+}
+
+// Scan header + geometry. Statuses follow src/reader.cpp:305-441.
+jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logger& log)
+{
+    if (!st.found_sof) return JPEGGPU_INVALID_JPEG;
+    if (cur.left() < 3) return JPEGGPU_INVALID_JPEG;
+    const int length = (int)cur.u16();
+    if (length < 3) return JPEGGPU_INVALID_JPEG;
+    const int ns = (int)cur.u8();
+    if (ns < 1 || ns > 4) return JPEGGPU_INVALID_JPEG;
+    if (plan.num_scans >= kMaxScans) return JPEGGPU_INVALID_JPEG;
+    const int rest = 2 * ns + 3;
+    if (length - 3 != rest) return JPEGGPU_INVALID_JPEG;
+    if (cur.left() < (size_t)rest) return JPEGGPU_INCOMPLETE_BITSTREAM;
+
+    ScanPlan& sp = plan.scans[plan.num_scans];
+    sp = ScanPlan{};
+    ScanGeom& g = sp.geom;
+    memset(&g, 0, sizeof(g));
+    g.num_comp = ns;
+    const bool interleaved = ns > 1;
+    int table_of[kMaxTables]; // global table index -> slot in this scan, -1 if unused
+    for (int i = 0; i < kMaxTables; ++i) table_of[i] = -1;
+    int slot = 0;
+    for (int a = 0; a < ns; ++a) {
+        const int selector = (int)cur.u8();
+        const unsigned td_ta = cur.u8();
+        const int td = (int)(td_ta >> 4), ta = (int)(td_ta & 15);
+        log.log("\tc_id: %d, dc: %d, ac: %d\n", selector, td, ta);
+        int ci = -1;
+        for (int i = 0; i < plan.num_comp; ++i)
+            if (plan.comps[i].id == selector) {
+                ci = i;
+                break;
+            }
+        if (ci < 0) return JPEGGPU_INVALID_JPEG;
+        // T.81 A.2: scan components follow frame order
+        if (a > 0 && ci <= g.frame_comp[a - 1]) return JPEGGPU_INVALID_JPEG;
+        if (st.comp_coded[ci]) return JPEGGPU_INVALID_JPEG; // baseline codes a component once
+        if (td > 3 || ta > 3) return JPEGGPU_INVALID_JPEG;
+        const int gdc = td * 2 + 0, gac = ta * 2 + 1;
+        if (!st.huff[gdc].defined || !st.huff[gac].defined) return JPEGGPU_INVALID_JPEG;
+        const FrameComp& fc = plan.comps[ci];
+        if (!plan.q_defined[fc.qidx]) return JPEGGPU_INVALID_JPEG;
+        st.comp_coded[ci] = true;
+        if (table_of[gdc] < 0) {
+            table_of[gdc] = g.num_tables;
+            sp.tables[g.num_tables++] = st.huff[gdc];
+        }
+        if (table_of[gac] < 0) {
+            table_of[gac] = g.num_tables;
+            sp.tables[g.num_tables++] = st.huff[gac];
+        }
+        g.frame_comp[a] = ci;
+        sp.qidx[a] = fc.qidx;
+        g.ssx[a] = interleaved ? fc.ssx : 1;
+        g.ssy[a] = interleaved ? fc.ssy : 1;
+        g.du_off[a] = slot;
+        g.size_x[a] = fc.size_x;
+        g.size_y[a] = fc.size_y;
+        // T.81 A.2.3/A.2.4: the coded plane is padded to whole MCUs
+        g.blocks_x[a] = ceil_div(fc.size_x, 8 * g.ssx[a]) * g.ssx[a];
+        g.blocks_y[a] = ceil_div(fc.size_y, 8 * g.ssy[a]) * g.ssy[a];
+        g.mcus_x = g.blocks_x[a] / g.ssx[a];
+        g.mcus_y = g.blocks_y[a] / g.ssy[a];
+        const int dus = g.ssx[a] * g.ssy[a];
+        if (slot + dus > kMaxDuPerMcu) return JPEGGPU_INVALID_JPEG; // T.81 B.2.3
+        for (int j = 0; j < dus; ++j) {
+            g.slot_dc[slot] = (uint8_t)table_of[gdc];
+            g.slot_ac[slot] = (uint8_t)table_of[gac];
+            g.slot_comp[slot] = (uint8_t)a;
+            ++slot;
+        }
+    }
+    g.dus_per_mcu = slot;
+    // MCU counts of all components must agree (they do by construction of A.1.1 sizes, but a
+    // non-conforming frame header could break it): recompute from the first and verify.
+    for (int a = 0; a < ns; ++a) {
+        if (g.blocks_x[a] / g.ssx[a] != g.mcus_x || g.blocks_y[a] / g.ssy[a] != g.mcus_y)
+            return JPEGGPU_INVALID_JPEG;
+    }
+    const int64_t total = (int64_t)g.mcus_x * g.mcus_y;
+    if (total * g.dus_per_mcu * 64 >= (1ll << 31)) return JPEGGPU_NOT_SUPPORTED;
+    g.total_mcus = (int)total;
+    g.restart_interval = plan.restart_interval ? plan.restart_interval : g.total_mcus;
+    g.du_prefix[0] = 0;
+    for (int a = 0; a < ns; ++a)
+        g.du_prefix[a + 1] = g.du_prefix[a] + (uint32_t)(g.blocks_x[a] * g.blocks_y[a]);
+    cur.u8(); // Ss, Se, Ah/Al: fixed for baseline (src/reader.cpp:427-429 ignores them too)
+    cur.u8();
+    cur.u8();
+    ++plan.num_scans;
+    return walk_scan(cur, sp);
+}
+
+jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log)
+{
+    Cursor cur{data, data, data + size};
+    ParseState st;
+    plan.width = plan.height = plan.num_comp = 0;
+    plan.restart_interval = 0;
+    plan.num_scans = 0;
+    memset(plan.q_defined, 0, sizeof(plan.q_defined));
+    plan.file = data;
+    plan.file_size = size;
+
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    if (cur.u8() != 0xff || cur.u8() != 0xd8) return JPEGGPU_INVALID_JPEG;
+    log.log("marker SOI\n");
+    for (;;) {
+        if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+        if (cur.u8() != 0xff) return JPEGGPU_INVALID_JPEG;
+        unsigned m = cur.u8();
+        while (m == 0xff && cur.left() > 0) m = cur.u8(); // fill bytes before a marker
+        log.log("%s\n", marker_name(m));
+        jpeggpu_status s = JPEGGPU_SUCCESS;
+        if (m == 0xc0 || m == 0xc1) {
+            if (st.found_sof) return JPEGGPU_INVALID_JPEG;
+            st.found_sof = true;
+            s = read_sof(cur, plan, log);
+        } else if (m >= 0xc2 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc) {
+            log.log("\tunsupported JPEG type\n");
+            return JPEGGPU_NOT_SUPPORTED;
+        } else if (m == 0xc4) {
+            s = read_dht(cur, st, log);
+        } else if (m == 0xd9) {
+            break;
+        } else if (m == 0xda) {
+            s = read_sos(cur, plan, st, log);
+        } else if (m == 0xdb) {
+            s = read_dqt(cur, plan, log);
+        } else if (m == 0xdd) {
+            s = read_dri(cur, plan, log);
+        } else {
+            s = skip_segment(cur, log);
+        }
+        if (s != JPEGGPU_SUCCESS) return s;
+    }
+    if (!st.found_sof) return JPEGGPU_INVALID_JPEG;
+    for (int c = 0; c < plan.num_comp; ++c)
+        if (!st.comp_coded[c]) {
+            log.log("\tcomponent with index %d not defined in scan\n", c);
+            return JPEGGPU_INVALID_JPEG;
+        }
+    return JPEGGPU_SUCCESS;
+}
+
+} // namespace
+
+jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log)
+{
+    try {
+        return parse_impl(data, size, plan, log);
+    } catch (const std::bad_alloc&) {
+        return JPEGGPU_OUT_OF_HOST_MEMORY;
+    }
+}
+
+} // namespace jb2

@@ -1,0 +1,121 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle, bit-exact:
+quantised coefficient planes and output samples.  Runs on the B200 box (-m gpu)."""
+import numpy as np
+import pytest
+
+import inputs
+import oracle_bindings as ob
+
+pytestmark = pytest.mark.gpu
+
+
+def run_ours(data, want_coefficients=True):
+    from jpeggpu_b200.torch_io import decode_file
+    return decode_file(data, want_coefficients=want_coefficients)
+
+
+def check_against_oracle(data, label):
+    ref = ob.decode(data)
+    assert ref["status"] == 0, (label, ref["status"])
+    info, planes, coefs = run_ours(data)
+    oi = ref["info"]
+    assert info.num_components == oi.num_components
+    for c in range(info.num_components):
+        assert (info.sizes_x[c], info.sizes_y[c]) == (oi.size_x[c], oi.size_y[c])
+        assert coefs[c].shape == ref["planes"][c].shape, (label, c)
+        ndiff = int((coefs[c] != ref["planes"][c]).sum())
+        assert ndiff == 0, f"{label}: component {c}: {ndiff} coefficients differ"
+        pd = int((planes[c] != ref["pixels"][c]).sum())
+        assert pd == 0, f"{label}: component {c}: {pd} samples differ"
+
+
+def test_img6510_matches_oracle():
+    data = inputs.img6510()
+    if data is None:
+        pytest.skip("IMG_6510.JPG not staged (run tools/gen_inputs.py where /root/reference exists)")
+    check_against_oracle(data, "IMG_6510")
+
+
+@pytest.mark.parametrize("w,h,seed,q", [(4032, 3024, 6510, 90), (3008, 2000, 1, 90),
+                                        (3008, 2000, 2, 95), (3001, 1999, 3, 90),
+                                        (1920, 1080, 1, 90)])
+def test_stb_synthetic_matches_oracle(w, h, seed, q):
+    data = inputs.synth(w, h, seed, q)
+    if data is None:
+        pytest.skip("stb generator not built")
+    check_against_oracle(data, f"stb {w}x{h} q{q}")
+
+
+def test_48mp_no_restart_matches_oracle():
+    data = inputs.synth(8064, 6048, 48)
+    if data is None:
+        pytest.skip("stb generator not built")
+    check_against_oracle(data, "stb 48MP")
+
+
+PILLOW_CASES = [
+    dict(w=3008, h=2000, seed=11, mode="YCbCr", subsampling=0),
+    dict(w=3008, h=2000, seed=12, mode="YCbCr", subsampling=1),
+    dict(w=3008, h=2000, seed=13, mode="YCbCr", subsampling=2),
+    dict(w=3008, h=2000, seed=14, mode="L"),
+    dict(w=1504, h=1000, seed=15, mode="CMYK"),
+    dict(w=1000, h=750, seed=16, mode="YCbCr", subsampling=2, restart_blocks=1),
+    dict(w=1000, h=750, seed=17, mode="YCbCr", subsampling=2, restart_blocks=7),
+    dict(w=1000, h=750, seed=18, mode="YCbCr", subsampling=1, restart_blocks=63),
+    dict(w=1000, h=750, seed=19, mode="YCbCr", subsampling=2, optimize=True, quality=97),
+    dict(w=1000, h=750, seed=20, mode="YCbCr", subsampling=0, optimize=True, quality=30),
+    dict(w=8, h=8, seed=21, mode="L"),
+    dict(w=1, h=1, seed=22, mode="YCbCr", subsampling=2),
+    dict(w=17, h=13, seed=23, mode="YCbCr", subsampling=2),
+    dict(w=250, h=3, seed=24, mode="YCbCr", subsampling=1, restart_blocks=2),
+    dict(w=640, h=480, seed=25, mode="L", restart_blocks=5, quality=100),
+]
+
+
+@pytest.mark.parametrize("case", PILLOW_CASES, ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items()))
+def test_libjpeg_encoded_variants_match_oracle(case):
+    data = inputs.pillow_jpeg(**case)
+    check_against_oracle(data, str(case))
+
+
+def test_pitch_and_untouched_bytes():
+    """Bytes between sizes_x and pitch stay untouched (reference contract)."""
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    data = inputs.pillow_jpeg(w=333, h=77, seed=31, mode="YCbCr", subsampling=2)
+    ref = ob.decode(data)
+    sess = DecodeSession()
+    info = sess.parse(pinned_bytes(data))
+    sess.transfer()
+    planes = []
+    for c in range(info.num_components):
+        t = torch.full((info.sizes_y[c], info.sizes_x[c] + 13), 0xAB, dtype=torch.uint8, device="cuda")
+        planes.append(t)
+    sess.decode(planes)
+    torch.cuda.synchronize()
+    for c, t in enumerate(planes):
+        a = t.cpu().numpy()
+        assert np.array_equal(a[:, : info.sizes_x[c]], ref["pixels"][c])
+        assert (a[:, info.sizes_x[c]:] == 0xAB).all()
+    sess.close()
+
+
+def test_decoder_reuse_and_determinism():
+    """One decoder object decodes different images back to back (parse resets all state)."""
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    files = [inputs.pillow_jpeg(w=640, h=480, seed=41, mode="YCbCr", subsampling=2),
+             inputs.pillow_jpeg(w=100, h=60, seed=42, mode="L"),
+             inputs.pillow_jpeg(w=800, h=600, seed=43, mode="YCbCr", subsampling=0, restart_blocks=3)]
+    sess = DecodeSession()
+    for rep in range(2):
+        for data in files:
+            ref = ob.decode(data)
+            info = sess.parse(pinned_bytes(data))
+            sess.transfer()
+            planes = sess.alloc_planes()
+            sess.decode(planes)
+            torch.cuda.synchronize()
+            for c, t in enumerate(planes):
+                assert np.array_equal(t.cpu().numpy()[:, : info.sizes_x[c]], ref["pixels"][c])
+    sess.close()
