@@ -56,6 +56,17 @@ enum jpeggpu_status jpeggpu_b200_get_scan_stats(
 /* Bytes jpeggpu_decoder_transfer copies host-to-device for the last parsed image. */
 enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, size_t* bytes);
 
+/* Per-kernel device times. With profiling on, jpeggpu_decoder_decode records a CUDA event on the
+ * caller's stream before every kernel; after the caller has synchronised the stream,
+ * get_kernel_times returns the milliseconds and launch count per kernel id of the last decode.
+ * Profiling is off by default (timed runs never use it). */
+#define JPEGGPU_B200_MAX_KERNELS 16
+enum jpeggpu_status jpeggpu_b200_set_profiling(jpeggpu_decoder_t decoder, int on);
+enum jpeggpu_status jpeggpu_b200_get_kernel_times(
+    jpeggpu_decoder_t decoder, float ms[JPEGGPU_B200_MAX_KERNELS],
+    int launches[JPEGGPU_B200_MAX_KERNELS]);
+const char* jpeggpu_b200_kernel_name(int id);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,7 +30,10 @@ API_SYMBOLS = [
     "jpeggpu_decoder_decode", "jpeggpu_decoder_cleanup",
     "jpeggpu_b200_get_coefficient_size", "jpeggpu_b200_decode_coefficients",
     "jpeggpu_b200_get_scan_stats", "jpeggpu_b200_get_transfer_size",
+    "jpeggpu_b200_set_profiling", "jpeggpu_b200_get_kernel_times", "jpeggpu_b200_kernel_name",
 ]
+
+MAX_KERNELS = 16
 
 
 class Subsampling(C.Structure):
@@ -101,6 +104,11 @@ def load_library(path=None):
                                                    C.c_size_t, C.c_void_p]
     L.jpeggpu_b200_get_scan_stats.argtypes = [dec, C.c_int, C.POINTER(ScanStats), C.POINTER(C.c_int)]
     L.jpeggpu_b200_get_transfer_size.argtypes = [dec, C.POINTER(C.c_size_t)]
+    L.jpeggpu_b200_set_profiling.argtypes = [dec, C.c_int]
+    L.jpeggpu_b200_get_kernel_times.argtypes = [dec, C.POINTER(C.c_float * MAX_KERNELS),
+                                                C.POINTER(C.c_int * MAX_KERNELS)]
+    L.jpeggpu_b200_kernel_name.restype = C.c_char_p
+    L.jpeggpu_b200_kernel_name.argtypes = [C.c_int]
     if path is None:
         _lib = L
     return L
@@ -178,6 +186,21 @@ class Decoder:
         _check(self.lib.jpeggpu_b200_get_transfer_size(self.handle, C.byref(n)),
                "jpeggpu_b200_get_transfer_size")
         return n.value
+
+    def set_profiling(self, on):
+        _check(self.lib.jpeggpu_b200_set_profiling(self.handle, int(on)), "jpeggpu_b200_set_profiling")
+
+    def kernel_times(self):
+        """{kernel name: (milliseconds, launches)} of the last decode (stream must be synced)."""
+        ms, n = (C.c_float * MAX_KERNELS)(), (C.c_int * MAX_KERNELS)()
+        _check(self.lib.jpeggpu_b200_get_kernel_times(self.handle, C.byref(ms), C.byref(n)),
+               "jpeggpu_b200_get_kernel_times")
+        out = {}
+        for i in range(MAX_KERNELS):
+            name = self.lib.jpeggpu_b200_kernel_name(i).decode()
+            if name and n[i]:
+                out[name] = (ms[i], n[i])
+        return out
 
     def cleanup(self):
         if self.handle:

@@ -50,8 +50,14 @@ struct jpeggpu_decoder {
     size_t staging_cap = 0;
     bool staging_pinned = false;
     std::vector<uint16_t> lut_scratch;
+    StageTimer timer;
 
-    ~jpeggpu_decoder() { release_staging(); }
+    ~jpeggpu_decoder()
+    {
+        release_staging();
+        if (timer.created)
+            for (int i = 0; i < StageTimer::kMaxMarks; ++i) cudaEventDestroy(timer.ev[i]);
+    }
 
     void release_staging()
     {
@@ -208,15 +214,17 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
     if (!parsed) return JPEGGPU_INVALID_ARGUMENT;
     if (!d_tmp || tmp_size < total_bytes) return JPEGGPU_INTERNAL_ERROR; // src/util.hpp:66-68
     if ((reinterpret_cast<uintptr_t>(d_tmp) & 255u) != 0) return JPEGGPU_INVALID_ARGUMENT;
+    timer.n = 0;
     for (int s = 0; s < plan.num_scans; ++s) {
         const ScanPlan& sp = plan.scans[s];
         const ScanGeom& g = sp.geom;
         const ScanLayout& L = layout[s];
         const ScanBufs b = bufs(s, d_tmp);
+        timer.mark(stream, kIdMemset);
         JB2_CUDA(cudaMemsetAsync(b.ctrl, 0, L.zero_bytes, stream));
-        JB2_CUDA(launch_destuff(g, b, stream));
-        JB2_CUDA(launch_huffman(g, b, stream));
-        JB2_CUDA(launch_dc(g, b, stream));
+        JB2_CUDA(launch_destuff(g, b, stream, &timer));
+        JB2_CUDA(launch_huffman(g, b, stream, &timer));
+        JB2_CUDA(launch_dc(g, b, stream, &timer));
         if (img) {
             OutPlanes out;
             memset(&out, 0, sizeof(out));
@@ -226,7 +234,7 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
                 out.pitch[a] = img->pitch[ci];
                 memcpy(out.q[a], plan.qtables[sp.qidx[a]], 64);
             }
-            JB2_CUDA(launch_idct(g, b, out, stream));
+            JB2_CUDA(launch_idct(g, b, out, stream, &timer));
         }
         if (coef_planes) {
             CoefPlanes cp;
@@ -235,9 +243,10 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
                 cp.ptr[a] = coef_planes[g.frame_comp[a]];
                 cp.stride[a] = g.blocks_x[a] * 8;
             }
-            JB2_CUDA(launch_transpose(g, b, cp, stream));
+            JB2_CUDA(launch_transpose(g, b, cp, stream, &timer));
         }
     }
+    timer.mark(stream, kIdCount);
     return JPEGGPU_SUCCESS;
 }
 
@@ -433,6 +442,51 @@ enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, si
     if (!decoder || !bytes || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
     *bytes = decoder->transfer_bytes;
     return JPEGGPU_SUCCESS;
+}
+
+enum jpeggpu_status jpeggpu_b200_set_profiling(jpeggpu_decoder_t decoder, int on)
+{
+    if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
+    StageTimer& t = decoder->timer;
+    if (on && !t.created) {
+        for (int i = 0; i < StageTimer::kMaxMarks; ++i)
+            if (cudaEventCreate(&t.ev[i]) != cudaSuccess) return JPEGGPU_INTERNAL_ERROR;
+        t.created = true;
+    }
+    t.on = on != 0;
+    t.n = 0;
+    return JPEGGPU_SUCCESS;
+}
+
+enum jpeggpu_status jpeggpu_b200_get_kernel_times(
+    jpeggpu_decoder_t decoder, float ms[JPEGGPU_B200_MAX_KERNELS], int launches[JPEGGPU_B200_MAX_KERNELS])
+{
+    if (!decoder || !ms) return JPEGGPU_INVALID_ARGUMENT;
+    StageTimer& t = decoder->timer;
+    for (int i = 0; i < JPEGGPU_B200_MAX_KERNELS; ++i) {
+        ms[i] = 0.f;
+        if (launches) launches[i] = 0;
+    }
+    if (!t.on) return JPEGGPU_INVALID_ARGUMENT;
+    for (int i = 0; i + 1 < t.n; ++i) {
+        float d = 0.f;
+        if (cudaEventElapsedTime(&d, t.ev[i], t.ev[i + 1]) != cudaSuccess)
+            return JPEGGPU_INTERNAL_ERROR; // the caller has not synchronised the stream yet
+        if (t.id[i] < JPEGGPU_B200_MAX_KERNELS) {
+            ms[t.id[i]] += d;
+            if (launches) launches[t.id[i]] += 1;
+        }
+    }
+    return JPEGGPU_SUCCESS;
+}
+
+const char* jpeggpu_b200_kernel_name(int id)
+{
+    static const char* names[kIdCount] = {
+        "memset", "destuff_count", "destuff_apply", "huff_speculate", "huff_repair_0",
+        "huff_repair_1", "huff_repair_2", "huff_fixup", "sub_scan", "huff_write", "dc_tile_sums",
+        "dc_apply", "idct_kernel", "transpose_kernel"};
+    return id >= 0 && id < kIdCount ? names[id] : "";
 }
 
 } // extern "C"

@@ -33,13 +33,37 @@ struct ScanBufs {
     int* dc_agg;               // 4 per DC tile
 };
 
-cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream);
-cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream);
-cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream);
+// Optional per-kernel timing (jpeggpu_b200_set_profiling): an event is recorded on the launching
+// stream before every kernel and one after the last; off by default and absent from timed runs.
+enum KernelId {
+    kIdMemset = 0, kIdDestuffCount, kIdDestuffApply, kIdSpeculate, kIdRepair0, kIdRepair1,
+    kIdRepair2, kIdFixup, kIdSubScan, kIdWrite, kIdDcSums, kIdDcApply, kIdIdct, kIdTranspose,
+    kIdCount
+};
+
+struct StageTimer {
+    static constexpr int kMaxMarks = 64;
+    cudaEvent_t ev[kMaxMarks];
+    int id[kMaxMarks];
+    int n = 0;
+    bool on = false;
+    bool created = false;
+    void mark(cudaStream_t stream, int kernel_id)
+    {
+        if (!on || n >= kMaxMarks) return;
+        id[n] = kernel_id;
+        cudaEventRecord(ev[n], stream);
+        ++n;
+    }
+};
+
+cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm);
+cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm);
+cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm);
 cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& out,
-                        cudaStream_t stream);
+                        cudaStream_t stream, StageTimer* tm);
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
-                             cudaStream_t stream);
+                             cudaStream_t stream, StageTimer* tm);
 
 // Kernel launches issued per scan by each stage (for bench.py's gpu_launches claim).
 int count_launches(const ScanGeom& g, bool with_transpose);

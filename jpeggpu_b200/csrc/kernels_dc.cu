@@ -176,11 +176,13 @@ dc_apply(const ScanGeom g, int16_t* __restrict__ coef, const int* __restrict__ a
 
 } // namespace
 
-cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream)
+cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.total_mcus == 0) return cudaSuccess;
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
+    tm->mark(stream, kIdDcSums);
     dc_tile_sums<<<tiles, kDcTile, 0, stream>>>(g, b.coef, b.dc_agg);
+    tm->mark(stream, kIdDcApply);
     dc_apply<<<tiles, kDcTile, 0, stream>>>(g, b.coef, b.dc_agg);
     return cudaGetLastError();
 }

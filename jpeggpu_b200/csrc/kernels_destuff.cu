@@ -157,11 +157,13 @@ destuff_apply(const uint8_t* __restrict__ src, uint32_t n,
 
 } // namespace
 
-cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream)
+cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.scan_bytes == 0) return cudaSuccess;
     const uint32_t tiles = (g.scan_bytes + kDestuffTile - 1) / kDestuffTile;
+    tm->mark(stream, kIdDestuffCount);
     destuff_count<<<tiles, kDestuffThreads, 0, stream>>>(b.scan_bytes, g.scan_bytes, b.tile_agg);
+    tm->mark(stream, kIdDestuffApply);
     destuff_apply<<<tiles, kDestuffThreads, 0, stream>>>(
         b.scan_bytes, g.scan_bytes, b.tile_agg, b.segs, g.num_segments,
         reinterpret_cast<uint8_t*>(b.destuffed));

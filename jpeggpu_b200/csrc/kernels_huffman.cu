@@ -176,7 +176,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
 
 } // namespace
 
-cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream)
+cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.num_subs == 0) return cudaSuccess;
     const size_t smem = (size_t)((g.lut_pool_u16 + 1) / 2) * 4;
@@ -190,11 +190,17 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
         attr_done = true;
     }
     const uint32_t blocks = (g.num_subs + kHuffThreads - 1) / kHuffThreads;
+    tm->mark(stream, kIdSpeculate);
     huff_speculate<<<blocks, kHuffThreads, smem, stream>>>(g, b);
-    for (int pass = 0; pass < kRepairPasses; ++pass)
+    for (int pass = 0; pass < kRepairPasses; ++pass) {
+        tm->mark(stream, kIdRepair0 + pass);
         huff_repair<<<blocks, kHuffThreads, smem, stream>>>(g, b, pass);
+    }
+    tm->mark(stream, kIdFixup);
     huff_fixup<<<(g.num_segments + 31) / 32, 32, smem, stream>>>(g, b);
+    tm->mark(stream, kIdSubScan);
     sub_scan<<<1, kScanThreads, 0, stream>>>(b.entries, g.num_subs, b.qpos);
+    tm->mark(stream, kIdWrite);
     huff_write<<<blocks, kHuffThreads, smem, stream>>>(g, b);
     return cudaGetLastError();
 }

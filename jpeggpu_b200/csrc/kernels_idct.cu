@@ -159,19 +159,21 @@ transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const CoefP
 } // namespace
 
 cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& out,
-                        cudaStream_t stream)
+                        cudaStream_t stream, StageTimer* tm)
 {
     const uint32_t total = g.du_prefix[g.num_comp];
     if (total == 0) return cudaSuccess;
+    tm->mark(stream, kIdIdct);
     idct_kernel<<<(total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0, stream>>>(g, b.coef, out);
     return cudaGetLastError();
 }
 
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
-                             cudaStream_t stream)
+                             cudaStream_t stream, StageTimer* tm)
 {
     const uint32_t total = g.du_prefix[g.num_comp] * 8u;
     if (total == 0) return cudaSuccess;
+    tm->mark(stream, kIdTranspose);
     transpose_kernel<<<(total + 255) / 256, 256, 0, stream>>>(g, b.coef, planes);
     return cudaGetLastError();
 }
