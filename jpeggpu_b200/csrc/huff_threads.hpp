@@ -27,7 +27,8 @@ JB2_HD unsigned long long pack_entry(uint16_t gs, uint16_t xs, uint32_t n)
 }
 
 // Decode subsequence i of a segment from packed entry state `gs`; returns {gs, exit, n}.
-JB2_HD unsigned long long decode_sub(const DecodeTables& T, const uint32_t* words,
+template <class Mem>
+JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t K, const uint32_t* words,
                                      uint32_t seg_bits, uint32_t i, uint16_t gs)
 {
     const uint32_t start = i * (uint32_t)kSubBits;
@@ -37,13 +38,14 @@ JB2_HD unsigned long long decode_sub(const DecodeTables& T, const uint32_t* word
     uint32_t c = (gs >> 5) & 15u;
     const uint32_t z = gs >> 9;
     uint32_t q = z;
-    decode_span<false>(T, words, p, end, q, c, nullptr, 0u, nullptr);
+    decode_span<false>(M, K, words, p, end, q, c, nullptr, 0u);
     const uint32_t o = p > sub_end ? p - sub_end : 0u;
     return pack_entry(gs, pack_state(o, c, q & 63u), q - z);
 }
 
 // huff_speculate body: guess the entry state of subsequence j by a cold run-in, then decode it.
-JB2_HD unsigned long long speculate_one(const DecodeTables& T, const SegDesc* segs, int num_segs,
+template <class Mem>
+JB2_HD unsigned long long speculate_one(const Mem& M, uint32_t K, const SegDesc* segs, int num_segs,
                                         const uint32_t* destuffed, uint32_t j, uint32_t* seg_out)
 {
     const uint32_t k = find_segment(segs, num_segs, j);
@@ -55,14 +57,14 @@ JB2_HD unsigned long long speculate_one(const DecodeTables& T, const SegDesc* se
     const uint32_t i0 = i > (uint32_t)kRunInSubs ? i - (uint32_t)kRunInSubs : 0u;
     uint32_t p = i0 * (uint32_t)kSubBits, q = 0, c = 0;
     const uint32_t boundary = i * (uint32_t)kSubBits;
-    decode_span<false>(T, words, p, boundary, q, c, nullptr, 0u, nullptr);
+    decode_span<false>(M, K, words, p, boundary, q, c, nullptr, 0u);
     const uint16_t gs = pack_state(p - boundary, c, q & 63u);
-    return decode_sub(T, words, seg.nbytes * 8u, i, gs);
+    return decode_sub(M, K, words, seg.nbytes * 8u, i, gs);
 }
 
 // huff_repair body. Returns the number of records rewritten.
-template <typename EntryPtr>
-JB2_HD uint32_t repair_one(const DecodeTables& T, const SegDesc* segs, const uint32_t* seg_idx,
+template <class Mem, typename EntryPtr>
+JB2_HD uint32_t repair_one(const Mem& M, uint32_t K, const SegDesc* segs, const uint32_t* seg_idx,
                            const uint32_t* destuffed, EntryPtr entries, uint32_t j)
 {
     const SegDesc seg = segs[seg_idx[j]];
@@ -75,7 +77,7 @@ JB2_HD uint32_t repair_one(const DecodeTables& T, const SegDesc* segs, const uin
     uint32_t repaired = 0;
     for (uint32_t m = j; m < seg_end; ++m) {
         if (m != j && state == (uint16_t)entries[m]) break;
-        const unsigned long long e = decode_sub(T, words, seg_bits, m - seg.sub_off, state);
+        const unsigned long long e = decode_sub(M, K, words, seg_bits, m - seg.sub_off, state);
         entries[m] = e;
         state = (uint16_t)(e >> 16);
         ++repaired;
@@ -84,7 +86,8 @@ JB2_HD uint32_t repair_one(const DecodeTables& T, const SegDesc* segs, const uin
 }
 
 // huff_fixup body: sequential verification of one segment.
-JB2_HD void fixup_segment(const DecodeTables& T, const SegDesc seg, const uint32_t* destuffed,
+template <class Mem>
+JB2_HD void fixup_segment(const Mem& M, uint32_t K, const SegDesc seg, const uint32_t* destuffed,
                           unsigned long long* all_entries)
 {
     const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
@@ -96,7 +99,7 @@ JB2_HD void fixup_segment(const DecodeTables& T, const SegDesc seg, const uint32
     for (uint32_t i = 1; i < count; ++i) {
         unsigned long long e = entries[i];
         if ((uint16_t)e != state) {
-            e = decode_sub(T, words, seg_bits, i, state);
+            e = decode_sub(M, K, words, seg_bits, i, state);
             entries[i] = e;
         }
         state = (uint16_t)(e >> 16);
@@ -104,10 +107,11 @@ JB2_HD void fixup_segment(const DecodeTables& T, const SegDesc seg, const uint32
 }
 
 // huff_write body.
-JB2_HD void write_one(const DecodeTables& T, const ScanGeom& g, const SegDesc* segs,
+template <class Mem>
+JB2_HD void write_one(const Mem& M, const ScanGeom& g, const SegDesc* segs,
                       const uint32_t* seg_idx, const uint32_t* destuffed,
                       const unsigned long long* entries, const uint32_t* qpos, int16_t* coef,
-                      const uint8_t* natural, uint32_t j)
+                      uint32_t j)
 {
     const uint32_t k = seg_idx[j];
     const SegDesc seg = segs[k];
@@ -124,7 +128,7 @@ JB2_HD void write_one(const DecodeTables& T, const ScanGeom& g, const SegDesc* s
     uint32_t p = i * (uint32_t)kSubBits + (gs & 31u);
     const uint32_t end = umin((i + 1u) * (uint32_t)kSubBits, seg.nbytes * 8u);
     const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
-    decode_span<true>(T, words, p, end, q, c, out, q_limit, natural);
+    decode_span<true>(M, (uint32_t)g.dus_per_mcu, words, p, end, q, c, out, q_limit);
 }
 
 } // namespace jb2

@@ -32,10 +32,8 @@ namespace {
 __constant__ uint8_t c_natural[64] = {JB2_NATURAL_ORDER};
 
 struct SharedTables {
-    uint16_t dc_off[kMaxDuPerMcu];
-    uint16_t ac_off[kMaxDuPerMcu];
-    uint8_t dc_slot[kMaxDuPerMcu];
-    uint8_t ac_slot[kMaxDuPerMcu];
+    uint32_t offs[kMaxDuPerMcu]; // dc_off | ac_off << 16
+    uint32_t tbls[kMaxDuPerMcu]; // dc table slot | ac table slot << 8
     uint8_t natural[64];
 };
 
@@ -50,28 +48,30 @@ __device__ __forceinline__ void stage_tables(const ScanGeom& g, const uint16_t* 
     for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
     if (threadIdx.x < kMaxDuPerMcu) {
         const int s = threadIdx.x < g.dus_per_mcu ? threadIdx.x : 0;
-        st.dc_off[threadIdx.x] = g.table_off[g.slot_dc[s]];
-        st.ac_off[threadIdx.x] = g.table_off[g.slot_ac[s]];
-        st.dc_slot[threadIdx.x] = g.slot_dc[s];
-        st.ac_slot[threadIdx.x] = g.slot_ac[s];
+        st.offs[threadIdx.x] = (uint32_t)g.table_off[g.slot_dc[s]] |
+                               ((uint32_t)g.table_off[g.slot_ac[s]] << 16);
+        st.tbls[threadIdx.x] = (uint32_t)g.slot_dc[s] | ((uint32_t)g.slot_ac[s] << 8);
     }
     if (threadIdx.x < 64) st.natural[threadIdx.x] = c_natural[threadIdx.x];
     __syncthreads();
 }
 
-__device__ __forceinline__ DecodeTables make_tables(const ScanGeom& g, const SharedTables& st,
-                                                    const HuffSlow* slow)
-{
-    DecodeTables T;
-    T.lut = s_lut;
-    T.slow = slow;
-    T.dc_off = st.dc_off;
-    T.ac_off = st.ac_off;
-    T.dc_slot = st.dc_slot;
-    T.ac_slot = st.ac_slot;
-    T.dus_per_mcu = g.dus_per_mcu;
-    return T;
-}
+// Device memory policy of decode_span: LUTs and per-slot tables in shared memory, the destuffed
+// scan read as 16-byte chunks through the read-only path.
+struct DevMem {
+    const SharedTables* st;
+    const HuffSlow* slow_;
+    __device__ __forceinline__ uint16_t lut(uint32_t i) const { return s_lut[i]; }
+    __device__ __forceinline__ uint32_t slot_offs(uint32_t c) const { return st->offs[c]; }
+    __device__ __forceinline__ uint32_t slot_tbls(uint32_t c) const { return st->tbls[c]; }
+    __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
+    __device__ __forceinline__ uint32_t natural(uint32_t i) const { return st->natural[i]; }
+    __device__ __forceinline__ Chunk4 chunk(const uint32_t* words, uint32_t i) const
+    {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(words) + i);
+        return Chunk4{v.x, v.y, v.z, v.w};
+    }
+};
 
 __global__ void __launch_bounds__(kHuffThreads)
 huff_speculate(const ScanGeom g, const ScanBufs b)
@@ -80,9 +80,10 @@ huff_speculate(const ScanGeom g, const ScanBufs b)
     stage_tables(g, b.lut_pool, st);
     const uint32_t j = blockIdx.x * kHuffThreads + threadIdx.x;
     if (j >= g.num_subs) return;
-    const DecodeTables T = make_tables(g, st, b.slow);
+    const DevMem M{&st, b.slow};
     uint32_t k;
-    const unsigned long long e = speculate_one(T, b.segs, g.num_segments, b.destuffed, j, &k);
+    const unsigned long long e =
+        speculate_one(M, (uint32_t)g.dus_per_mcu, b.segs, g.num_segments, b.destuffed, j, &k);
     b.seg_idx[j] = k;
     reinterpret_cast<unsigned long long*>(b.entries)[j] = e;
 }
@@ -98,9 +99,9 @@ huff_repair(const ScanGeom g, const ScanBufs b, int pass)
     stage_tables(g, b.lut_pool, st);
     const uint32_t j = blockIdx.x * kHuffThreads + threadIdx.x;
     if (j >= g.num_subs) return;
-    const DecodeTables T = make_tables(g, st, b.slow);
+    const DevMem M{&st, b.slow};
     volatile unsigned long long* entries = reinterpret_cast<volatile unsigned long long*>(b.entries);
-    const uint32_t repaired = repair_one(T, b.segs, b.seg_idx, b.destuffed, entries, j);
+    const uint32_t repaired = repair_one(M, (uint32_t)g.dus_per_mcu, b.segs, b.seg_idx, b.destuffed, entries, j);
     if (repaired) atomicAdd(&b.ctrl->repairs[pass], repaired);
 }
 
@@ -115,8 +116,8 @@ huff_fixup(const ScanGeom g, const ScanBufs b)
     stage_tables(g, b.lut_pool, st);
     const uint32_t k = blockIdx.x * 32 + threadIdx.x;
     if (k >= (uint32_t)g.num_segments) return;
-    const DecodeTables T = make_tables(g, st, b.slow);
-    fixup_segment(T, b.segs[k], b.destuffed, reinterpret_cast<unsigned long long*>(b.entries));
+    const DevMem M{&st, b.slow};
+    fixup_segment(M, (uint32_t)g.dus_per_mcu, b.segs[k], b.destuffed, reinterpret_cast<unsigned long long*>(b.entries));
 }
 
 constexpr int kScanThreads = 1024;
@@ -169,9 +170,9 @@ huff_write(const ScanGeom g, const ScanBufs b)
     stage_tables(g, b.lut_pool, st);
     const uint32_t j = blockIdx.x * kHuffThreads + threadIdx.x;
     if (j >= g.num_subs) return;
-    const DecodeTables T = make_tables(g, st, b.slow);
-    write_one(T, g, b.segs, b.seg_idx, b.destuffed,
-              reinterpret_cast<const unsigned long long*>(b.entries), b.qpos, b.coef, st.natural, j);
+    const DevMem M{&st, b.slow};
+    write_one(M, g, b.segs, b.seg_idx, b.destuffed,
+              reinterpret_cast<const unsigned long long*>(b.entries), b.qpos, b.coef, j);
 }
 
 } // namespace

@@ -60,16 +60,14 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     HuffSlow slow[kMaxTables];
     for (int t = 0; t < g.num_tables; ++t) g.table_off[t] = (uint16_t)build_lut(sp.tables[t], pool, slow[t]);
     g.lut_pool_u16 = (uint32_t)pool.size();
-    uint16_t dc_off[kMaxDuPerMcu], ac_off[kMaxDuPerMcu];
-    uint8_t dc_slot[kMaxDuPerMcu], ac_slot[kMaxDuPerMcu];
+    uint32_t offs[kMaxDuPerMcu], tbls[kMaxDuPerMcu];
     for (int s = 0; s < kMaxDuPerMcu; ++s) {
         const int ss = s < g.dus_per_mcu ? s : 0;
-        dc_off[s] = g.table_off[g.slot_dc[ss]];
-        ac_off[s] = g.table_off[g.slot_ac[ss]];
-        dc_slot[s] = g.slot_dc[ss];
-        ac_slot[s] = g.slot_ac[ss];
+        offs[s] = (uint32_t)g.table_off[g.slot_dc[ss]] | ((uint32_t)g.table_off[g.slot_ac[ss]] << 16);
+        tbls[s] = (uint32_t)g.slot_dc[ss] | ((uint32_t)g.slot_ac[ss] << 8);
     }
-    DecodeTables T{pool.data(), slow, dc_off, ac_off, dc_slot, ac_slot, g.dus_per_mcu};
+    const HostMem T{pool.data(), offs, tbls, slow, kNat};
+    const uint32_t K = (uint32_t)g.dus_per_mcu;
 
     // destuff: the contract of destuff_count + destuff_apply
     const uint32_t N = g.num_subs;
@@ -103,7 +101,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
 
     std::vector<unsigned long long> entries(N);
     std::vector<uint32_t> seg_idx(N), qpos(N + 1);
-    for (uint32_t j = 0; j < N; ++j) entries[j] = speculate_one(T, sp.segs.data(), g.num_segments, words, j, &seg_idx[j]);
+    for (uint32_t j = 0; j < N; ++j) entries[j] = speculate_one(T, K, sp.segs.data(), g.num_segments, words, j, &seg_idx[j]);
     // count wrong guesses
     int wrong = 0;
     for (uint32_t j = 0; j < N; ++j) {
@@ -122,7 +120,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
             const SegDesc& sg = sp.segs[seg_idx[j]];
             if (j == sg.sub_off) continue;
             if ((uint16_t)(snap[j - 1] >> 16) == (uint16_t)snap[j]) continue;
-            total += repair_one(T, sp.segs.data(), seg_idx.data(), words, entries.data(), j);
+            total += repair_one(T, K, sp.segs.data(), seg_idx.data(), words, entries.data(), j);
         }
         stats[pass] = (int)total;
         last = total;
@@ -135,7 +133,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     stats[3] = (int)N;
     stats[4] = bad;
     if (last != 0)
-        for (int k = 0; k < g.num_segments; ++k) fixup_segment(T, sp.segs[k], words, entries.data());
+        for (int k = 0; k < g.num_segments; ++k) fixup_segment(T, K, sp.segs[k], words, entries.data());
     uint32_t acc = 0;
     for (uint32_t j = 0; j < N; ++j) {
         qpos[j] = acc;
@@ -144,7 +142,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     qpos[N] = acc;
     memset(coef, 0, need * sizeof(int16_t));
     for (uint32_t j = 0; j < N; ++j)
-        write_one(T, g, sp.segs.data(), seg_idx.data(), words, entries.data(), qpos.data(), coef, kNat, j);
+        write_one(T, g, sp.segs.data(), seg_idx.data(), words, entries.data(), qpos.data(), coef, j);
     // DC: the contract of dc_tile_sums + dc_apply
     for (int a = 0; a < g.num_comp; ++a) {
         int pred = 0;
