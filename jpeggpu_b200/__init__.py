@@ -12,7 +12,8 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CSRC = os.path.join(ROOT, "jpeggpu_b200", "csrc")
-LIB_PATH = os.path.join(ROOT, "jpeggpu_b200", "lib", "libjpeggpu_b200.so")
+LIB_PATH = os.environ.get("JPEGGPU_B200_LIB") or os.path.join(ROOT, "jpeggpu_b200", "lib",
+                                                             "libjpeggpu_b200.so")
 
 MAX_COMP = 4
 

@@ -7,15 +7,16 @@
 //  * a symbol belongs to the subsequence in which it STARTS; the exit state records how many
 //    bits it ran past the boundary (the reference stops before such a symbol and keeps a cache);
 //  * one LUT probe yields code length + magnitude size + run, so the sync passes never extract
-//    the magnitude bits at all; the DC and the AC table are probed in parallel and selected
-//    afterwards, which keeps the table choice off the dependent chain;
-//  * the bit buffer is a 64-bit register fed from a 16-byte register chunk with the following
-//    chunk already in flight (destuff stores the scan as big-endian words), not a per-thread
-//    shared-memory cache: no global-load latency is exposed inside the symbol loop.
+//    the magnitude bits at all; the table for the next symbol is chosen when the slot
+//    counter is updated, off the bit-position dependent chain;
+//  * the bit buffer is a four-word register window read with one funnel shift per symbol and
+//    refilled two words ahead by a predicated load (destuff stores the scan as big-endian
+//    words), not a per-thread shared-memory cache: no branch and no exposed load latency
+//    inside the symbol loop.
 //
 // Memory access goes through a policy type `Mem` (shared memory on the device, plain arrays on the
 // host):  lut(i) -> uint16_t, slot_offs(c) -> dc_off | ac_off << 16, slot_tbls(c) -> dc table
-// slot | ac table slot << 8, chunk(words, i) -> 4 consecutive words, slow(slot) -> HuffSlow,
+// slot | ac table slot << 8, word(words, i) -> one big-endian word of the scan (word_if: predicated form), slow(slot) -> HuffSlow,
 // natural(i) -> zig-zag to raster index.
 #ifndef JB2_HUFF_CORE_HPP_
 #define JB2_HUFF_CORE_HPP_
@@ -23,10 +24,6 @@
 #include "common.hpp"
 
 namespace jb2 {
-
-struct Chunk4 {
-    uint32_t x, y, z, w;
-};
 
 // canonical search for codes the two LUT levels do not cover (pathological tables only)
 JB2_HD uint16_t slow_entry(const HuffSlow& t, uint32_t peek16)
@@ -60,78 +57,109 @@ JB2_HD int extend_value(uint32_t bits, uint32_t size)
     return bits < (1u << (size - 1)) ? (int)bits - (int)(1u << size) + 1 : (int)bits;
 }
 
+JB2_HD uint32_t funnel_left(uint32_t hi, uint32_t lo, uint32_t shift) // shift in [0, 31]
+{
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(lo, hi, shift);
+#else
+    return (uint32_t)(((((uint64_t)hi << 32) | lo) << shift) >> 32);
+#endif
+}
+
+// Per-scan table selection held in registers: the DU slots of an MCU are grouped by component
+// (at most four groups), so the table pair of slot c is a three-compare select chain instead of
+// a memory lookup (the reference does the same with an if-chain, src/decode_huffman.cu:323-338).
+struct SlotTables {
+    uint32_t t1, t2, t3;   // first slot of component group 1, 2, 3 (== K when absent)
+    uint32_t o0, o1, o2, o3; // dc_off | ac_off << 16 per group
+    uint32_t K;
+    JB2_HD uint32_t offs(uint32_t c) const { return c < t1 ? o0 : (c < t2 ? o1 : (c < t3 ? o2 : o3)); }
+};
+
+template <class Mem>
+JB2_HD SlotTables make_slot_tables(const Mem& M, uint32_t K)
+{
+    SlotTables S;
+    S.K = K;
+    S.o0 = S.o1 = S.o2 = S.o3 = M.slot_offs(0);
+    S.t1 = S.t2 = S.t3 = K;
+    uint32_t groups = 0, prev = S.o0;
+    for (uint32_t c = 1; c < K; ++c) {
+        const uint32_t v = M.slot_offs(c);
+        if (v != prev && groups < 3) {
+            ++groups;
+            if (groups == 1) S.t1 = c, S.o1 = S.o2 = S.o3 = v;
+            else if (groups == 2) S.t2 = c, S.o2 = S.o3 = v;
+            else S.t3 = c, S.o3 = v;
+            prev = v;
+        }
+    }
+    return S;
+}
+
 // Decode symbols that start in [p, end).  State: p bit position (segment relative), q linear
 // slot counter (q & 63 = zig-zag index), c DU index inside the MCU (K DUs per MCU).
 // WRITE: store non-zero coefficients at out[(q >> 6) * 64 + natural[q & 63]] while q < q_limit.
+//
+// Bit reader: a sliding window of four big-endian words w0..w3; the next 32 bits of the stream
+// are funnel(w0:w1 << o) with o in [0, 32).  Consuming bits only adds to o; when o crosses 32
+// the window slides by one word and the word two ahead is fetched (predicated, no branch), so a
+// load has at least 64 bits of decoding to complete before its value is needed.
+// The loop body is branch-free apart from the rare long-code path: lanes of a warp sit at
+// unrelated stream positions, so any data-dependent branch would be taken by some lane in
+// nearly every iteration and serialise the whole warp.
 template <bool WRITE, class Mem>
-JB2_HD void decode_span(const Mem& M, uint32_t K, const uint32_t* words, uint32_t& p,
+JB2_HD void decode_span(const Mem& M, const SlotTables& S, const uint32_t* words, uint32_t& p,
                         uint32_t end, uint32_t& q, uint32_t& c, int16_t* out, uint32_t q_limit)
 {
     if (p >= end) return;
     uint32_t pp = p, qq = q, cc = c;
+    uint32_t wi = pp >> 5;
+    uint32_t o = pp & 31u;
+    uint32_t w0 = M.word(words, wi), w1 = M.word(words, wi + 1), w2 = M.word(words, wi + 2),
+             w3 = M.word(words, wi + 3);
+    wi += 4;
 
-    // bit reader: `cur` is the chunk being consumed, `nxt` the prefetched one
-    uint32_t ci = pp >> 7;
-    uint32_t k = (pp >> 5) & 3u;
-    Chunk4 cur = M.chunk(words, ci), nxt = M.chunk(words, ci + 1);
-    auto take = [&]() -> uint32_t {
-        const uint32_t w = k == 0 ? cur.x : (k == 1 ? cur.y : (k == 2 ? cur.z : cur.w));
-        if (++k == 4) {
-            cur = nxt;
-            ++ci;
-            nxt = M.chunk(words, ci + 1);
-            k = 0;
-        }
-        return w;
-    };
-    const uint32_t w0 = take(), w1 = take();
-    uint64_t buf = (((uint64_t)w0 << 32) | (uint64_t)w1) << (pp & 31u);
-    int avail = 64 - (int)(pp & 31u);
-
-    uint32_t offs = M.slot_offs(cc);
-    uint32_t cn = cc + 1 == K ? 0 : cc + 1;
-    uint32_t offs_next = M.slot_offs(cn);
+    uint32_t offs = S.offs(cc);
+    uint32_t tbl = (qq & 63u) == 0 ? (offs & 0xffffu) : (offs >> 16);
 
     while (pp < end) {
         if (WRITE && qq >= q_limit) break;
-        if (avail <= 32) {
-            buf |= (uint64_t)take() << (32 - avail);
-            avail += 32;
-        }
-        const uint32_t hi = (uint32_t)(buf >> 32);
-        const uint32_t i1 = hi >> (32 - kLutBits);
-        const uint16_t e_dc = M.lut((offs & 0xffffu) + i1);
-        const uint16_t e_ac = M.lut((offs >> 16) + i1);
-        const bool is_dc = (qq & 63u) == 0;
-        uint16_t e = is_dc ? e_dc : e_ac;
+        const uint32_t peek = funnel_left(w0, w1, o);
+        uint32_t e = M.lut(tbl + (peek >> (32 - kLutBits)));
         if (e >= kEntrySlow) {
             const uint32_t tbls = M.slot_tbls(cc);
-            e = lookup_long(M, is_dc ? (offs & 0xffffu) : (offs >> 16),
-                            is_dc ? (tbls & 0xffu) : (tbls >> 8), hi >> 16, e);
+            e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16,
+                            (uint16_t)e);
         }
         const uint32_t skip = e & 31u;
-        const uint32_t size = (e >> 5) & 15u;
         const uint32_t adv = e >> 9;
         const uint32_t block_end = (qq | 63u) + 1u;
         if (WRITE) {
+            const uint32_t size = (e >> 5) & 15u;
             const uint32_t pos = qq + adv - 1u;
             if (size != 0 && pos < block_end) {
-                const uint32_t bits = (uint32_t)((buf << (skip - size)) >> (64 - size));
+                const uint32_t bits = (peek << (skip - size)) >> (32 - size);
                 out[(size_t)(pos & ~63u) + M.natural(pos & 63u)] = (int16_t)extend_value(bits, size);
             }
         }
-        buf <<= skip;
-        avail -= (int)skip;
+        o += skip;
         pp += skip;
-        uint32_t qn = qq + adv;
-        if (qn >= block_end) { // data unit complete (or overshoot on a garbage stream)
-            qn = block_end;
-            cc = cn;
-            offs = offs_next;
-            cn = cc + 1 == K ? 0 : cc + 1;
-            offs_next = M.slot_offs(cn);
-        }
-        qq = qn;
+        const bool slide = o >= 32u;
+        w0 = slide ? w1 : w0;
+        w1 = slide ? w2 : w1;
+        w2 = slide ? w3 : w2;
+        M.word_if(words, wi, slide, w3); // predicated load straight into w3: not waited for here
+        o = slide ? o - 32u : o;
+        wi += slide ? 1u : 0u;
+        // slot bookkeeping: a data unit ends on EOB / slot 63 (or overshoot on a garbage stream)
+        const uint32_t qn = qq + adv;
+        const bool done = qn >= block_end;
+        qq = done ? block_end : qn;
+        const uint32_t c1 = cc + 1u == S.K ? 0u : cc + 1u;
+        cc = done ? c1 : cc;
+        offs = S.offs(cc);
+        tbl = done ? (offs & 0xffffu) : (offs >> 16);
     }
     p = pp;
     q = qq;
@@ -150,10 +178,10 @@ struct HostMem {
     JB2_HD uint32_t slot_tbls(uint32_t c) const { return tbls_[c]; }
     JB2_HD const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     JB2_HD uint32_t natural(uint32_t i) const { return natural_[i]; }
-    JB2_HD Chunk4 chunk(const uint32_t* words, uint32_t i) const
+    JB2_HD uint32_t word(const uint32_t* words, uint32_t i) const { return words[i]; }
+    JB2_HD void word_if(const uint32_t* words, uint32_t i, bool pred, uint32_t& dst) const
     {
-        const uint32_t* w = words + (size_t)i * 4;
-        return Chunk4{w[0], w[1], w[2], w[3]};
+        if (pred) dst = words[i];
     }
 };
 

@@ -28,7 +28,7 @@ JB2_HD unsigned long long pack_entry(uint16_t gs, uint16_t xs, uint32_t n)
 
 // Decode subsequence i of a segment from packed entry state `gs`; returns {gs, exit, n}.
 template <class Mem>
-JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t K, const uint32_t* words,
+JB2_HD unsigned long long decode_sub(const Mem& M, const SlotTables& K, const uint32_t* words,
                                      uint32_t seg_bits, uint32_t i, uint16_t gs)
 {
     const uint32_t start = i * (uint32_t)kSubBits;
@@ -45,7 +45,7 @@ JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t K, const uint32_t* w
 
 // huff_speculate body: guess the entry state of subsequence j by a cold run-in, then decode it.
 template <class Mem>
-JB2_HD unsigned long long speculate_one(const Mem& M, uint32_t K, const SegDesc* segs, int num_segs,
+JB2_HD unsigned long long speculate_one(const Mem& M, const SlotTables& K, const SegDesc* segs, int num_segs,
                                         const uint32_t* destuffed, uint32_t j, uint32_t* seg_out)
 {
     const uint32_t k = find_segment(segs, num_segs, j);
@@ -64,7 +64,7 @@ JB2_HD unsigned long long speculate_one(const Mem& M, uint32_t K, const SegDesc*
 
 // huff_repair body. Returns the number of records rewritten.
 template <class Mem, typename EntryPtr>
-JB2_HD uint32_t repair_one(const Mem& M, uint32_t K, const SegDesc* segs, const uint32_t* seg_idx,
+JB2_HD uint32_t repair_one(const Mem& M, const SlotTables& K, const SegDesc* segs, const uint32_t* seg_idx,
                            const uint32_t* destuffed, EntryPtr entries, uint32_t j)
 {
     const SegDesc seg = segs[seg_idx[j]];
@@ -87,7 +87,7 @@ JB2_HD uint32_t repair_one(const Mem& M, uint32_t K, const SegDesc* segs, const 
 
 // huff_fixup body: sequential verification of one segment.
 template <class Mem>
-JB2_HD void fixup_segment(const Mem& M, uint32_t K, const SegDesc seg, const uint32_t* destuffed,
+JB2_HD void fixup_segment(const Mem& M, const SlotTables& K, const SegDesc seg, const uint32_t* destuffed,
                           unsigned long long* all_entries)
 {
     const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
@@ -108,7 +108,7 @@ JB2_HD void fixup_segment(const Mem& M, uint32_t K, const SegDesc seg, const uin
 
 // huff_write body.
 template <class Mem>
-JB2_HD void write_one(const Mem& M, const ScanGeom& g, const SegDesc* segs,
+JB2_HD void write_one(const Mem& M, const SlotTables& K, const ScanGeom& g, const SegDesc* segs,
                       const uint32_t* seg_idx, const uint32_t* destuffed,
                       const unsigned long long* entries, const uint32_t* qpos, int16_t* coef,
                       uint32_t j)
@@ -128,7 +128,7 @@ JB2_HD void write_one(const Mem& M, const ScanGeom& g, const SegDesc* segs,
     uint32_t p = i * (uint32_t)kSubBits + (gs & 31u);
     const uint32_t end = umin((i + 1u) * (uint32_t)kSubBits, seg.nbytes * 8u);
     const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
-    decode_span<true>(M, (uint32_t)g.dus_per_mcu, words, p, end, q, c, out, q_limit);
+    decode_span<true>(M, K, words, p, end, q, c, out, q_limit);
 }
 
 } // namespace jb2

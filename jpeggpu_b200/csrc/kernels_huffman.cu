@@ -57,7 +57,7 @@ __device__ __forceinline__ void stage_tables(const ScanGeom& g, const uint16_t* 
 }
 
 // Device memory policy of decode_span: LUTs and per-slot tables in shared memory, the destuffed
-// scan read as 16-byte chunks through the read-only path.
+// scan read word by word through the read-only path (L1 resident).
 struct DevMem {
     const SharedTables* st;
     const HuffSlow* slow_;
@@ -66,10 +66,19 @@ struct DevMem {
     __device__ __forceinline__ uint32_t slot_tbls(uint32_t c) const { return st->tbls[c]; }
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t natural(uint32_t i) const { return st->natural[i]; }
-    __device__ __forceinline__ Chunk4 chunk(const uint32_t* words, uint32_t i) const
+    __device__ __forceinline__ uint32_t word(const uint32_t* words, uint32_t i) const
     {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(words) + i);
-        return Chunk4{v.x, v.y, v.z, v.w};
+        return __ldg(words + i);
+    }
+    // Predicated load written straight into `dst`, so the scoreboard wait happens where the
+    // word is next read (one window slide later), not where it is requested.
+    __device__ __forceinline__ void word_if(const uint32_t* words, uint32_t i, bool pred,
+                                            uint32_t& dst) const
+    {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t"
+                     "@p ld.global.nc.u32 %0, [%1];\n\t}"
+                     : "+r"(dst)
+                     : "l"(words + i), "r"((uint32_t)pred));
     }
 };
 
@@ -83,7 +92,7 @@ huff_speculate(const ScanGeom g, const ScanBufs b)
     const DevMem M{&st, b.slow};
     uint32_t k;
     const unsigned long long e =
-        speculate_one(M, (uint32_t)g.dus_per_mcu, b.segs, g.num_segments, b.destuffed, j, &k);
+        speculate_one(M, make_slot_tables(M, (uint32_t)g.dus_per_mcu), b.segs, g.num_segments, b.destuffed, j, &k);
     b.seg_idx[j] = k;
     reinterpret_cast<unsigned long long*>(b.entries)[j] = e;
 }
@@ -101,7 +110,7 @@ huff_repair(const ScanGeom g, const ScanBufs b, int pass)
     if (j >= g.num_subs) return;
     const DevMem M{&st, b.slow};
     volatile unsigned long long* entries = reinterpret_cast<volatile unsigned long long*>(b.entries);
-    const uint32_t repaired = repair_one(M, (uint32_t)g.dus_per_mcu, b.segs, b.seg_idx, b.destuffed, entries, j);
+    const uint32_t repaired = repair_one(M, make_slot_tables(M, (uint32_t)g.dus_per_mcu), b.segs, b.seg_idx, b.destuffed, entries, j);
     if (repaired) atomicAdd(&b.ctrl->repairs[pass], repaired);
 }
 
@@ -117,7 +126,7 @@ huff_fixup(const ScanGeom g, const ScanBufs b)
     const uint32_t k = blockIdx.x * 32 + threadIdx.x;
     if (k >= (uint32_t)g.num_segments) return;
     const DevMem M{&st, b.slow};
-    fixup_segment(M, (uint32_t)g.dus_per_mcu, b.segs[k], b.destuffed, reinterpret_cast<unsigned long long*>(b.entries));
+    fixup_segment(M, make_slot_tables(M, (uint32_t)g.dus_per_mcu), b.segs[k], b.destuffed, reinterpret_cast<unsigned long long*>(b.entries));
 }
 
 constexpr int kScanThreads = 1024;
@@ -171,7 +180,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
     const uint32_t j = blockIdx.x * kHuffThreads + threadIdx.x;
     if (j >= g.num_subs) return;
     const DevMem M{&st, b.slow};
-    write_one(M, g, b.segs, b.seg_idx, b.destuffed,
+    write_one(M, make_slot_tables(M, (uint32_t)g.dus_per_mcu), g, b.segs, b.seg_idx, b.destuffed,
               reinterpret_cast<const unsigned long long*>(b.entries), b.qpos, b.coef, j);
 }
 

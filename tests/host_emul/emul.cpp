@@ -67,7 +67,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         tbls[s] = (uint32_t)g.slot_dc[ss] | ((uint32_t)g.slot_ac[ss] << 8);
     }
     const HostMem T{pool.data(), offs, tbls, slow, kNat};
-    const uint32_t K = (uint32_t)g.dus_per_mcu;
+    const SlotTables K = make_slot_tables(T, (uint32_t)g.dus_per_mcu);
 
     // destuff: the contract of destuff_count + destuff_apply
     const uint32_t N = g.num_subs;
@@ -142,7 +142,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     qpos[N] = acc;
     memset(coef, 0, need * sizeof(int16_t));
     for (uint32_t j = 0; j < N; ++j)
-        write_one(T, g, sp.segs.data(), seg_idx.data(), words, entries.data(), qpos.data(), coef, j);
+        write_one(T, K, g, sp.segs.data(), seg_idx.data(), words, entries.data(), qpos.data(), coef, j);
     // DC: the contract of dc_tile_sums + dc_apply
     for (int a = 0; a < g.num_comp; ++a) {
         int pred = 0;
