@@ -33,11 +33,18 @@ constexpr int kMaxTables = 8;     // 4 DC + 4 AC (src/defs.hpp:91)
 constexpr int kSubBytes = JB2_SUB_BYTES;
 constexpr int kSubBits = kSubBytes * 8;
 constexpr int kSubWords = kSubBytes / 4;
-// Run-in: a thread cold-starts this many subsequences before its own to guess its entry state.
-#ifndef JB2_RUNIN_SUBS
-#define JB2_RUNIN_SUBS 6
+// Overlap: the first kOverlapSubs lanes of a sync warp only warm up the decoder state for the
+// warp's remaining 32 - kOverlapSubs subsequences (kernels_huffman.cu).
+#ifndef JB2_OVERLAP_SUBS
+#define JB2_OVERLAP_SUBS 6
 #endif
-constexpr int kRunInSubs = JB2_RUNIN_SUBS;
+constexpr int kOverlapSubs = JB2_OVERLAP_SUBS;
+constexpr int kChunkSubs = 32 - kOverlapSubs; // subsequences whose records one sync warp owns
+
+// Destuff tiling (the host walk emits one TileDesc per tile, kernels_destuff.cu consumes them).
+constexpr int kDestuffThreads = 256;
+constexpr int kDestuffBytesPerThread = 16;
+constexpr int kDestuffTile = kDestuffThreads * kDestuffBytesPerThread; // stuffed bytes per CTA
 
 // ---- Huffman lookup tables -------------------------------------------------------------------
 // One table = header (8 u16) + primary LUT (2^kLutBits u16, indexed by the next kLutBits bits)
@@ -85,9 +92,16 @@ struct SegDesc {          // one per restart segment, built by the host walk
 };
 
 struct SubEntry { // per-subsequence sync record, stored as one 8-byte word
-    uint16_t g;   // packed entry state
+    uint16_t g;   // packed entry state (bit 15: first subsequence of a restart segment)
     uint16_t x;   // packed exit state given g
     uint32_t n;   // slots advanced inside the subsequence given g
+};
+constexpr uint16_t kStateHead = 0x8000u;
+constexpr uint16_t kStateMask = 0x7fffu;
+
+struct TileDesc {         // one per kDestuffTile stuffed bytes, built by the host walk
+    uint32_t kept_before; // destuffed data bytes of the scan before the tile's first byte
+    uint32_t segs_before; // restart markers completed before the tile's first byte
 };
 
 // packed state: overflow bits past the boundary (5) | DU index in MCU (4) | zig-zag index (6)
@@ -134,8 +148,10 @@ struct CoefPlanes {
 
 // Control block at the front of the per-scan work area (zeroed every decode).
 struct Control {
-    uint32_t repairs[8]; // repairs made by sync-repair pass i
-    uint32_t pad[8];
+    uint32_t relinked;    // warp-boundary mismatches healed inside huff_sync
+    uint32_t slow_repairs; // records rewritten by huff_link's sequential fallback
+    uint32_t link_rounds;
+    uint32_t pad[13];
 };
 
 // zig-zag -> natural order (T.81 Figure A.6; same table as src/defs.hpp:94-102)

@@ -4,7 +4,8 @@
 //    geometry), not by walking the pipeline twice with do_it=false/true;
 //  * one packed staging block + one copy per scan (entropy-coded bytes only) instead of the
 //    whole file plus 9+ table copies (src/decoder.cpp:175-208, quirk Q9);
-//  * one memset per scan; 12 launches per scan instead of ~40 stream operations;
+//  * no memset (kernels clear what they need) and 7 launches per scan instead of ~40 stream
+//    operations;
 //  * cumulative scratch-size check (reference quirk Q7).
 #include "huff_lut.hpp"
 #include "kernels.hpp"
@@ -26,12 +27,14 @@ size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct ScanLayout {
     // upload block (offsets inside the staging block == inside d_tmp)
-    size_t off_lut = 0, off_slow = 0, off_segs = 0;
+    size_t off_lut = 0, off_slow = 0, off_segs = 0, off_tiles = 0;
     // uploaded entropy-coded bytes
     size_t off_bytes = 0;
     // work area (shared by all scans of the image; scans run back to back on one stream)
-    size_t off_ctrl = 0, off_destuffed = 0, off_coef = 0, zero_bytes = 0;
-    size_t off_tile_agg = 0, off_entries = 0, off_qpos = 0, off_seg_idx = 0, off_dc_agg = 0;
+    size_t off_ctrl = 0, off_destuffed = 0, off_coef = 0, off_dc = 0;
+    size_t off_entries = 0, off_qpos = 0, off_seg_idx = 0, off_dc_agg = 0;
+    size_t coef_bytes = 0, dc_bytes = 0;
+    uint32_t num_chunks = 0;
     uint32_t destuffed_bytes = 0;
     uint32_t num_dus = 0;
 };
@@ -110,7 +113,7 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
             const uint32_t at = build_lut(sp.tables[t], pool, slow[s][t]);
             sp.geom.table_off[t] = (uint16_t)(at - pool_begin[s]);
         }
-        if (pool.size() & 1) pool.push_back(0);
+        while (pool.size() & 7) pool.push_back(0); // kernels stage the pool with 16-byte loads
         sp.geom.lut_pool_u16 = (uint32_t)(pool.size() - pool_begin[s]);
         if (sp.geom.lut_pool_u16 > 47 * 1024) return JPEGGPU_NOT_SUPPORTED; // > 94 KiB of LUTs
     }
@@ -124,6 +127,8 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         off += align256(sizeof(HuffSlow) * kMaxTables);
         L.off_segs = off;
         off += align256(sizeof(SegDesc) * (size_t)g.num_segments);
+        L.off_tiles = off;
+        off += align256(sizeof(TileDesc) * plan.scans[s].tiles.size());
     }
     upload_bytes = off;
     transfer_bytes = upload_bytes;
@@ -142,15 +147,17 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         size_t o = work_begin;
         L.num_dus = (uint32_t)g.total_mcus * (uint32_t)g.dus_per_mcu;
         L.destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
-        L.off_ctrl = o;
-        o += align256(sizeof(Control));
+        L.num_chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
+        L.off_ctrl = o; // control block and sync mailboxes are cleared as one range
+        o += align256(sizeof(Control) + (size_t)L.num_chunks * 4);
         L.off_destuffed = o;
         o += align256((size_t)g.num_subs * kSubBytes + 64);
         L.off_coef = o;
-        o += align256((size_t)L.num_dus * 128);
-        L.zero_bytes = o - L.off_ctrl;
-        L.off_tile_agg = o;
-        o += align256(((size_t)g.scan_bytes / kDestuffTile + 1) * 8);
+        L.coef_bytes = (size_t)L.num_dus * 128;
+        o += align256(L.coef_bytes);
+        L.off_dc = o;
+        L.dc_bytes = ((size_t)L.num_dus * 2 + 15) & ~(size_t)15;
+        o += align256(L.dc_bytes);
         L.off_entries = o;
         o += align256((size_t)g.num_subs * sizeof(SubEntry));
         L.off_qpos = o;
@@ -173,6 +180,8 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         memcpy(staging + L.off_slow, slow[s], sizeof(HuffSlow) * (size_t)sp.geom.num_tables);
         if (!sp.segs.empty())
             memcpy(staging + L.off_segs, sp.segs.data(), sizeof(SegDesc) * sp.segs.size());
+        if (!sp.tiles.empty())
+            memcpy(staging + L.off_tiles, sp.tiles.data(), sizeof(TileDesc) * sp.tiles.size());
     }
     return JPEGGPU_SUCCESS;
 }
@@ -186,10 +195,15 @@ ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
     b.segs = reinterpret_cast<const SegDesc*>(base + L.off_segs);
     b.lut_pool = reinterpret_cast<const uint16_t*>(base + L.off_lut);
     b.slow = reinterpret_cast<const HuffSlow*>(base + L.off_slow);
+    b.tiles = reinterpret_cast<const TileDesc*>(base + L.off_tiles);
     b.ctrl = reinterpret_cast<Control*>(base + L.off_ctrl);
+    b.chunk_state = reinterpret_cast<uint32_t*>(base + L.off_ctrl + sizeof(Control));
+    b.num_chunks = L.num_chunks;
     b.destuffed = reinterpret_cast<uint32_t*>(base + L.off_destuffed);
     b.coef = reinterpret_cast<int16_t*>(base + L.off_coef);
-    b.tile_agg = reinterpret_cast<unsigned long long*>(base + L.off_tile_agg);
+    b.coef_bytes = L.coef_bytes;
+    b.dc = reinterpret_cast<int16_t*>(base + L.off_dc);
+    b.dc_bytes = L.dc_bytes;
     b.entries = reinterpret_cast<SubEntry*>(base + L.off_entries);
     b.qpos = reinterpret_cast<uint32_t*>(base + L.off_qpos);
     b.seg_idx = reinterpret_cast<uint32_t*>(base + L.off_seg_idx);
@@ -218,10 +232,11 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
     for (int s = 0; s < plan.num_scans; ++s) {
         const ScanPlan& sp = plan.scans[s];
         const ScanGeom& g = sp.geom;
-        const ScanLayout& L = layout[s];
         const ScanBufs b = bufs(s, d_tmp);
-        timer.mark(stream, kIdMemset);
-        JB2_CUDA(cudaMemsetAsync(b.ctrl, 0, L.zero_bytes, stream));
+        if (g.num_subs == 0) { // degenerate scan without entropy data: huff_sync will not run
+            JB2_CUDA(cudaMemsetAsync(b.coef, 0, b.coef_bytes, stream));
+            JB2_CUDA(cudaMemsetAsync(b.dc, 0, b.dc_bytes, stream));
+        }
         JB2_CUDA(launch_destuff(g, b, stream, &timer));
         JB2_CUDA(launch_huffman(g, b, stream, &timer));
         JB2_CUDA(launch_dc(g, b, stream, &timer));
@@ -483,9 +498,8 @@ enum jpeggpu_status jpeggpu_b200_get_kernel_times(
 const char* jpeggpu_b200_kernel_name(int id)
 {
     static const char* names[kIdCount] = {
-        "memset", "destuff_count", "destuff_apply", "huff_speculate", "huff_repair_0",
-        "huff_repair_1", "huff_repair_2", "huff_fixup", "sub_scan", "huff_write", "dc_tile_sums",
-        "dc_apply", "idct_kernel", "transpose_kernel"};
+        "destuff_kernel", "huff_sync", "huff_link", "huff_write", "dc_tile_sums", "dc_apply",
+        "idct_kernel", "transpose_kernel"};
     return id >= 0 && id < kIdCount ? names[id] : "";
 }
 

@@ -1,5 +1,5 @@
-// huff_threads.hpp — the per-thread bodies of the Huffman sync / write kernels as host+device
-// functions, so tests/host_emul can run the exact same logic sequentially on a CPU.
+// huff_threads.hpp — the per-thread bodies of the Huffman sync / link / write kernels as
+// host+device functions, so tests/host_emul can run the exact same logic sequentially on a CPU.
 #ifndef JB2_HUFF_THREADS_HPP_
 #define JB2_HUFF_THREADS_HPP_
 
@@ -25,110 +25,83 @@ JB2_HD unsigned long long pack_entry(uint16_t gs, uint16_t xs, uint32_t n)
 {
     return (unsigned long long)gs | ((unsigned long long)xs << 16) | ((unsigned long long)n << 32);
 }
+JB2_HD uint16_t entry_g(unsigned long long e) { return (uint16_t)e; }
+JB2_HD uint16_t entry_x(unsigned long long e) { return (uint16_t)(e >> 16); }
+JB2_HD uint32_t entry_n(unsigned long long e) { return (uint32_t)(e >> 32); }
 
-// Decode subsequence i of a segment from packed entry state `gs`; returns {gs, exit, n}.
+JB2_HD uint32_t subs_in_segment(const SegDesc& seg)
+{
+    return (seg.nbytes + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes;
+}
+
+// Decode subsequence i of a segment (policy M addresses words relative to the segment start)
+// from packed entry state `gs` (15 bits); returns {gs, exit state, slots advanced}.
 template <class Mem>
-JB2_HD unsigned long long decode_sub(const Mem& M, const SlotTables& K, const uint32_t* words,
-                                     uint32_t seg_bits, uint32_t i, uint16_t gs)
+JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t seg_bits, uint32_t i, uint16_t gs)
 {
     const uint32_t start = i * (uint32_t)kSubBits;
     const uint32_t sub_end = start + (uint32_t)kSubBits;
     const uint32_t end = umin(sub_end, seg_bits);
     uint32_t p = start + (gs & 31u);
     uint32_t c = (gs >> 5) & 15u;
-    const uint32_t z = gs >> 9;
+    const uint32_t z = (gs >> 9) & 63u;
     uint32_t q = z;
-    decode_span<false>(M, K, words, p, end, q, c, nullptr, 0u);
+    decode_span<false>(M, p, end, q, c, nullptr, nullptr, 0u);
     const uint32_t o = p > sub_end ? p - sub_end : 0u;
     return pack_entry(gs, pack_state(o, c, q & 63u), q - z);
 }
 
-// huff_speculate body: guess the entry state of subsequence j by a cold run-in, then decode it.
-template <class Mem>
-JB2_HD unsigned long long speculate_one(const Mem& M, const SlotTables& K, const SegDesc* segs, int num_segs,
-                                        const uint32_t* destuffed, uint32_t j, uint32_t* seg_out)
+// huff_link: does the record of subsequence j start where its predecessor stopped?
+JB2_HD bool boundary_ok(unsigned long long prev, unsigned long long cur)
 {
-    const uint32_t k = find_segment(segs, num_segs, j);
-    const SegDesc seg = segs[k];
-    *seg_out = k;
-    const uint32_t i = j - seg.sub_off;
-    const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
-    // run-in: cold start (or the true segment start) up to kRunInSubs subsequences earlier
-    const uint32_t i0 = i > (uint32_t)kRunInSubs ? i - (uint32_t)kRunInSubs : 0u;
-    uint32_t p = i0 * (uint32_t)kSubBits, q = 0, c = 0;
-    const uint32_t boundary = i * (uint32_t)kSubBits;
-    decode_span<false>(M, K, words, p, boundary, q, c, nullptr, 0u);
-    const uint16_t gs = pack_state(p - boundary, c, q & 63u);
-    return decode_sub(M, K, words, seg.nbytes * 8u, i, gs);
+    return (entry_g(cur) & kStateHead) != 0 || (entry_g(cur) & kStateMask) == entry_x(prev);
 }
 
-// huff_repair body. Returns the number of records rewritten.
+// huff_link fallback: re-decode forward from subsequence j (entry = exit of j-1) until the
+// stored records agree again.  M addresses words relative to the segment start.  Returns the
+// number of records rewritten.
 template <class Mem, typename EntryPtr>
-JB2_HD uint32_t repair_one(const Mem& M, const SlotTables& K, const SegDesc* segs, const uint32_t* seg_idx,
-                           const uint32_t* destuffed, EntryPtr entries, uint32_t j)
+JB2_HD uint32_t relink_from(const Mem& M, const SegDesc& seg, EntryPtr entries, uint32_t j)
 {
-    const SegDesc seg = segs[seg_idx[j]];
-    if (j == seg.sub_off) return 0; // first record of a segment starts from the initial state
-    uint16_t state = (uint16_t)(entries[j - 1] >> 16);
-    if (state == (uint16_t)entries[j]) return 0;
-    const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
     const uint32_t seg_bits = seg.nbytes * 8u;
-    const uint32_t seg_end = seg.sub_off + (seg.nbytes + kSubBytes - 1) / kSubBytes;
-    uint32_t repaired = 0;
+    const uint32_t seg_end = seg.sub_off + subs_in_segment(seg);
+    uint16_t state = entry_x(entries[j - 1]);
+    uint32_t rewritten = 0;
     for (uint32_t m = j; m < seg_end; ++m) {
-        if (m != j && state == (uint16_t)entries[m]) break;
-        const unsigned long long e = decode_sub(M, K, words, seg_bits, m - seg.sub_off, state);
+        if (m != j && (entry_g(entries[m]) & kStateMask) == state) break;
+        const unsigned long long e = decode_sub(M, seg_bits, m - seg.sub_off, state);
         entries[m] = e;
-        state = (uint16_t)(e >> 16);
-        ++repaired;
+        state = entry_x(e);
+        ++rewritten;
     }
-    return repaired;
+    return rewritten;
 }
 
-// huff_fixup body: sequential verification of one segment.
-template <class Mem>
-JB2_HD void fixup_segment(const Mem& M, const SlotTables& K, const SegDesc seg, const uint32_t* destuffed,
-                          unsigned long long* all_entries)
+// Placement of a restart segment in the coefficient buffer (T.81 E.1.4: every segment but the
+// last holds Ri MCUs).  Returns false for a surplus segment (nothing to place).
+JB2_HD bool segment_extent(const ScanGeom& g, uint32_t k, uint32_t& first_du, uint32_t& q_limit)
 {
-    const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
-    const uint32_t seg_bits = seg.nbytes * 8u;
-    const uint32_t count = (seg.nbytes + kSubBytes - 1) / kSubBytes;
-    unsigned long long* entries = all_entries + seg.sub_off;
-    if (count == 0) return;
-    uint16_t state = (uint16_t)(entries[0] >> 16);
-    for (uint32_t i = 1; i < count; ++i) {
-        unsigned long long e = entries[i];
-        if ((uint16_t)e != state) {
-            e = decode_sub(M, K, words, seg_bits, i, state);
-            entries[i] = e;
-        }
-        state = (uint16_t)(e >> 16);
-    }
-}
-
-// huff_write body.
-template <class Mem>
-JB2_HD void write_one(const Mem& M, const SlotTables& K, const ScanGeom& g, const SegDesc* segs,
-                      const uint32_t* seg_idx, const uint32_t* destuffed,
-                      const unsigned long long* entries, const uint32_t* qpos, int16_t* coef,
-                      uint32_t j)
-{
-    const uint32_t k = seg_idx[j];
-    const SegDesc seg = segs[k];
-    // MCUs coded by this segment (T.81 E.1.4: every segment but the last holds Ri MCUs)
     const unsigned long long mcu0 = (unsigned long long)k * (unsigned)g.restart_interval;
-    if (mcu0 >= (unsigned long long)g.total_mcus) return; // surplus segment: nothing to place
+    if (mcu0 >= (unsigned long long)g.total_mcus) return false;
     const uint32_t mcus = umin((uint32_t)g.restart_interval, (uint32_t)g.total_mcus - (uint32_t)mcu0);
-    const uint32_t q_limit = mcus * (uint32_t)g.dus_per_mcu * 64u;
-    int16_t* out = coef + (size_t)mcu0 * g.dus_per_mcu * 64;
-    const uint32_t i = j - seg.sub_off;
-    const uint16_t gs = (uint16_t)entries[j];
-    uint32_t q = qpos[j] - qpos[seg.sub_off];
+    first_du = (uint32_t)mcu0 * (uint32_t)g.dus_per_mcu;
+    q_limit = mcus * (uint32_t)g.dus_per_mcu * 64u;
+    return true;
+}
+
+// huff_write body: decode subsequence i of segment k from its verified record and place the
+// coefficients.  q0 = slot (segment relative) at which the subsequence starts.
+template <class Mem>
+JB2_HD void write_sub(const Mem& M, const ScanGeom& g, const SegDesc& seg, uint32_t k, uint32_t i,
+                      uint16_t gs, uint32_t q0, int16_t* coef, int16_t* dc)
+{
+    uint32_t first_du, q_limit;
+    if (!segment_extent(g, k, first_du, q_limit)) return;
+    uint32_t q = q0;
     uint32_t c = (gs >> 5) & 15u;
     uint32_t p = i * (uint32_t)kSubBits + (gs & 31u);
     const uint32_t end = umin((i + 1u) * (uint32_t)kSubBits, seg.nbytes * 8u);
-    const uint32_t* words = destuffed + (size_t)seg.sub_off * kSubWords;
-    decode_span<true>(M, K, words, p, end, q, c, out, q_limit);
+    decode_span<true>(M, p, end, q, c, coef + (size_t)first_du * 64, dc + first_du, q_limit);
 }
 
 } // namespace jb2

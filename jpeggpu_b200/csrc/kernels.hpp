@@ -10,25 +10,26 @@
 
 namespace jb2 {
 
-constexpr int kDestuffThreads = 256;
-constexpr int kDestuffBytesPerThread = 16;
-constexpr int kDestuffTile = kDestuffThreads * kDestuffBytesPerThread; // stuffed bytes per CTA
 constexpr int kHuffThreads = 128;
-constexpr int kRepairPasses = 3;
-constexpr int kDcTile = 256; // MCUs per CTA in the DC scan
+constexpr int kDcTile = 256;  // MCUs per CTA in the DC scan
 
 // Device pointers of one scan (all inside the caller's scratch buffer).
 struct ScanBufs {
     const uint8_t* scan_bytes; // stuffed entropy-coded bytes (uploaded)
     const SegDesc* segs;       // uploaded
+    const TileDesc* tiles;     // uploaded: one per kDestuffTile stuffed bytes
     const uint16_t* lut_pool;  // uploaded
     const HuffSlow* slow;      // uploaded
-    Control* ctrl;             // zeroed
-    uint32_t* destuffed;       // zeroed; big-endian words, segment k at sub_off * kSubWords
-    int16_t* coef;             // zeroed; DU-major coded order, 64 natural-order int16 per DU
-    unsigned long long* tile_agg; // destuff tile aggregates
+    Control* ctrl;             // zeroed by destuff
+    uint32_t* chunk_state;     // zeroed by destuff: one mailbox per sync warp
+    uint32_t num_chunks;
+    uint32_t* destuffed;       // big-endian words, segment k at sub_off * kSubWords
+    int16_t* coef;             // zeroed by huff_sync; DU-major coded order, 64 natural-order int16 per DU
+    size_t coef_bytes;         // multiple of 16
+    int16_t* dc;               // zeroed by huff_sync; one DC difference per DU, coded order
+    size_t dc_bytes;           // multiple of 16
     SubEntry* entries;         // N
-    uint32_t* qpos;            // N + 1 exclusive prefix of entries[].n
+    uint32_t* qpos;            // N: first slot (segment relative) of every subsequence
     uint32_t* seg_idx;         // N
     int* dc_agg;               // 4 per DC tile
 };
@@ -36,8 +37,7 @@ struct ScanBufs {
 // Optional per-kernel timing (jpeggpu_b200_set_profiling): an event is recorded on the launching
 // stream before every kernel and one after the last; off by default and absent from timed runs.
 enum KernelId {
-    kIdMemset = 0, kIdDestuffCount, kIdDestuffApply, kIdSpeculate, kIdRepair0, kIdRepair1,
-    kIdRepair2, kIdFixup, kIdSubScan, kIdWrite, kIdDcSums, kIdDcApply, kIdIdct, kIdTranspose,
+    kIdDestuff = 0, kIdSync, kIdLink, kIdWrite, kIdDcSums, kIdDcApply, kIdIdct, kIdTranspose,
     kIdCount
 };
 

@@ -4,6 +4,9 @@
 //
 // Work unit = MCU.  Restart boundaries fall on multiples of the restart interval, so the carry
 // into a tile of kDcTile MCUs is pure arithmetic over per-tile aggregates:
+// Input: the compact array of DC differences huff_write produced (one int16 per DU, coded
+// order: contiguous, unlike the reference's 128-byte-strided permutation iterator); output: the
+// absolute DC value stored into slot 0 of every DU of the coefficient buffer.
 //   dc_tile_sums : agg[t][a] = sum of component a's DC differences over the MCUs of tile t that
 //                  follow the last restart boundary inside t (whole tile if none)
 //   dc_apply     : carry = sum of agg over the tiles back to the one holding the segment start,
@@ -19,17 +22,17 @@ struct Dc4 {
     int v[kMaxComp];
 };
 
-__device__ __forceinline__ void load_mcu(const ScanGeom& g, const int16_t* __restrict__ coef,
+__device__ __forceinline__ void load_mcu(const ScanGeom& g, const int16_t* __restrict__ dc,
                                          uint32_t mcu, int (&diff)[kMaxDuPerMcu], Dc4& tot)
 {
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) tot.v[a] = 0;
-    const int16_t* base = coef + (size_t)mcu * g.dus_per_mcu * 64;
+    const int16_t* base = dc + (size_t)mcu * g.dus_per_mcu;
 #pragma unroll
     for (int s = 0; s < kMaxDuPerMcu; ++s) {
         diff[s] = 0;
         if (s < g.dus_per_mcu) {
-            diff[s] = base[s * 64];
+            diff[s] = base[s];
             const int a = g.slot_comp[s];
 #pragma unroll
             for (int k = 0; k < kMaxComp; ++k)
@@ -89,7 +92,7 @@ __device__ __forceinline__ Dc4 block_segmented_scan(Dc4 val, bool head, Dc4* war
 }
 
 __global__ void __launch_bounds__(kDcTile)
-dc_tile_sums(const ScanGeom g, const int16_t* __restrict__ coef, int* __restrict__ agg)
+dc_tile_sums(const ScanGeom g, const int16_t* __restrict__ dc, int* __restrict__ agg)
 {
     __shared__ Dc4 warp_val[kDcTile / 32];
     __shared__ uint32_t warp_flag[kDcTile / 32];
@@ -99,7 +102,7 @@ dc_tile_sums(const ScanGeom g, const int16_t* __restrict__ coef, int* __restrict
     Dc4 tot;
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) tot.v[a] = 0;
-    if (valid) load_mcu(g, coef, mcu, diff, tot);
+    if (valid) load_mcu(g, dc, mcu, diff, tot);
     const bool head = valid && (mcu % (uint32_t)g.restart_interval) == 0;
     Dc4 tail;
     block_segmented_scan(tot, head, warp_val, warp_flag, tail);
@@ -110,7 +113,8 @@ dc_tile_sums(const ScanGeom g, const int16_t* __restrict__ coef, int* __restrict
 }
 
 __global__ void __launch_bounds__(kDcTile)
-dc_apply(const ScanGeom g, int16_t* __restrict__ coef, const int* __restrict__ agg)
+dc_apply(const ScanGeom g, const int16_t* __restrict__ dc, int16_t* __restrict__ coef,
+         const int* __restrict__ agg)
 {
     __shared__ Dc4 warp_val[kDcTile / 32];
     __shared__ uint32_t warp_flag[kDcTile / 32];
@@ -146,7 +150,7 @@ dc_apply(const ScanGeom g, int16_t* __restrict__ coef, const int* __restrict__ a
     Dc4 tot;
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) tot.v[a] = 0;
-    if (valid) load_mcu(g, coef, mcu, diff, tot);
+    if (valid) load_mcu(g, dc, mcu, diff, tot);
     const bool head = valid && (mcu % ri) == 0;
     Dc4 tail;
     const Dc4 inc = block_segmented_scan(tot, head, warp_val, warp_flag, tail);
@@ -181,9 +185,9 @@ cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream,
     if (g.total_mcus == 0) return cudaSuccess;
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
     tm->mark(stream, kIdDcSums);
-    dc_tile_sums<<<tiles, kDcTile, 0, stream>>>(g, b.coef, b.dc_agg);
+    dc_tile_sums<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.dc_agg);
     tm->mark(stream, kIdDcApply);
-    dc_apply<<<tiles, kDcTile, 0, stream>>>(g, b.coef, b.dc_agg);
+    dc_apply<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.coef, b.dc_agg);
     return cudaGetLastError();
 }
 

@@ -1,13 +1,15 @@
 // kernels_destuff.cu — byte unstuffing + restart-segment placement (reference stage a1,
 // src/decode_destuff.cu:37-148 + the three CUB scans at :220-316).
 //
-// Two launches, 16-byte vector loads, no per-byte int arrays:
-//   destuff_count : per 4 KiB tile of stuffed bytes, count data bytes and restart markers
-//   destuff_apply : tile prefix = sum of the earlier tiles' aggregates (tiny, L2 resident),
-//                   block scan, compaction through shared memory, coalesced byte stores.
+// One launch, 16-byte vector loads, no per-byte int arrays: each CTA takes one 4 KiB tile of
+// stuffed bytes.  The tile's prefix (data bytes and restart markers before it) comes from the
+// host walk that already visits every 0xff to find the end of the scan (parser.cpp walk_scan,
+// the reference's src/reader.cpp:443-489), so tiles are independent: classify, block scan,
+// compaction through shared memory, coalesced stores.  The kernel also clears the control block
+// and the sync mailboxes of the Huffman stage and writes the zero padding behind every segment.
 // Output is the destuffed scan stored as big-endian 32-bit words (byte d lands at d ^ 3) so the
 // Huffman kernels read MSB-first words directly; segment k starts at segs[k].sub_off*kSubBytes.
-// Algorithmic bytes: Sb read + Sd written (the count pass re-reads Sb from L2).
+// Algorithmic bytes: Sb read + Sd written.
 #include "kernels.hpp"
 
 namespace jb2 {
@@ -76,46 +78,21 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* w
 }
 
 __global__ void __launch_bounds__(kDestuffThreads)
-destuff_count(const uint8_t* __restrict__ src, uint32_t n, unsigned long long* __restrict__ agg)
+destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __restrict__ tiles,
+               const SegDesc* __restrict__ segs, int num_segments, uint8_t* __restrict__ dst,
+               uint32_t* __restrict__ clear, uint32_t clear_words)
 {
     __shared__ uint32_t warp_sums[kDestuffThreads / 32];
-    const uint32_t base = (blockIdx.x * kDestuffThreads + threadIdx.x) * kDestuffBytesPerThread;
-    Chunk ck;
-    classify(src, n, base, ck);
-    uint32_t v = __popc(ck.keep) | (__popc(ck.rst) << 16);
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-    if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t t = 0;
-        for (int w = 0; w < kDestuffThreads / 32; ++w) t += warp_sums[w];
-        agg[blockIdx.x] = (unsigned long long)(t & 0xffffu) | ((unsigned long long)(t >> 16) << 32);
-    }
-}
-
-__global__ void __launch_bounds__(kDestuffThreads)
-destuff_apply(const uint8_t* __restrict__ src, uint32_t n,
-              const unsigned long long* __restrict__ agg, const SegDesc* __restrict__ segs,
-              int num_segments, uint8_t* __restrict__ dst)
-{
-    __shared__ uint32_t warp_sums[kDestuffThreads / 32];
-    __shared__ unsigned long long red[kDestuffThreads / 32];
     __shared__ uint8_t stage[kDestuffTile];
     __shared__ uint16_t seg_delta[kDestuffTile];
 
-    // tile prefix: data bytes and restart markers in all earlier tiles
-    unsigned long long prior = 0;
-    for (uint32_t t = threadIdx.x; t < blockIdx.x; t += kDestuffThreads) prior += agg[t];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) prior += __shfl_xor_sync(0xffffffffu, prior, d);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = prior;
-    __syncthreads();
-    prior = 0;
-#pragma unroll
-    for (int w = 0; w < kDestuffThreads / 32; ++w) prior += red[w];
-    const uint32_t kept_base = (uint32_t)prior;
-    const uint32_t seg_base = (uint32_t)(prior >> 32);
+    for (uint32_t i = blockIdx.x * kDestuffThreads + threadIdx.x; i < clear_words;
+         i += gridDim.x * kDestuffThreads)
+        clear[i] = 0u;
+
+    const TileDesc tile = tiles[blockIdx.x];
+    const uint32_t kept_base = tile.kept_before;
+    const uint32_t seg_base = tile.segs_before;
 
     const uint32_t base = (blockIdx.x * kDestuffThreads + threadIdx.x) * kDestuffBytesPerThread;
     Chunk ck;
@@ -136,22 +113,18 @@ destuff_apply(const uint8_t* __restrict__ src, uint32_t n,
     __syncthreads();
 
     const uint32_t tile_kept = tile_total & 0xffffu;
-    // destination of data byte number k of the scan: k + sub_off*kSubBytes - kept_before
-    uint32_t adj0 = 0;
-    if ((int)seg_base < num_segments)
-        adj0 = segs[seg_base].sub_off * (uint32_t)kSubBytes - segs[seg_base].kept_before;
     for (uint32_t o = threadIdx.x; o < tile_kept; o += kDestuffThreads) {
-        const uint32_t sd = seg_delta[o];
-        uint32_t adj = adj0;
-        if (sd) {
-            const uint32_t s = seg_base + sd;
-            if ((int)s >= num_segments) continue; // cannot happen: host and device rules agree
-            adj = segs[s].sub_off * (uint32_t)kSubBytes - segs[s].kept_before;
-        } else if ((int)seg_base >= num_segments) {
-            continue;
-        }
-        const uint32_t d = kept_base + o + adj;
+        const uint32_t s = seg_base + seg_delta[o];
+        if ((int)s >= num_segments) continue; // cannot happen: host and device rules agree
+        const SegDesc sd = segs[s];
+        // data byte number k of the scan lands at k - kept_before + sub_off * kSubBytes
+        const uint32_t r = kept_base + o - sd.kept_before; // index inside the segment
+        const uint32_t d = r + sd.sub_off * (uint32_t)kSubBytes;
         dst[d ^ 3u] = stage[o];
+        if (r + 1u == sd.nbytes) { // last byte of the segment: pad to a whole subsequence
+            const uint32_t pad_end = (d + (uint32_t)kSubBytes) / (uint32_t)kSubBytes * (uint32_t)kSubBytes;
+            for (uint32_t z = d + 1u; z < pad_end; ++z) dst[z ^ 3u] = 0;
+        }
     }
 }
 
@@ -161,12 +134,12 @@ cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
 {
     if (g.scan_bytes == 0) return cudaSuccess;
     const uint32_t tiles = (g.scan_bytes + kDestuffTile - 1) / kDestuffTile;
-    tm->mark(stream, kIdDestuffCount);
-    destuff_count<<<tiles, kDestuffThreads, 0, stream>>>(b.scan_bytes, g.scan_bytes, b.tile_agg);
-    tm->mark(stream, kIdDestuffApply);
-    destuff_apply<<<tiles, kDestuffThreads, 0, stream>>>(
-        b.scan_bytes, g.scan_bytes, b.tile_agg, b.segs, g.num_segments,
-        reinterpret_cast<uint8_t*>(b.destuffed));
+    // the control block and the mailboxes are contiguous (planner): one clear range
+    const uint32_t clear_words = (uint32_t)(sizeof(Control) / 4) + b.num_chunks;
+    tm->mark(stream, kIdDestuff);
+    destuff_kernel<<<tiles, kDestuffThreads, 0, stream>>>(
+        b.scan_bytes, g.scan_bytes, b.tiles, b.segs, g.num_segments,
+        reinterpret_cast<uint8_t*>(b.destuffed), reinterpret_cast<uint32_t*>(b.ctrl), clear_words);
     return cudaGetLastError();
 }
 

@@ -181,8 +181,8 @@ cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPla
 int count_launches(const ScanGeom& g, bool with_transpose)
 {
     int n = 0;
-    if (g.scan_bytes) n += 2;
-    if (g.num_subs) n += 1 + kRepairPasses + 1 + 1 + 1;
+    if (g.scan_bytes) n += 1;
+    if (g.num_subs) n += 3;
     if (g.total_mcus) n += 2;
     n += 1; // idct
     if (with_transpose) n += 1;

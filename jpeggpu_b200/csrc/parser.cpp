@@ -227,13 +227,28 @@ jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp)
         kept_before += kept;
         kept = 0;
     };
+    // tile directory for the destuff kernel: totals before every kDestuffTile-th stuffed byte
+    uint64_t tile_next = 0;
+    auto emit_tiles = [&](uint64_t upto, uint64_t from, bool counting) {
+        // boundaries in [tile_next, upto]; inside a run of plain bytes (counting) every byte
+        // between `from` and the boundary is a data byte
+        while (tile_next <= upto) {
+            TileDesc t;
+            t.kept_before = (uint32_t)(kept_before + kept + (counting ? tile_next - from : 0));
+            t.segs_before = (uint32_t)sp.segs.size();
+            sp.tiles.push_back(t);
+            tile_next += kDestuffTile;
+        }
+    };
     for (;;) {
         const uint8_t* ff = (const uint8_t*)memchr(p, 0xff, (size_t)(end - p));
         if (!ff) return JPEGGPU_INVALID_JPEG; // no EOI
+        emit_tiles((uint64_t)(ff - scan_begin), (uint64_t)(p - scan_begin), true);
         kept += (uint64_t)(ff - p);
         const uint8_t* q = ff + 1;
         while (q < end && *q == 0xff) ++q; // fill bytes
         if (q >= end) return JPEGGPU_INVALID_JPEG;
+        emit_tiles((uint64_t)(q - scan_begin), 0, false);
         const unsigned m = *q;
         if (m == 0) {
             ++kept;
@@ -256,6 +271,7 @@ jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp)
     sp.geom.scan_bytes = (uint32_t)(sp.end - sp.begin);
     sp.geom.num_subs = (uint32_t)sub_off;
     sp.geom.num_segments = (int)sp.segs.size();
+    sp.tiles.resize(((size_t)sp.geom.scan_bytes + kDestuffTile - 1) / kDestuffTile);
     return JPEGGPU_SUCCESS;
 }
 

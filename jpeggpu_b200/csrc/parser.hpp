@@ -29,6 +29,7 @@ struct ScanPlan {
     ScanGeom geom;
     size_t begin = 0, end = 0;   // byte range of the entropy-coded data in the file
     std::vector<SegDesc> segs;   // restart-segment directory
+    std::vector<TileDesc> tiles; // destuff tile directory
     HuffSpec tables[kMaxTables]; // the tables this scan uses, by table slot
     int qidx[kMaxComp] = {};     // quantisation table of each scan component
 };

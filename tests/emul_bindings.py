@@ -39,10 +39,12 @@ def parse(data: bytes):
     return st, out
 
 
-def decode_scan(data: bytes, scan, coef_count, destuffed_bytes=0):
+def decode_scan(data: bytes, scan, coef_count, destuffed_bytes=0, corrupt_records=False):
     buf = np.frombuffer(data, dtype=np.uint8)
     coef = np.zeros(coef_count, dtype=np.int16)
     stats = np.zeros(8, dtype=np.int32)
+    if corrupt_records:
+        stats[7] = 12345  # emul.cpp test hook: damage sync records before huff_link
     dst = np.zeros(destuffed_bytes, dtype=np.uint8) if destuffed_bytes else None
     st = lib().emul_decode_scan(buf.ctypes.data, len(data), scan, coef.ctypes.data, coef.size,
                                 dst.ctypes.data if dst is not None else None, destuffed_bytes,

@@ -41,8 +41,9 @@ int emul_parse(const uint8_t* data, size_t size, int* out /* [16] */)
 // Full emulated decode of scan `scan_idx` into DU-major coded-order coefficients (DC absolute).
 // coef must hold total_mcus * dus_per_mcu * 64 int16.  destuffed_out (optional) receives the
 // destuffed buffer in natural byte order (num_subs * kSubBytes bytes).
-// stats: [0..2] repairs per pass, [3] num_subs, [4] records still inconsistent before fixup,
-//        [5] number of speculate guesses that were wrong.
+// stats: [0] chunk boundaries healed inside huff_sync, [1] most fix-point rounds of any warp,
+//        [2] records rewritten by huff_link's fallback, [3] num_subs, [4] link rounds;
+//        in: stats[7] == 12345 corrupts records before huff_link (fallback test hook).
 int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* coef,
                      size_t coef_count, uint8_t* destuffed_out, size_t destuffed_cap, int* stats)
 {
@@ -60,36 +61,42 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     HuffSlow slow[kMaxTables];
     for (int t = 0; t < g.num_tables; ++t) g.table_off[t] = (uint16_t)build_lut(sp.tables[t], pool, slow[t]);
     g.lut_pool_u16 = (uint32_t)pool.size();
-    uint32_t offs[kMaxDuPerMcu], tbls[kMaxDuPerMcu];
-    for (int s = 0; s < kMaxDuPerMcu; ++s) {
-        const int ss = s < g.dus_per_mcu ? s : 0;
-        offs[s] = (uint32_t)g.table_off[g.slot_dc[ss]] | ((uint32_t)g.table_off[g.slot_ac[ss]] << 16);
-        tbls[s] = (uint32_t)g.slot_dc[ss] | ((uint32_t)g.slot_ac[ss] << 8);
-    }
-    const HostMem T{pool.data(), offs, tbls, slow, kNat};
-    const SlotTables K = make_slot_tables(T, (uint32_t)g.dus_per_mcu);
+    SlotPair pairs[kMaxDuPerMcu];
+    uint32_t tbls[kMaxDuPerMcu];
+    make_slot_pairs(g, pairs, tbls);
 
-    // destuff: the contract of destuff_count + destuff_apply
+    // destuff: the contract of destuff_kernel, tile by tile from the host tile directory
     const uint32_t N = g.num_subs;
-    std::vector<uint8_t> dst((size_t)N * kSubBytes + 64, 0);
+    std::vector<uint8_t> dst((size_t)N * kSubBytes + 64, 0xa5); // poison: padding must be written
     {
         const uint8_t* src = data + sp.begin;
-        uint32_t kept = 0, seg = 0, prev = 0;
-        for (uint32_t i = 0; i < g.scan_bytes; ++i) {
-            const uint32_t b = src[i];
-            const bool after_ff = prev == 0xff;
-            const bool keep = after_ff ? b == 0 : b != 0xff;
-            const bool rst = after_ff && b >= 0xd0 && b <= 0xd7;
-            if (keep) {
-                if ((int)seg >= g.num_segments) return -3;
-                const uint32_t adj = sp.segs[seg].sub_off * (uint32_t)kSubBytes - sp.segs[seg].kept_before;
-                const uint32_t d = kept + adj;
-                if (d >= dst.size()) return -4;
-                dst[d ^ 3u] = after_ff ? 0xff : (uint8_t)b;
-                ++kept;
+        const uint32_t tiles = (g.scan_bytes + kDestuffTile - 1) / kDestuffTile;
+        if (sp.tiles.size() != tiles) return -6;
+        for (uint32_t t = 0; t < tiles; ++t) {
+            uint32_t kept = sp.tiles[t].kept_before, seg = sp.tiles[t].segs_before;
+            const uint32_t i0 = t * kDestuffTile, i1 = umin(i0 + kDestuffTile, g.scan_bytes);
+            uint32_t prev = i0 ? src[i0 - 1] : 0u;
+            for (uint32_t i = i0; i < i1; ++i) {
+                const uint32_t b = src[i];
+                const bool after_ff = prev == 0xff;
+                const bool keep = after_ff ? b == 0 : b != 0xff;
+                const bool rst = after_ff && b >= 0xd0 && b <= 0xd7;
+                if (keep) {
+                    if ((int)seg >= g.num_segments) return -3;
+                    const SegDesc& sd = sp.segs[seg];
+                    const uint32_t r = kept - sd.kept_before;
+                    const uint32_t d = r + sd.sub_off * (uint32_t)kSubBytes;
+                    if (d >= dst.size()) return -4;
+                    dst[d ^ 3u] = after_ff ? 0xff : (uint8_t)b;
+                    if (r + 1 == sd.nbytes) {
+                        const uint32_t pad_end = (d + kSubBytes) / kSubBytes * kSubBytes;
+                        for (uint32_t z = d + 1; z < pad_end; ++z) dst[z ^ 3u] = 0;
+                    }
+                    ++kept;
+                }
+                if (rst) ++seg;
+                prev = b;
             }
-            if (rst) ++seg;
-            prev = b;
         }
     }
     if (destuffed_out) {
@@ -98,51 +105,125 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         for (size_t d = 0; d < n; ++d) destuffed_out[d] = dst[d ^ 3u];
     }
     const uint32_t* words = reinterpret_cast<const uint32_t*>(dst.data());
+    auto mem_of = [&](const SegDesc& seg) {
+        return HostMem{pool.data(), pairs, tbls, slow, kNat, words + (size_t)seg.sub_off * kSubWords};
+    };
 
+    // huff_sync: one "warp" per chunk, lanes emulated by arrays; chunks in launch order so the
+    // left mailbox is always there (one valid schedule of the kernel)
     std::vector<unsigned long long> entries(N);
     std::vector<uint32_t> seg_idx(N), qpos(N + 1);
-    for (uint32_t j = 0; j < N; ++j) entries[j] = speculate_one(T, K, sp.segs.data(), g.num_segments, words, j, &seg_idx[j]);
-    // count wrong guesses
-    int wrong = 0;
-    for (uint32_t j = 0; j < N; ++j) {
-        const SegDesc& sg = sp.segs[seg_idx[j]];
-        if (j != sg.sub_off && (uint16_t)(entries[j - 1] >> 16) != (uint16_t)entries[j]) ++wrong;
-    }
-    stats[5] = wrong;
-    uint32_t last = 1;
-    for (int pass = 0; pass < 3; ++pass) {
-        stats[pass] = 0;
-        if (pass > 0 && last == 0) continue;
-        // emulate concurrency pessimistically: every thread decides from a snapshot
-        std::vector<unsigned long long> snap(entries);
-        uint32_t total = 0;
-        for (uint32_t j = 0; j < N; ++j) {
-            const SegDesc& sg = sp.segs[seg_idx[j]];
-            if (j == sg.sub_off) continue;
-            if ((uint16_t)(snap[j - 1] >> 16) == (uint16_t)snap[j]) continue;
-            total += repair_one(T, K, sp.segs.data(), seg_idx.data(), words, entries.data(), j);
+    const uint32_t chunks = (N + kChunkSubs - 1) / kChunkSubs;
+    std::vector<uint32_t> mailbox(chunks, 0);
+    int relinked = 0, rounds_max = 0, rounds_sum = 0;
+    for (uint32_t chunk = 0; chunk < chunks; ++chunk) {
+        const uint32_t chunk_first = chunk * kChunkSubs;
+        bool active[32], head[32];
+        uint32_t k[32], i[32], seg_bits[32];
+        uint16_t entry[32];
+        unsigned long long rec[32];
+        for (int l = 0; l < 32; ++l) {
+            const long long sub = (long long)chunk_first - kOverlapSubs + l;
+            active[l] = sub >= 0 && sub < (long long)N;
+            head[l] = false;
+            entry[l] = 0;
+            rec[l] = 0;
+            if (!active[l]) continue;
+            k[l] = find_segment(sp.segs.data(), g.num_segments, (uint32_t)sub);
+            const SegDesc& seg = sp.segs[k[l]];
+            i[l] = (uint32_t)sub - seg.sub_off;
+            head[l] = i[l] == 0;
+            seg_bits[l] = seg.nbytes * 8u;
+            rec[l] = decode_sub(mem_of(seg), seg_bits[l], i[l], 0);
         }
-        stats[pass] = (int)total;
-        last = total;
+        auto iterate = [&](int frozen) {
+            int rounds = 0;
+            for (;;) {
+                uint16_t want[32];
+                bool any = false;
+                for (int l = 0; l < 32; ++l) {
+                    const uint16_t px = l ? entry_x(rec[l - 1]) : 0;
+                    want[l] = (l <= frozen || head[l] || !active[l]) ? entry[l] : px;
+                    any |= want[l] != entry[l];
+                }
+                if (!any) break;
+                ++rounds;
+                for (int l = 0; l < 32; ++l)
+                    if (want[l] != entry[l]) {
+                        entry[l] = want[l];
+                        rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l]);
+                    }
+            }
+            if (rounds > rounds_max) rounds_max = rounds;
+            rounds_sum += rounds;
+        };
+        iterate(0);
+        const uint32_t last_sub = umin(chunk_first + kChunkSubs, N) - 1;
+        const int last_lane = (int)(last_sub - chunk_first) + kOverlapSubs;
+        mailbox[chunk] = 0x80000000u | entry_x(rec[last_lane]);
+        if (chunk > 0 && !head[kOverlapSubs]) {
+            const uint32_t left = mailbox[chunk - 1];
+            if ((uint16_t)(left & 0xffffu) != entry[kOverlapSubs]) {
+                const int l = kOverlapSubs;
+                entry[l] = (uint16_t)(left & 0xffffu);
+                rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l]);
+                ++relinked;
+                iterate(kOverlapSubs);
+                mailbox[chunk] = 0x80000000u | entry_x(rec[last_lane]);
+            }
+        }
+        for (int l = kOverlapSubs; l < 32; ++l)
+            if (active[l]) {
+                const uint32_t sub = chunk_first - kOverlapSubs + l;
+                entries[sub] = pack_entry((uint16_t)(entry[l] | (head[l] ? kStateHead : 0)),
+                                          entry_x(rec[l]), entry_n(rec[l]));
+                seg_idx[sub] = k[l];
+            }
     }
-    int bad = 0;
-    for (uint32_t j = 0; j < N; ++j) {
-        const SegDesc& sg = sp.segs[seg_idx[j]];
-        if (j != sg.sub_off && (uint16_t)(entries[j - 1] >> 16) != (uint16_t)entries[j]) ++bad;
-    }
+    stats[0] = relinked;
+    stats[1] = rounds_max;
+    stats[5] = rounds_sum;
+    stats[6] = (int)chunks;
     stats[3] = (int)N;
-    stats[4] = bad;
-    if (last != 0)
-        for (int k = 0; k < g.num_segments; ++k) fixup_segment(T, K, sp.segs[k], words, entries.data());
+
+    // huff_link: verify chunk boundaries, sequential fallback, segmented exclusive scan
+    if (stats[7] == 12345) // test hook: corrupt some records to exercise the fallback
+        for (uint32_t j = 3; j < N; j += 7)
+            if (!(entry_g(entries[j]) & kStateHead)) entries[j] = pack_entry(entry_g(entries[j]) ^ 0x21, entry_x(entries[j]) ^ 0x40, 5);
+    uint32_t stride = stats[7] == 12345 ? 1 : kChunkSubs;
+    int slow_fix = 0, link_rounds = 0;
+    for (;;) {
+        std::vector<unsigned long long> snap(entries); // every thread decides from a snapshot
+        uint32_t bad = 0;
+        for (uint32_t j = stride; j < N; j += stride)
+            if (!boundary_ok(snap[j - 1], snap[j])) {
+                ++bad;
+                const SegDesc& seg = sp.segs[seg_idx[j]];
+                slow_fix += (int)relink_from(mem_of(seg), seg, entries.data(), j);
+            }
+        if (!bad) break;
+        stride = 1;
+        ++link_rounds;
+    }
+    stats[2] = slow_fix;
+    stats[4] = link_rounds;
+    for (uint32_t j = 1; j < N; ++j)
+        if (!boundary_ok(entries[j - 1], entries[j])) return -7; // inconsistent chain
     uint32_t acc = 0;
     for (uint32_t j = 0; j < N; ++j) {
+        if (entry_g(entries[j]) & kStateHead) acc = 0;
         qpos[j] = acc;
-        acc += (uint32_t)(entries[j] >> 32);
+        acc += entry_n(entries[j]);
     }
-    qpos[N] = acc;
+
+    // huff_write
     memset(coef, 0, need * sizeof(int16_t));
-    for (uint32_t j = 0; j < N; ++j)
-        write_one(T, K, g, sp.segs.data(), seg_idx.data(), words, entries.data(), qpos.data(), coef, j);
+    std::vector<int16_t> dc((size_t)g.total_mcus * g.dus_per_mcu, 0);
+    for (uint32_t j = 0; j < N; ++j) {
+        const SegDesc& seg = sp.segs[seg_idx[j]];
+        write_sub(mem_of(seg), g, seg, seg_idx[j], j - seg.sub_off,
+                  (uint16_t)(entry_g(entries[j]) & kStateMask), qpos[j], coef, dc.data());
+    }
     // DC: the contract of dc_tile_sums + dc_apply
     for (int a = 0; a < g.num_comp; ++a) {
         int pred = 0;
@@ -150,9 +231,9 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
             if (m % g.restart_interval == 0) pred = 0;
             for (int s = 0; s < g.dus_per_mcu; ++s)
                 if (g.slot_comp[s] == a) {
-                    int16_t* du = coef + ((size_t)m * g.dus_per_mcu + s) * 64;
-                    pred += du[0];
-                    du[0] = (int16_t)pred;
+                    const size_t du = (size_t)m * g.dus_per_mcu + s;
+                    pred += dc[du];
+                    coef[du * 64] = (int16_t)pred;
                 }
         }
     }
