@@ -47,16 +47,23 @@ constexpr int kDestuffBytesPerThread = 16;
 constexpr int kDestuffTile = kDestuffThreads * kDestuffBytesPerThread; // stuffed bytes per CTA
 
 // ---- Huffman lookup tables -------------------------------------------------------------------
-// One table = header (8 u16) + primary LUT (2^kLutBits u16, indexed by the next kLutBits bits)
-// + secondary LUT (lut2_size u16, indexed by peek16 - base16) for codes longer than kLutBits
-// + slow-path arrays for pathological tables whose long-code region exceeds kLut2Max.
-// Entry: bits 0-4 total bits to skip (code length + magnitude bits, >= 1),
-//        bits 5-8 magnitude size, bits 9-15 slot advance (run + 1; 64 = end of block).
-constexpr int kLutBits = 10;
+// One table = header (8 words) + primary LUT (2^kLutBits words, indexed by the next kLutBits
+// bits) + secondary LUT (lut2_size words, indexed by peek16 - base16) for codes longer than
+// kLutBits + slow-path arrays for pathological tables whose long-code region exceeds kLut2Max.
+// Entry (32 bit): bits 31-27 total bits to skip (code length + magnitude bits, >= 1),
+//                 bits 11-8 magnitude size, bits 6-0 slot advance (run + 1; 64 = end of block).
+// The skip field sits at the top so that "position += skip" is a single shift-add and the
+// advance at the bottom so that it is a single mask; an entry whose skip field is zero is a
+// marker (kEntryLong / kEntrySlow).
+#ifndef JB2_LUT_BITS
+#define JB2_LUT_BITS 12
+#endif
+constexpr int kLutBits = JB2_LUT_BITS;
 constexpr int kLut1Size = 1 << kLutBits;
-constexpr int kLut2Max = 4096;
-constexpr uint16_t kEntryLong = 0xffffu; // primary miss: go to the secondary LUT
-constexpr uint16_t kEntrySlow = 0xfffeu; // secondary miss: canonical length search
+constexpr int kLut2Max = 2048;
+constexpr uint32_t kEntryLong = 1u; // primary miss: go to the secondary LUT
+constexpr uint32_t kEntrySlow = 2u; // secondary miss: canonical length search
+constexpr uint32_t kEntryMarkerLimit = 1u << 27; // e < limit  <=>  marker
 
 struct HuffSlow {       // canonical decode data (T.81 F.2.2.3), used by the slow path only
     uint32_t limit[17]; // limit[l] = (maxcode[l] + 1) << (16 - l), l = 1..16; 0 if no codes
@@ -66,7 +73,7 @@ struct HuffSlow {       // canonical decode data (T.81 F.2.2.3), used by the slo
     uint8_t pad[3];
 };
 
-JB2_HD uint16_t make_entry(unsigned symbol, int code_len, bool is_dc)
+JB2_HD uint32_t make_entry(unsigned symbol, int code_len, bool is_dc)
 {
     unsigned size, adv;
     if (is_dc) {
@@ -78,9 +85,12 @@ JB2_HD uint16_t make_entry(unsigned symbol, int code_len, bool is_dc)
         // src/decode_huffman.cu:236-242: size 0 is ZRL when run == 15, otherwise end of block
         adv = size ? run + 1 : (run == 15 ? 16u : 64u);
     }
-    unsigned skip = (unsigned)code_len + size; // <= 16 + 15
-    return (uint16_t)(skip | (size << 5) | (adv << 9));
+    const unsigned skip = (unsigned)code_len + size; // <= 16 + 15
+    return (skip << 27) | (size << 8) | adv;
 }
+JB2_HD uint32_t entry_skip(uint32_t e) { return e >> 27; }
+JB2_HD uint32_t entry_adv(uint32_t e) { return e & 127u; }
+JB2_HD uint32_t entry_size(uint32_t e) { return (e >> 8) & 15u; }
 
 // ---- device-visible descriptors ---------------------------------------------------------------
 
@@ -131,8 +141,8 @@ struct ScanGeom { // by-value kernel parameter describing one scan
     int blocks_x[kMaxComp], blocks_y[kMaxComp]; // coded plane size in DUs (MCU padded)
     int size_x[kMaxComp], size_y[kMaxComp];     // output plane size in samples
     uint32_t du_prefix[kMaxComp + 1];           // prefix sum of blocks_x*blocks_y
-    uint16_t table_off[kMaxTables];             // u16 offset of each table in the LUT pool
-    uint32_t lut_pool_u16;                      // total u16 in the pool
+    uint32_t table_off[kMaxTables];             // word offset of each table in the LUT pool
+    uint32_t lut_pool_words;                    // total 32-bit words in the pool
 };
 
 struct OutPlanes {
@@ -151,7 +161,9 @@ struct Control {
     uint32_t relinked;    // warp-boundary mismatches healed inside huff_sync
     uint32_t slow_repairs; // records rewritten by huff_link's sequential fallback
     uint32_t link_rounds;
-    uint32_t pad[13];
+    uint32_t link_verify_ns; // device-side phase times of huff_link (diagnostics)
+    uint32_t link_scan_ns;
+    uint32_t pad[11];
 };
 
 // zig-zag -> natural order (T.81 Figure A.6; same table as src/defs.hpp:94-102)

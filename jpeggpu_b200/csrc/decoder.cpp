@@ -52,7 +52,13 @@ struct jpeggpu_decoder {
     uint8_t* staging = nullptr;
     size_t staging_cap = 0;
     bool staging_pinned = false;
-    std::vector<uint16_t> lut_scratch;
+    struct LutCache {
+        std::vector<uint8_t> key;
+        std::vector<uint32_t> pool;
+        HuffSlow slow[kMaxTables];
+        uint32_t table_off[kMaxTables];
+    } lut_cache[kMaxScans];
+    std::vector<uint8_t> lut_key;
     StageTimer timer;
 
     ~jpeggpu_decoder()
@@ -101,28 +107,35 @@ struct jpeggpu_decoder {
 jpeggpu_status jpeggpu_decoder::plan_scratch()
 {
     size_t off = 0;
-    // pass 1: sizes of the upload block
-    std::vector<uint16_t>& pool = lut_scratch;
-    HuffSlow slow[kMaxScans][kMaxTables];
-    std::vector<size_t> pool_begin(plan.num_scans + 1, 0);
-    pool.clear();
+    // pass 1: decode LUTs.  Expanding a DHT into the LUT pool costs tens of microseconds, and
+    // consecutive images nearly always carry the same tables (same encoder): the pool of every
+    // scan slot is cached and keyed by the raw table specifications.
     for (int s = 0; s < plan.num_scans; ++s) {
         ScanPlan& sp = plan.scans[s];
-        pool_begin[s] = pool.size();
+        LutCache& lc = lut_cache[s];
+        lut_key.clear();
         for (int t = 0; t < sp.geom.num_tables; ++t) {
-            const uint32_t at = build_lut(sp.tables[t], pool, slow[s][t]);
-            sp.geom.table_off[t] = (uint16_t)(at - pool_begin[s]);
+            const HuffSpec& h = sp.tables[t];
+            lut_key.push_back(h.is_dc ? 1 : 0);
+            lut_key.insert(lut_key.end(), h.counts, h.counts + 16);
+            lut_key.insert(lut_key.end(), h.vals, h.vals + 256);
         }
-        while (pool.size() & 7) pool.push_back(0); // kernels stage the pool with 16-byte loads
-        sp.geom.lut_pool_u16 = (uint32_t)(pool.size() - pool_begin[s]);
-        if (sp.geom.lut_pool_u16 > 47 * 1024) return JPEGGPU_NOT_SUPPORTED; // > 94 KiB of LUTs
+        if (lc.key != lut_key) {
+            lc.pool.clear();
+            for (int t = 0; t < sp.geom.num_tables; ++t)
+                lc.table_off[t] = build_lut(sp.tables[t], lc.pool, lc.slow[t]);
+            while (lc.pool.size() & 3) lc.pool.push_back(0); // staged with 16-byte loads
+            lc.key = lut_key;
+        }
+        for (int t = 0; t < sp.geom.num_tables; ++t) sp.geom.table_off[t] = lc.table_off[t];
+        sp.geom.lut_pool_words = (uint32_t)lc.pool.size();
+        if (sp.geom.lut_pool_words > 40 * 1024) return JPEGGPU_NOT_SUPPORTED; // > 160 KiB of LUTs
     }
-    pool_begin[plan.num_scans] = pool.size();
     for (int s = 0; s < plan.num_scans; ++s) {
         ScanLayout& L = layout[s];
         const ScanGeom& g = plan.scans[s].geom;
         L.off_lut = off;
-        off += align256((size_t)g.lut_pool_u16 * 2);
+        off += align256((size_t)g.lut_pool_words * 4);
         L.off_slow = off;
         off += align256(sizeof(HuffSlow) * kMaxTables);
         L.off_segs = off;
@@ -172,12 +185,12 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
 
     jpeggpu_status st = reserve_staging(upload_bytes);
     if (st != JPEGGPU_SUCCESS) return st;
-    memset(staging, 0, upload_bytes);
     for (int s = 0; s < plan.num_scans; ++s) {
         const ScanLayout& L = layout[s];
         const ScanPlan& sp = plan.scans[s];
-        memcpy(staging + L.off_lut, pool.data() + pool_begin[s], (size_t)sp.geom.lut_pool_u16 * 2);
-        memcpy(staging + L.off_slow, slow[s], sizeof(HuffSlow) * (size_t)sp.geom.num_tables);
+        const LutCache& lc = lut_cache[s];
+        memcpy(staging + L.off_lut, lc.pool.data(), (size_t)sp.geom.lut_pool_words * 4);
+        memcpy(staging + L.off_slow, lc.slow, sizeof(HuffSlow) * (size_t)sp.geom.num_tables);
         if (!sp.segs.empty())
             memcpy(staging + L.off_segs, sp.segs.data(), sizeof(SegDesc) * sp.segs.size());
         if (!sp.tiles.empty())
@@ -193,7 +206,7 @@ ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
     ScanBufs b;
     b.scan_bytes = base + L.off_bytes;
     b.segs = reinterpret_cast<const SegDesc*>(base + L.off_segs);
-    b.lut_pool = reinterpret_cast<const uint16_t*>(base + L.off_lut);
+    b.lut_pool = reinterpret_cast<const uint32_t*>(base + L.off_lut);
     b.slow = reinterpret_cast<const HuffSlow*>(base + L.off_slow);
     b.tiles = reinterpret_cast<const TileDesc*>(base + L.off_tiles);
     b.ctrl = reinterpret_cast<Control*>(base + L.off_ctrl);

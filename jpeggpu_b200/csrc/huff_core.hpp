@@ -13,17 +13,20 @@
 //    window slides by predicated moves and the following word is fetched unconditionally every
 //    iteration from shared memory, so the symbol loop has no data-dependent branch besides the
 //    rare long-code path and no load latency on its dependent chain except the LUT probe;
-//  * the table pair of the current data unit and of the next one come from one 8-byte
-//    shared-memory record per MCU slot, fetched in the shadow of the LUT probe.
+//  * the tables of the current data unit and of the next one come from one 16-byte
+//    shared-memory record per MCU slot, fetched in the shadow of the LUT probe; tables, slots
+//    and words are addressed through policy-defined handles (shared-memory byte addresses on
+//    the device), so no index-to-address arithmetic sits in the loop.
 //
 // Memory access goes through a policy type `Mem` (shared memory on the device, plain arrays on
 // the host):
-//   lut(i)        -> uint16_t LUT pool entry
-//   pair(c)       -> SlotPair of MCU slot c
-//   slot_tbls(c)  -> dc table slot | ac table slot << 8   (slow path only)
-//   slow(slot)    -> HuffSlow
-//   natural(i)    -> zig-zag to raster index
-//   word(i)       -> big-endian word i of the scan window the policy was built for
+//   lut(tbl, i)    -> entry i of the table with handle tbl
+//   slot_handle(c) -> handle of MCU slot c;  rec(h) -> SlotRec of that slot
+//   slot_tbls(c)   -> dc table slot | ac table slot << 8   (slow path only)
+//   slow(slot)     -> HuffSlow
+//   natural(i)     -> zig-zag to raster index
+//   word_handle(i) -> handle of big-endian word i of the scan window the policy was built for;
+//   word(h)        -> that word; consecutive words are kWordStep handles apart
 #ifndef JB2_HUFF_CORE_HPP_
 #define JB2_HUFF_CORE_HPP_
 
@@ -31,14 +34,18 @@
 
 namespace jb2 {
 
-// Per MCU slot c: the tables of its data unit and what follows it.
-struct SlotPair {
-    uint32_t x; // ac table offset of slot c | dc table offset of slot next(c) << 16
-    uint32_t y; // next(c) | dc table offset of slot c << 16
+// Per MCU slot c: the tables of its data unit and what follows it.  The fields are HANDLES whose
+// meaning belongs to the memory policy (host: word offsets / indices; device: shared-memory byte
+// addresses), so that the symbol loop never converts an index into an address.
+struct SlotRec {
+    uint32_t x; // ac table of slot c
+    uint32_t y; // dc table of slot next(c)
+    uint32_t z; // handle of slot next(c)
+    uint32_t w; // dc table of slot c (low 24 bits) | c << 24
 };
 
 // canonical search for codes the two LUT levels do not cover (pathological tables only)
-JB2_HD uint16_t slow_entry(const HuffSlow& t, uint32_t peek16)
+JB2_HD uint32_t slow_entry(const HuffSlow& t, uint32_t peek16)
 {
     int l = kLutBits + 1;
     for (; l < 16; ++l)
@@ -50,14 +57,14 @@ JB2_HD uint16_t slow_entry(const HuffSlow& t, uint32_t peek16)
 
 // second-level lookup for codes longer than kLutBits
 template <class Mem>
-JB2_HD uint16_t lookup_long(const Mem& M, uint32_t tbl_off, uint32_t tbl_slot, uint32_t peek16,
-                            uint16_t e)
+JB2_HD uint32_t lookup_long(const Mem& M, uint32_t tbl, uint32_t tbl_slot, uint32_t peek16,
+                            uint32_t e)
 {
     if (e == kEntryLong) {
-        const uint32_t base16 = M.lut(tbl_off - 8);
-        const uint32_t n2 = M.lut(tbl_off - 7);
+        const uint32_t base16 = M.lut(tbl, (uint32_t)-8);
+        const uint32_t n2 = M.lut(tbl, (uint32_t)-7);
         const uint32_t i2 = peek16 - base16;
-        e = i2 < n2 ? M.lut(tbl_off + kLut1Size + i2) : kEntrySlow;
+        e = i2 < n2 ? M.lut(tbl, (uint32_t)kLut1Size + i2) : kEntrySlow;
     }
     if (e == kEntrySlow) e = slow_entry(M.slow(tbl_slot), peek16);
     return e;
@@ -79,6 +86,45 @@ JB2_HD uint32_t funnel_left_wrap(uint32_t hi, uint32_t lo, uint32_t shift)
 #endif
 }
 
+// Window slide: when the bit position crosses a word boundary the window moves one word on.
+JB2_HD void slide_window(uint32_t& w0, uint32_t& w1, uint32_t& wn, uint32_t nx, uint32_t pp,
+                         uint32_t pn, uint32_t step)
+{
+#if defined(__CUDA_ARCH__)
+    // one LOP3 with predicate output + three predicated moves (the compiler's own lowering of
+    // the C below took eleven instructions)
+    asm("{\n\t.reg .pred s;\n\t.reg .b32 t;\n\t"
+        "xor.b32 t, %3, %4;\n\tand.b32 t, t, 32;\n\tsetp.ne.u32 s, t, 0;\n\t"
+        "@s mov.b32 %0, %1;\n\t@s mov.b32 %1, %5;\n\t@s add.u32 %2, %2, %6;\n\t}"
+        : "+r"(w0), "+r"(w1), "+r"(wn)
+        : "r"(pn), "r"(pp), "r"(nx), "r"(step));
+#else
+    const bool slide = ((pn ^ pp) & 32u) != 0;
+    w0 = slide ? w1 : w0;
+    w1 = slide ? nx : w1;
+    wn += slide ? step : 0u;
+#endif
+}
+
+// End of a data unit (EOB / slot 63; advance <= 64, so at most one boundary is crossed): the
+// slot counter snaps to the boundary, the MCU slot and the table move on.
+JB2_HD void advance_unit(uint32_t& qq, uint32_t qn, uint32_t& ch, uint32_t& tbl, const SlotRec& r)
+{
+#if defined(__CUDA_ARCH__)
+    asm("{\n\t.reg .pred d;\n\t.reg .b32 t;\n\t"
+        "xor.b32 t, %3, %0;\n\tand.b32 t, t, 64;\n\tsetp.ne.u32 d, t, 0;\n\t"
+        "mov.b32 %0, %3;\n\t@d and.b32 %0, %3, 0xffffffc0;\n\t"
+        "@d mov.b32 %1, %6;\n\tselp.b32 %2, %5, %4, d;\n\t}"
+        : "+r"(qq), "+r"(ch), "=r"(tbl)
+        : "r"(qn), "r"(r.x), "r"(r.y), "r"(r.z));
+#else
+    const bool done = ((qn ^ qq) & 64u) != 0;
+    qq = done ? (qn & ~63u) : qn;
+    ch = done ? r.z : ch;
+    tbl = done ? r.y : r.x;
+#endif
+}
+
 // Decode the symbols that start in [p, end).  State: p bit position inside the policy's word
 // window, q linear slot counter (q & 63 = zig-zag index), c MCU slot of the current data unit.
 // WRITE: store the non-zero AC coefficients at out[(q >> 6) * 64 + natural[q & 63]] and every DC
@@ -87,86 +133,97 @@ template <bool WRITE, class Mem>
 JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, uint32_t& c,
                         int16_t* out, int16_t* dc_out, uint32_t q_limit)
 {
-    if (p >= end) return;
-    uint32_t pp = p, qq = q, cc = c;
-    uint32_t wnext = (pp >> 5) + 2u;
-    uint32_t w0 = M.word(wnext - 2u), w1 = M.word(wnext - 1u);
-    SlotPair pr = M.pair(cc);
-    uint32_t tbl = (qq & 63u) == 0 ? (pr.y >> 16) : (pr.x & 0xffffu);
+    if (p >= end || (WRITE && q >= q_limit)) return;
+    uint32_t pp = p, qq = q;
+    uint32_t ch = M.slot_handle(c);
+    SlotRec r = M.rec(ch);
+    uint32_t tbl = (qq & 63u) == 0 ? (r.w & 0xffffffu) : r.x;
+    uint32_t wn = M.word_handle((pp >> 5) + 2u);
+    uint32_t w0 = M.word(wn - 2u * Mem::kWordStep), w1 = M.word(wn - Mem::kWordStep);
+    uint32_t peek = funnel_left_wrap(w0, w1, pp);
+    uint32_t e = M.lut(tbl, peek >> (32 - kLutBits));
 
-    while (pp < end) {
-        if (WRITE && qq >= q_limit) break;
-        const uint32_t nx = M.word(wnext); // not needed before the window slides
-        pr = M.pair(cc);
-        const uint32_t peek = funnel_left_wrap(w0, w1, pp);
-        uint32_t e = M.lut(tbl + (peek >> (32 - kLutBits)));
-        if (e >= kEntrySlow) {
-            const uint32_t tbls = M.slot_tbls(cc);
-            e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16,
-                            (uint16_t)e);
+    // The loop is rotated: each iteration consumes the entry `e` of the symbol at pp and then
+    // probes the LUT for the symbol that follows, so that the only branch of the hot loop is its
+    // back edge (taken while the next entry is an ordinary one) and the probe is issued before
+    // the bookkeeping of the current symbol.
+    for (;;) {
+        if (e < kEntryMarkerLimit) { // rare: code longer than kLutBits
+            M.note_long_code();
+            const uint32_t tbls = M.slot_tbls(r.w >> 24);
+            e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16, e);
         }
-        const uint32_t skip = e & 31u;
-        const uint32_t adv = e >> 9;
-        const uint32_t block_end = (qq | 63u) + 1u;
-        if (WRITE) {
-            const uint32_t size = (e >> 5) & 15u;
-            const uint32_t pos = qq + adv - 1u;
-            const bool is_dc = (qq & 63u) == 0;
-            if ((size != 0 || is_dc) && pos < block_end) {
-                int v = 0;
-                if (size != 0) {
-                    const uint32_t bits = (peek << (skip - size)) >> (32 - size);
-                    v = extend_value(bits, size);
+        bool more;
+        do {
+            const uint32_t nx = M.word(wn); // not needed before the window slides
+            const uint32_t skip = entry_skip(e);
+            const uint32_t qn = qq + entry_adv(e);
+            if (WRITE) {
+                const uint32_t size = entry_size(e);
+                const uint32_t pos = qn - 1u;
+                const bool is_dc = (qq & 63u) == 0;
+                if ((size != 0 || is_dc) && ((pos ^ qq) & 64u) == 0) {
+                    int v = 0;
+                    if (size != 0) {
+                        const uint32_t bits = (peek << (skip - size)) >> (32 - size);
+                        v = extend_value(bits, size);
+                    }
+                    if (is_dc) dc_out[pos >> 6] = (int16_t)v;
+                    else out[(size_t)(pos & ~63u) + M.natural(pos & 63u)] = (int16_t)v;
                 }
-                if (is_dc) dc_out[pos >> 6] = (int16_t)v;
-                else out[(size_t)(pos & ~63u) + M.natural(pos & 63u)] = (int16_t)v;
             }
-        }
-        const uint32_t pn = pp + skip;
-        const bool slide = ((pn ^ pp) & 32u) != 0;
-        w0 = slide ? w1 : w0;
-        w1 = slide ? nx : w1;
-        wnext += slide ? 1u : 0u;
-        pp = pn;
-        // slot bookkeeping: a data unit ends on EOB / slot 63 (or overshoot on a garbage stream)
-        const uint32_t qn = qq + adv;
-        const bool done = qn >= block_end;
-        qq = done ? block_end : qn;
-        cc = done ? (pr.y & 0xffu) : cc;
-        tbl = done ? (pr.x >> 16) : (pr.x & 0xffffu);
+            const uint32_t pn = pp + skip;
+            slide_window(w0, w1, wn, nx, pp, pn, Mem::kWordStep);
+            pp = pn;
+            advance_unit(qq, qn, ch, tbl, r);
+            peek = funnel_left_wrap(w0, w1, pp);
+            e = M.lut(tbl, peek >> (32 - kLutBits)); // entry of the next symbol
+            r = M.rec(ch);
+            more = pp < end && (!WRITE || qq < q_limit);
+        } while (more && e >= kEntryMarkerLimit);
+        if (!more) break;
     }
     p = pp;
     q = qq;
-    c = cc;
+    c = r.w >> 24;
 }
 
-// Fills the per-slot records from the scan geometry (host and device).
-JB2_HD void make_slot_pairs(const ScanGeom& g, SlotPair* pairs, uint32_t* tbls)
+// Fills the per-slot records with host-style handles (word offsets and slot indices).
+JB2_HD void make_slot_recs(const ScanGeom& g, SlotRec* recs, uint32_t* tbls)
 {
     for (int s = 0; s < kMaxDuPerMcu; ++s) {
         const int cur = s < g.dus_per_mcu ? s : 0;
         const int nxt = cur + 1 == g.dus_per_mcu ? 0 : cur + 1;
-        pairs[s].x = (uint32_t)g.table_off[g.slot_ac[cur]] |
-                     ((uint32_t)g.table_off[g.slot_dc[nxt]] << 16);
-        pairs[s].y = (uint32_t)nxt | ((uint32_t)g.table_off[g.slot_dc[cur]] << 16);
+        recs[s].x = g.table_off[g.slot_ac[cur]];
+        recs[s].y = g.table_off[g.slot_dc[nxt]];
+        recs[s].z = (uint32_t)nxt;
+        recs[s].w = g.table_off[g.slot_dc[cur]] | ((uint32_t)cur << 24);
         tbls[s] = (uint32_t)g.slot_dc[cur] | ((uint32_t)g.slot_ac[cur] << 8);
     }
 }
 
 // Plain-array policy (host emulation; also documents what the device policy must provide).
 struct HostMem {
-    const uint16_t* lut_;
-    const SlotPair* pairs_;
+    const uint32_t* lut_;
+    const SlotRec* recs_;
     const uint32_t* tbls_; // per MCU slot: dc table slot | ac table slot << 8
     const HuffSlow* slow_;
     const uint8_t* natural_;
     const uint32_t* words_; // word 0 = first word of the restart segment
-    JB2_HD uint16_t lut(uint32_t i) const { return lut_[i]; }
-    JB2_HD SlotPair pair(uint32_t c) const { return pairs_[c]; }
+    static constexpr uint32_t kWordStep = 1;
+    JB2_HD uint32_t lut(uint32_t tbl, uint32_t i) const { return lut_[(uint32_t)(tbl + i)]; }
+    JB2_HD uint32_t slot_handle(uint32_t c) const { return c; }
+    JB2_HD SlotRec rec(uint32_t h) const { return recs_[h]; }
     JB2_HD uint32_t slot_tbls(uint32_t c) const { return tbls_[c]; }
     JB2_HD const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     JB2_HD uint32_t natural(uint32_t i) const { return natural_[i]; }
-    JB2_HD uint32_t word(uint32_t i) const { return words_[i]; }
+    JB2_HD uint32_t word_handle(uint32_t i) const { return i; }
+    JB2_HD uint32_t word(uint32_t h) const { return words_[h]; }
+    long* long_codes_ = nullptr; // optional statistics
+    JB2_HD void note_long_code() const
+    {
+        if (long_codes_) ++*long_codes_;
+    }
 };
 
 } // namespace jb2

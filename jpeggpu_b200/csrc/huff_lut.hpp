@@ -1,7 +1,7 @@
 // huff_lut.hpp — host-side expansion of a DHT specification into the two-level decode LUT
 // (layout in common.hpp).  Replaces compute_huffman_table of src/reader.cpp:186-224, whose
 // 8-bit {value, nbits} LUT + maxcode search becomes a 10-bit primary + exact secondary LUT that
-// already folds the magnitude size and the run into one 16-bit entry.
+// already folds the magnitude size and the run into one 32-bit entry.
 #ifndef JB2_HUFF_LUT_HPP_
 #define JB2_HUFF_LUT_HPP_
 
@@ -12,10 +12,10 @@
 
 namespace jb2 {
 
-constexpr int kLutHeader = 8; // u16 words before the primary LUT: [0] base16, [1] lut2 size
+constexpr int kLutHeader = 8; // words before the primary LUT: [0] base16, [1] lut2 size
 
 // Appends one table to `pool`; returns the u16 offset of its primary LUT. Fills `slow`.
-inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint16_t>& pool, HuffSlow& slow)
+inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, HuffSlow& slow)
 {
     const bool is_dc = spec.is_dc;
     // canonical codes (T.81 Annex C)
@@ -58,15 +58,15 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint16_t>& pool, Huf
 
     const size_t header_at = pool.size();
     pool.resize(header_at + kLutHeader + kLut1Size + lut2_size);
-    uint16_t* hdr = pool.data() + header_at;
-    uint16_t* lut1 = hdr + kLutHeader;
-    uint16_t* lut2 = lut1 + kLut1Size;
+    uint32_t* hdr = pool.data() + header_at;
+    uint32_t* lut1 = hdr + kLutHeader;
+    uint32_t* lut2 = lut1 + kLut1Size;
     for (int i = 0; i < kLutHeader; ++i) hdr[i] = 0;
-    hdr[0] = (uint16_t)(base16 & 0xffffu); // 0x10000 wraps to 0 with lut2_size 0: never used
-    hdr[1] = (uint16_t)lut2_size;
+    hdr[0] = base16; // 0x10000 with lut2_size 0: never matches
+    hdr[1] = lut2_size;
     // unused code space: behave like the reference's forced 16-bit termination
     // (src/decode_huffman.cu:177-193) with symbol 0
-    const uint16_t invalid = make_entry(0, 16, is_dc);
+    const uint32_t invalid = make_entry(0, 16, is_dc);
     for (int i = 0; i < kLut1Size; ++i) lut1[i] = invalid;
     for (uint32_t i = 0; i < lut2_size; ++i) lut2[i] = truncated ? kEntrySlow : invalid;
     const uint32_t first_long_prefix = base16 >> (16 - kLutBits);
@@ -74,7 +74,7 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint16_t>& pool, Huf
 
     for (int i = 0; i < nsym; ++i) {
         const int l = len_of[i];
-        const uint16_t e = make_entry(spec.vals[i], l, is_dc);
+        const uint32_t e = make_entry(spec.vals[i], l, is_dc);
         if (l <= kLutBits) {
             const uint32_t first = (uint32_t)code_of[i] << (kLutBits - l);
             const uint32_t n = 1u << (kLutBits - l);

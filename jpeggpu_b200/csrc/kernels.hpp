@@ -8,6 +8,8 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
+
 namespace jb2 {
 
 constexpr int kHuffThreads = 128;
@@ -18,7 +20,7 @@ struct ScanBufs {
     const uint8_t* scan_bytes; // stuffed entropy-coded bytes (uploaded)
     const SegDesc* segs;       // uploaded
     const TileDesc* tiles;     // uploaded: one per kDestuffTile stuffed bytes
-    const uint16_t* lut_pool;  // uploaded
+    const uint32_t* lut_pool;  // uploaded
     const HuffSlow* slow;      // uploaded
     Control* ctrl;             // zeroed by destuff
     uint32_t* chunk_state;     // zeroed by destuff: one mailbox per sync warp
@@ -64,6 +66,29 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
                         cudaStream_t stream, StageTimer* tm);
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
                              cudaStream_t stream, StageTimer* tm);
+
+// True the first time it is called for the current device with this mask: launch wrappers set
+// their kernel attributes once per device.
+inline bool first_use_on_device(std::atomic<unsigned long long>& mask)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (mask.load(std::memory_order_relaxed) & bit) return false;
+    mask.fetch_or(bit);
+    return true;
+}
+
+// Every kernel of the library asks for the same shared-memory carveout: when consecutive
+// kernels prefer different L1/shared splits the SMs are drained and reconfigured between them,
+// which showed up as ~25 us of idle time in front of each Huffman kernel.
+template <class Kernel>
+inline void prefer_max_shared(Kernel* k, int max_dynamic_bytes = 0)
+{
+    cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (max_dynamic_bytes)
+        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dynamic_bytes);
+}
 
 // Kernel launches issued per scan by each stage (for bench.py's gpu_launches claim).
 int count_launches(const ScanGeom& g, bool with_transpose);

@@ -183,6 +183,11 @@ dc_apply(const ScanGeom g, const int16_t* __restrict__ dc, int16_t* __restrict__
 cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.total_mcus == 0) return cudaSuccess;
+    static std::atomic<unsigned long long> configured{0};
+    if (first_use_on_device(configured)) {
+        prefer_max_shared(dc_tile_sums);
+        prefer_max_shared(dc_apply);
+    }
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
     tm->mark(stream, kIdDcSums);
     dc_tile_sums<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.dc_agg);

@@ -44,13 +44,55 @@ constexpr int kSyncWinWords = kSyncWinSubs * kSubWords + kWinMargin;
 constexpr int kWriteWinWords = kHuffThreads * kSubWords + kWinMargin;
 static_assert(kSyncWinWords % 4 == 0 && kWriteWinWords % 4 == 0, "window must be uint4 sized");
 
-struct SharedTables {
-    SlotPair pairs[kMaxDuPerMcu];
+struct __align__(16) SharedTables {
+    SlotRec recs[kMaxDuPerMcu]; // device handles: shared-memory byte addresses
     uint32_t tbls[kMaxDuPerMcu];
     uint8_t natural[64];
 };
 
 extern __shared__ __align__(16) uint4 s_dyn[]; // [window words | LUT pool]
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+// volatile: keeps the load where it is written (the compiler otherwise sinks the window prefetch
+// under the slide predicate, which exposes its latency)
+__device__ __forceinline__ uint32_t lds32_pinned(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ SlotRec lds_rec(uint32_t addr)
+{
+    SlotRec r;
+    asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+        : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+        : "r"(addr));
+    return r;
+}
+
+// Converts the host-style slot records into shared-memory addresses (thread 0, before the
+// barrier in stage()).  lut_addr = shared address of the LUT pool.
+__device__ __forceinline__ void make_device_recs(const ScanGeom& g, SharedTables& st, uint32_t lut_addr)
+{
+    make_slot_recs(g, st.recs, st.tbls);
+    const uint32_t recs_addr = smem_addr(st.recs);
+    for (int s = 0; s < kMaxDuPerMcu; ++s) {
+        SlotRec& r = st.recs[s];
+        r.x = lut_addr + r.x * 4u;
+        r.y = lut_addr + r.y * 4u;
+        r.z = recs_addr + r.z * (uint32_t)sizeof(SlotRec);
+        r.w = (lut_addr + (r.w & 0xffffffu) * 4u) | (r.w & 0xff000000u);
+    }
+}
 
 // Stage the LUT pool, the slot records and words [first_word, first_word + win_words) of the
 // destuffed scan (zero outside [0, total_words)).
@@ -67,54 +109,57 @@ __device__ __forceinline__ void stage(const ScanGeom& g, const ScanBufs& b, Shar
         if (w >= 0 && w + 4 <= total_words) v = __ldg(src + (w >> 2));
         reinterpret_cast<uint4*>(win)[i] = v;
     }
-    const uint32_t lut_vec = (g.lut_pool_u16 + 7) / 8; // pool is padded to 16 B by the planner
+    const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
     const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
     uint4* ldst = s_dyn + WIN_WORDS / 4;
     for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
-    if (threadIdx.x == 0) make_slot_pairs(g, st.pairs, st.tbls);
+    if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(ldst));
     if (threadIdx.x >= 32 && threadIdx.x < 96) st.natural[threadIdx.x - 32] = c_natural[threadIdx.x - 32];
     __syncthreads();
 }
 
-// Device memory policy of decode_span over the staged window.  `wrel` maps a segment-relative
-// word index to a window index.
-template <int WIN_WORDS>
+// Device memory policy of decode_span over the staged window: every handle is a shared-memory
+// byte address.  `win_addr` = address of the window word that holds segment-relative word 0.
 struct DevMem {
     const SharedTables* st;
     const HuffSlow* slow_;
-    int wrel;
-    __device__ __forceinline__ uint16_t lut(uint32_t i) const
+    uint32_t recs_addr;
+    uint32_t win_addr;
+    static constexpr uint32_t kWordStep = 4;
+    __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
+    __device__ __forceinline__ uint32_t slot_handle(uint32_t c) const
     {
-        return reinterpret_cast<const uint16_t*>(s_dyn + WIN_WORDS / 4)[i];
+        return recs_addr + c * (uint32_t)sizeof(SlotRec);
     }
-    __device__ __forceinline__ SlotPair pair(uint32_t c) const
-    {
-        const uint2 v = *reinterpret_cast<const uint2*>(&st->pairs[c]);
-        return SlotPair{v.x, v.y};
-    }
+    __device__ __forceinline__ SlotRec rec(uint32_t h) const { return lds_rec(h); }
     __device__ __forceinline__ uint32_t slot_tbls(uint32_t c) const { return st->tbls[c]; }
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t natural(uint32_t i) const { return st->natural[i]; }
-    __device__ __forceinline__ uint32_t word(uint32_t i) const
-    {
-        return reinterpret_cast<const uint32_t*>(s_dyn)[(int)i + wrel];
-    }
+    __device__ __forceinline__ uint32_t word_handle(uint32_t i) const { return win_addr + i * 4u; }
+    __device__ __forceinline__ uint32_t word(uint32_t h) const { return lds32_pinned(h); }
+    __device__ __forceinline__ void note_long_code() const {}
 };
 
-// Fallback policy of huff_link: tables in shared memory, the scan read from global memory.
+// Fallback policy of huff_link: tables in shared memory (LUT pool at s_dyn), the scan read from
+// global memory.
 struct GlobalMem {
     const SharedTables* st;
     const HuffSlow* slow_;
+    uint32_t recs_addr;
     const uint32_t* words;
-    __device__ __forceinline__ uint16_t lut(uint32_t i) const
+    static constexpr uint32_t kWordStep = 1;
+    __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
+    __device__ __forceinline__ uint32_t slot_handle(uint32_t c) const
     {
-        return reinterpret_cast<const uint16_t*>(s_dyn)[i];
+        return recs_addr + c * (uint32_t)sizeof(SlotRec);
     }
-    __device__ __forceinline__ SlotPair pair(uint32_t c) const { return st->pairs[c]; }
+    __device__ __forceinline__ SlotRec rec(uint32_t h) const { return lds_rec(h); }
     __device__ __forceinline__ uint32_t slot_tbls(uint32_t c) const { return st->tbls[c]; }
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t natural(uint32_t i) const { return st->natural[i]; }
-    __device__ __forceinline__ uint32_t word(uint32_t i) const { return __ldg(words + i); }
+    __device__ __forceinline__ uint32_t word_handle(uint32_t i) const { return i; }
+    __device__ __forceinline__ uint32_t word(uint32_t h) const { return __ldg(words + h); }
+    __device__ __forceinline__ void note_long_code() const {}
 };
 
 __device__ __forceinline__ void zero_fill(void* base, size_t bytes)
@@ -129,7 +174,7 @@ __device__ __forceinline__ void zero_fill(void* base, size_t bytes)
     for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) p[i] = z;
 }
 
-__global__ void __launch_bounds__(kHuffThreads)
+__global__ void __launch_bounds__(kHuffThreads, 1)
 huff_sync(const ScanGeom g, const ScanBufs b)
 {
     __shared__ SharedTables st;
@@ -147,14 +192,14 @@ huff_sync(const ScanGeom g, const ScanBufs b)
 
     uint32_t k = 0, i = 0, seg_bits = 0;
     bool head = false;
-    DevMem<kSyncWinWords> M{&st, b.slow, 0};
+    DevMem M{&st, b.slow, smem_addr(st.recs), 0};
     if (active) {
         k = find_segment(b.segs, g.num_segments, (uint32_t)sub);
         const SegDesc seg = b.segs[k];
         i = (uint32_t)sub - seg.sub_off;
         head = i == 0;
         seg_bits = seg.nbytes * 8u;
-        M.wrel = (int)((long long)seg.sub_off - win_sub0) * kSubWords;
+        M.win_addr = smem_addr(s_dyn) + (uint32_t)((int)((long long)seg.sub_off - win_sub0) * kSubBytes);
     }
 
     // fix-point iteration inside the warp; lanes <= frozen keep their entry state
@@ -209,7 +254,7 @@ huff_sync(const ScanGeom g, const ScanBufs b)
 
 constexpr int kLinkThreads = 1024;
 
-__global__ void __launch_bounds__(kLinkThreads)
+__global__ void __launch_bounds__(kLinkThreads, 1)
 huff_link(const ScanGeom g, const ScanBufs b)
 {
     __shared__ SharedTables st;
@@ -217,6 +262,8 @@ huff_link(const ScanGeom g, const ScanBufs b)
     volatile unsigned long long* entries = reinterpret_cast<volatile unsigned long long*>(b.entries);
     const uint32_t N = g.num_subs;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long t_start = 0, t_verified = 0;
+    if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
 
     // ---- verify (and, rarely, repair) ------------------------------------------------------
     uint32_t stride = (uint32_t)kChunkSubs; // first round: only chunk boundaries can disagree
@@ -228,10 +275,10 @@ huff_link(const ScanGeom g, const ScanBufs b)
             bad |= boundary_ok(entries[j - 1], entries[j]) ? 0u : 1u;
         if (!__syncthreads_or((int)bad)) break;
         if (!staged) { // tables are only needed on this path
-            const uint32_t lut_vec = (g.lut_pool_u16 + 7) / 8;
+            const uint32_t lut_vec = (g.lut_pool_words + 3) / 4;
             for (uint32_t v = threadIdx.x; v < lut_vec; v += kLinkThreads)
                 s_dyn[v] = __ldg(reinterpret_cast<const uint4*>(b.lut_pool) + v);
-            if (threadIdx.x == 0) make_slot_pairs(g, st.pairs, st.tbls);
+            if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(s_dyn));
             if (threadIdx.x < 64) st.natural[threadIdx.x] = c_natural[threadIdx.x];
             staged = true;
             __syncthreads();
@@ -240,7 +287,8 @@ huff_link(const ScanGeom g, const ScanBufs b)
         for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kLinkThreads) {
             if (boundary_ok(entries[j - 1], entries[j])) continue;
             const SegDesc seg = b.segs[b.seg_idx[j]];
-            const GlobalMem M{&st, b.slow, b.destuffed + (size_t)seg.sub_off * kSubWords};
+            const GlobalMem M{&st, b.slow, smem_addr(st.recs),
+                              b.destuffed + (size_t)seg.sub_off * kSubWords};
             rewritten += relink_from(M, seg, entries, j);
         }
         slow_total += rewritten;
@@ -249,51 +297,96 @@ huff_link(const ScanGeom g, const ScanBufs b)
         __syncthreads();
     }
 
+    if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_verified));
     // ---- segmented exclusive scan of the slot counts ---------------------------------------
-    const uint32_t per = (N + kLinkThreads - 1) / kLinkThreads;
-    const uint32_t j0 = umin(per * threadIdx.x, N), j1 = umin(j0 + per, N);
-    uint32_t sum = 0, flag = 0;
-    for (uint32_t j = j0; j < j1; ++j) {
-        const unsigned long long e = entries[j];
-        if (entry_g(e) & kStateHead) sum = 0, flag = 1;
-        sum += entry_n(e);
-    }
-    // inclusive segmented scan over threads of (sum, flag)
-    uint32_t inc = sum, f = flag;
+    // Tiles of 4 records per thread: coalesced 32-byte loads and 16-byte stores (a strided
+    // per-thread run made every load its own sector and took 10x longer on one SM).
+    __shared__ uint32_t s_carry, s_excl[kLinkThreads / 32];
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const unsigned long long* ent = reinterpret_cast<const unsigned long long*>(b.entries);
+    constexpr uint32_t kPer = 4, kTile = kLinkThreads * kPer;
+    for (uint32_t base = 0; base < N; base += kTile) {
+        const uint32_t j0 = base + threadIdx.x * kPer;
+        unsigned long long e[kPer];
+        if (j0 + kPer <= N) {
+            const ulonglong2 a0 = __ldcg(reinterpret_cast<const ulonglong2*>(ent + j0));
+            const ulonglong2 a1 = __ldcg(reinterpret_cast<const ulonglong2*>(ent + j0 + 2));
+            e[0] = a0.x, e[1] = a0.y, e[2] = a1.x, e[3] = a1.y;
+        } else {
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
-        const uint32_t upf = __shfl_up_sync(0xffffffffu, f, d);
-        if (lane >= d) {
-            if (!f) inc += up;
-            f |= upf;
+            for (uint32_t i = 0; i < kPer; ++i) e[i] = j0 + i < N ? __ldcg(ent + j0 + i) : 0ull;
         }
-    }
-    if (lane == 31) s_sum[warp] = inc, s_flag[warp] = f;
-    __syncthreads();
-    uint32_t carry = 0;
-    if (!f)
-        for (int w = warp - 1; w >= 0; --w) {
-            carry += s_sum[w];
-            if (s_flag[w]) break;
+        uint32_t sum = 0, flag = 0;
+#pragma unroll
+        for (uint32_t i = 0; i < kPer; ++i) {
+            if (entry_g(e[i]) & kStateHead) sum = 0, flag = 1;
+            sum += entry_n(e[i]);
         }
-    inc += carry; // inclusive over threads, restarted at segment heads
-    // Carry-in of thread t = inclusive value of thread t-1 (segment restarts already applied).
-    __shared__ uint32_t s_inc[kLinkThreads];
-    s_inc[threadIdx.x] = inc;
-    __syncthreads();
-    uint32_t acc = threadIdx.x ? s_inc[threadIdx.x - 1] : 0u;
-    for (uint32_t j = j0; j < j1; ++j) {
-        const unsigned long long e = entries[j];
-        if (entry_g(e) & kStateHead) acc = 0;
-        b.qpos[j] = acc;
-        acc += entry_n(e);
+        // inclusive segmented scan over threads of (sum, flag)
+        uint32_t inc = sum, f = flag;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+            const uint32_t upf = __shfl_up_sync(0xffffffffu, f, d);
+            if (lane >= d) {
+                if (!f) inc += up;
+                f |= upf;
+            }
+        }
+        if (lane == 31) s_sum[warp] = inc, s_flag[warp] = f;
+        __syncthreads();
+        if (warp == 0) { // second level: segmented scan of the 32 warp aggregates
+            uint32_t v = s_sum[lane], gf = s_flag[lane];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, v, d);
+                const uint32_t upg = __shfl_up_sync(0xffffffffu, gf, d);
+                if (lane >= d) {
+                    if (!gf) v += up;
+                    gf |= upg;
+                }
+            }
+            const uint32_t tile_carry = s_carry;
+            const uint32_t incl = gf ? v : v + tile_carry; // running value after warp `lane`
+            uint32_t excl = __shfl_up_sync(0xffffffffu, incl, 1);
+            if (lane == 0) excl = tile_carry;
+            s_excl[lane] = excl;
+            if (lane == 31) s_carry = incl; // every lane read tile_carry before the shuffles
+        }
+        __syncthreads();
+        // running value before this thread's records
+        uint32_t acc = __shfl_up_sync(0xffffffffu, inc, 1);
+        const uint32_t fex = __shfl_up_sync(0xffffffffu, f, 1);
+        if (lane == 0) acc = s_excl[warp];
+        else if (!fex) acc += s_excl[warp];
+        uint32_t out[kPer];
+#pragma unroll
+        for (uint32_t i = 0; i < kPer; ++i) {
+            if (entry_g(e[i]) & kStateHead) acc = 0;
+            out[i] = acc;
+            acc += entry_n(e[i]);
+        }
+        if (j0 + kPer <= N) {
+            *reinterpret_cast<uint4*>(b.qpos + j0) = make_uint4(out[0], out[1], out[2], out[3]);
+        } else {
+#pragma unroll
+            for (uint32_t i = 0; i < kPer; ++i)
+                if (j0 + i < N) b.qpos[j0 + i] = out[i];
+        }
+        // no barrier here: s_sum / s_excl are rewritten only behind the next tile's barriers
     }
     if (slow_total) atomicAdd(&b.ctrl->slow_repairs, slow_total);
-    if (threadIdx.x == 0) b.ctrl->link_rounds = rounds;
+    if (threadIdx.x == 0) {
+        unsigned long long t_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        b.ctrl->link_rounds = rounds;
+        b.ctrl->link_verify_ns = (uint32_t)(t_verified - t_start);
+        b.ctrl->link_scan_ns = (uint32_t)(t_end - t_verified);
+    }
 }
 
-__global__ void __launch_bounds__(kHuffThreads)
+__global__ void __launch_bounds__(kHuffThreads, 1)
 huff_write(const ScanGeom g, const ScanBufs b)
 {
     __shared__ SharedTables st;
@@ -303,7 +396,8 @@ huff_write(const ScanGeom g, const ScanBufs b)
     if (j >= g.num_subs) return;
     const uint32_t k = b.seg_idx[j];
     const SegDesc seg = b.segs[k];
-    const DevMem<kWriteWinWords> M{&st, b.slow, (int)((long long)seg.sub_off - (long long)sub0) * kSubWords};
+    const DevMem M{&st, b.slow, smem_addr(st.recs),
+                   smem_addr(s_dyn) + (uint32_t)((int)((long long)seg.sub_off - (long long)sub0) * kSubBytes)};
     const unsigned long long e = reinterpret_cast<const unsigned long long*>(b.entries)[j];
     write_sub(M, g, seg, k, j - seg.sub_off, (uint16_t)(entry_g(e) & kStateMask), b.qpos[j], b.coef, b.dc);
 }
@@ -313,14 +407,13 @@ huff_write(const ScanGeom g, const ScanBufs b)
 cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.num_subs == 0) return cudaSuccess;
-    const size_t lut_bytes = (size_t)((g.lut_pool_u16 + 7) / 8) * 16;
-    static bool attr_done = false; // per process; all kernels share the same upper bound
-    if (!attr_done) {
-        const int max_smem = 160 * 1024;
-        cudaFuncSetAttribute(huff_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        cudaFuncSetAttribute(huff_link, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        cudaFuncSetAttribute(huff_write, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-        attr_done = true;
+    const size_t lut_bytes = (size_t)((g.lut_pool_words + 3) / 4) * 16;
+    static std::atomic<unsigned long long> configured{0};
+    if (first_use_on_device(configured)) {
+        const int max_smem = 200 * 1024;
+        prefer_max_shared(huff_sync, max_smem);
+        prefer_max_shared(huff_link, max_smem);
+        prefer_max_shared(huff_write, max_smem);
     }
     const uint32_t chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
     tm->mark(stream, kIdSync);

@@ -9,7 +9,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SRC = os.path.join(ROOT, "tests", "host_emul", "emul.cpp")
 CSRC = os.path.join(ROOT, "jpeggpu_b200", "csrc")
-OUT = os.path.join(ROOT, "tests", "host_emul", "_build", "libemul.so")
+DEFS = os.environ.get("JB2_DEFS", "").split()  # e.g. "-DJB2_SUB_BYTES=32 -DJB2_OVERLAP_SUBS=12" (experiments)
+OUT = os.path.join(ROOT, "tests", "host_emul", "_build",
+                   "libemul" + "".join(d.replace("-D", "_").replace("=", "") for d in DEFS) + ".so")
 CUDA_INC = "/usr/local/cuda/include"
 
 _lib = None
@@ -21,7 +23,7 @@ def lib():
         deps = [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".hpp", ".cpp"))]
         if not os.path.exists(OUT) or any(os.path.getmtime(d) > os.path.getmtime(OUT) for d in deps):
             os.makedirs(os.path.dirname(OUT), exist_ok=True)
-            subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-I" + CSRC,
+            subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", *DEFS, "-I" + CSRC,
                             "-I" + os.path.join(ROOT, "include"), "-I" + CUDA_INC, SRC,
                             os.path.join(CSRC, "parser.cpp"), "-o", OUT], check=True)
         L = C.CDLL(OUT)

@@ -7,6 +7,8 @@
 #include "huff_threads.hpp"
 #include "parser.hpp"
 
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -57,13 +59,13 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     const size_t need = (size_t)g.total_mcus * g.dus_per_mcu * 64;
     if (coef_count < need) return -2;
 
-    std::vector<uint16_t> pool;
+    std::vector<uint32_t> pool;
     HuffSlow slow[kMaxTables];
-    for (int t = 0; t < g.num_tables; ++t) g.table_off[t] = (uint16_t)build_lut(sp.tables[t], pool, slow[t]);
-    g.lut_pool_u16 = (uint32_t)pool.size();
-    SlotPair pairs[kMaxDuPerMcu];
+    for (int t = 0; t < g.num_tables; ++t) g.table_off[t] = build_lut(sp.tables[t], pool, slow[t]);
+    g.lut_pool_words = (uint32_t)pool.size();
+    SlotRec recs[kMaxDuPerMcu];
     uint32_t tbls[kMaxDuPerMcu];
-    make_slot_pairs(g, pairs, tbls);
+    make_slot_recs(g, recs, tbls);
 
     // destuff: the contract of destuff_kernel, tile by tile from the host tile directory
     const uint32_t N = g.num_subs;
@@ -105,8 +107,10 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         for (size_t d = 0; d < n; ++d) destuffed_out[d] = dst[d ^ 3u];
     }
     const uint32_t* words = reinterpret_cast<const uint32_t*>(dst.data());
+    long long_codes = 0;
     auto mem_of = [&](const SegDesc& seg) {
-        return HostMem{pool.data(), pairs, tbls, slow, kNat, words + (size_t)seg.sub_off * kSubWords};
+        return HostMem{pool.data(), recs, tbls, slow, kNat, words + (size_t)seg.sub_off * kSubWords,
+                       &long_codes};
     };
 
     // huff_sync: one "warp" per chunk, lanes emulated by arrays; chunks in launch order so the
@@ -116,6 +120,8 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     const uint32_t chunks = (N + kChunkSubs - 1) / kChunkSubs;
     std::vector<uint32_t> mailbox(chunks, 0);
     int relinked = 0, rounds_max = 0, rounds_sum = 0;
+    long diag[3] = {0, 0, 0};
+    int passes_max = 0;
     for (uint32_t chunk = 0; chunk < chunks; ++chunk) {
         const uint32_t chunk_first = chunk * kChunkSubs;
         bool active[32], head[32];
@@ -136,6 +142,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
             seg_bits[l] = seg.nbytes * 8u;
             rec[l] = decode_sub(mem_of(seg), seg_bits[l], i[l], 0);
         }
+        int chunk_passes = 1;
         auto iterate = [&](int frozen) {
             int rounds = 0;
             for (;;) {
@@ -150,12 +157,22 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                 ++rounds;
                 for (int l = 0; l < 32; ++l)
                     if (want[l] != entry[l]) {
+                        if (rounds >= 4 && getenv("EMUL_DIAG")) {
+                            const uint16_t d = want[l] ^ entry[l];
+                            ++diag[(d & 0x1f) ? 0 : (d & 0x7e00) ? 1 : 2]; // o differs / z differs / c only
+                        }
                         entry[l] = want[l];
                         rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l]);
                     }
             }
+            if (rounds >= 100 && getenv("EMUL_DIAG")) {
+                fprintf(stderr, "chunk %u rounds %d frozen %d n:", chunk, rounds, frozen);
+                for (int l = 0; l < 32; l += 3) fprintf(stderr, " %u", entry_n(rec[l]));
+                fprintf(stderr, "\n");
+            }
             if (rounds > rounds_max) rounds_max = rounds;
             rounds_sum += rounds;
+            chunk_passes += rounds;
         };
         iterate(0);
         const uint32_t last_sub = umin(chunk_first + kChunkSubs, N) - 1;
@@ -172,6 +189,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                 mailbox[chunk] = 0x80000000u | entry_x(rec[last_lane]);
             }
         }
+        if (chunk_passes > passes_max) passes_max = chunk_passes;
         for (int l = kOverlapSubs; l < 32; ++l)
             if (active[l]) {
                 const uint32_t sub = chunk_first - kOverlapSubs + l;
@@ -180,10 +198,12 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                 seg_idx[sub] = k[l];
             }
     }
+    if (getenv("EMUL_DIAG")) fprintf(stderr, "late changes: o %ld, z(not o) %ld, c only %ld\n", diag[0], diag[1], diag[2]);
     stats[0] = relinked;
     stats[1] = rounds_max;
     stats[5] = rounds_sum;
     stats[6] = (int)chunks;
+    if (getenv("EMUL_DIAG")) fprintf(stderr, "S=%d R=%d chunks %u relinked %d passes_max %d rounds_avg %.2f\n", kSubBytes, kOverlapSubs, chunks, relinked, passes_max, (double)rounds_sum / chunks);
     stats[3] = (int)N;
 
     // huff_link: verify chunk boundaries, sequential fallback, segmented exclusive scan
@@ -217,6 +237,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     }
 
     // huff_write
+    long_codes = 0;
     memset(coef, 0, need * sizeof(int16_t));
     std::vector<int16_t> dc((size_t)g.total_mcus * g.dus_per_mcu, 0);
     for (uint32_t j = 0; j < N; ++j) {
@@ -224,6 +245,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         write_sub(mem_of(seg), g, seg, seg_idx[j], j - seg.sub_off,
                   (uint16_t)(entry_g(entries[j]) & kStateMask), qpos[j], coef, dc.data());
     }
+    if (getenv("EMUL_DIAG")) fprintf(stderr, "lut bits %d: long codes in the write pass %ld\n", kLutBits, long_codes);
     // DC: the contract of dc_tile_sums + dc_apply
     for (int a = 0; a < g.num_comp; ++a) {
         int pred = 0;

@@ -74,7 +74,7 @@ def test_parse_header_on_cpu(lib):
     st = d.scan_stats(0)
     assert st.dus_per_mcu == 6 and st.total_mcus == 41 * 30
     assert st.num_segments == (41 * 30 + 3) // 4
-    assert d.transfer_size() < len(data) + 64 * 1024
+    assert d.transfer_size() < len(data) + 256 * 1024  # + decode LUTs and directories
     w, h = d.coefficient_size()
     assert (w[0], h[0], w[1], h[1]) == (656, 480, 328, 240)
     d.cleanup()
