@@ -56,7 +56,7 @@ constexpr int kDestuffTile = kDestuffThreads * kDestuffBytesPerThread; // stuffe
 // advance at the bottom so that it is a single mask; an entry whose skip field is zero is a
 // marker (kEntryLong / kEntrySlow).
 #ifndef JB2_LUT_BITS
-#define JB2_LUT_BITS 12
+#define JB2_LUT_BITS 11
 #endif
 constexpr int kLutBits = JB2_LUT_BITS;
 constexpr int kLut1Size = 1 << kLutBits;
@@ -101,10 +101,13 @@ struct SegDesc {          // one per restart segment, built by the host walk
     uint32_t src_begin;   // stuffed offset (relative to scan start) of the first byte
 };
 
-struct SubEntry { // per-subsequence sync record, stored as one 8-byte word
+struct SubEntry { // per-subsequence sync record: two 8-byte words
     uint16_t g;   // packed entry state (bit 15: first subsequence of a restart segment)
     uint16_t x;   // packed exit state given g
     uint32_t n;   // slots advanced inside the subsequence given g
+    uint16_t gm;  // packed state at the middle of the subsequence (entry of its second half)
+    uint16_t nm;  // slots advanced inside the first half
+    uint32_t pad;
 };
 constexpr uint16_t kStateHead = 0x8000u;
 constexpr uint16_t kStateMask = 0x7fffu;
@@ -163,7 +166,14 @@ struct Control {
     uint32_t link_rounds;
     uint32_t link_verify_ns; // device-side phase times of huff_link (diagnostics)
     uint32_t link_scan_ns;
-    uint32_t pad[11];
+    uint32_t write_stage_ns;  // slowest CTA of huff_write: staging / decode / flush (diagnostics)
+    uint32_t write_decode_ns;
+    uint32_t write_flush_ns;
+    uint32_t sync_stage_ns;   // slowest CTA of huff_sync: staging / fix-point iteration
+    uint32_t sync_iter_ns;
+    uint32_t write_tiles_max; // most tiles any warp of huff_write assembled
+    uint32_t write_tiles;     // tiles assembled by all warps
+    uint32_t pad[4];
 };
 
 // zig-zag -> natural order (T.81 Figure A.6; same table as src/defs.hpp:94-102)

@@ -24,7 +24,8 @@
 //   slot_handle(c) -> handle of MCU slot c;  rec(h) -> SlotRec of that slot
 //   slot_tbls(c)   -> dc table slot | ac table slot << 8   (slow path only)
 //   slow(slot)     -> HuffSlow
-//   natural(i)     -> zig-zag to raster index
+//   put(slot, v)   -> store a non-zero coefficient (slot = data unit * 64 + zig-zag index,
+//                     segment relative; slot % 64 == 0 is a DC difference)
 //   word_handle(i) -> handle of big-endian word i of the scan window the policy was built for;
 //   word(h)        -> that word; consecutive words are kWordStep handles apart
 #ifndef JB2_HUFF_CORE_HPP_
@@ -127,11 +128,11 @@ JB2_HD void advance_unit(uint32_t& qq, uint32_t qn, uint32_t& ch, uint32_t& tbl,
 
 // Decode the symbols that start in [p, end).  State: p bit position inside the policy's word
 // window, q linear slot counter (q & 63 = zig-zag index), c MCU slot of the current data unit.
-// WRITE: store the non-zero AC coefficients at out[(q >> 6) * 64 + natural[q & 63]] and every DC
-// difference (zero or not) at dc_out[q >> 6], while q < q_limit.
+// WRITE: hand every non-zero coefficient (DC differences included) to the policy's put(slot, v),
+// slot = q of the coefficient (data unit q >> 6, zig-zag index q & 63), while q < q_limit.
 template <bool WRITE, class Mem>
 JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, uint32_t& c,
-                        int16_t* out, int16_t* dc_out, uint32_t q_limit)
+                        uint32_t q_limit)
 {
     if (p >= end || (WRITE && q >= q_limit)) return;
     uint32_t pp = p, qq = q;
@@ -159,17 +160,13 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
             const uint32_t skip = entry_skip(e);
             const uint32_t qn = qq + entry_adv(e);
             if (WRITE) {
+                // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
+                // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers)
                 const uint32_t size = entry_size(e);
                 const uint32_t pos = qn - 1u;
-                const bool is_dc = (qq & 63u) == 0;
-                if ((size != 0 || is_dc) && ((pos ^ qq) & 64u) == 0) {
-                    int v = 0;
-                    if (size != 0) {
-                        const uint32_t bits = (peek << (skip - size)) >> (32 - size);
-                        v = extend_value(bits, size);
-                    }
-                    if (is_dc) dc_out[pos >> 6] = (int16_t)v;
-                    else out[(size_t)(pos & ~63u) + M.natural(pos & 63u)] = (int16_t)v;
+                if (size != 0 && ((pos ^ qq) & 64u) == 0) {
+                    const uint32_t bits = (peek << (skip - size)) >> (32 - size);
+                    M.put(pos, extend_value(bits, size));
                 }
             }
             const uint32_t pn = pp + skip;
@@ -208,7 +205,6 @@ struct HostMem {
     const SlotRec* recs_;
     const uint32_t* tbls_; // per MCU slot: dc table slot | ac table slot << 8
     const HuffSlow* slow_;
-    const uint8_t* natural_;
     const uint32_t* words_; // word 0 = first word of the restart segment
     static constexpr uint32_t kWordStep = 1;
     JB2_HD uint32_t lut(uint32_t tbl, uint32_t i) const { return lut_[(uint32_t)(tbl + i)]; }
@@ -216,9 +212,15 @@ struct HostMem {
     JB2_HD SlotRec rec(uint32_t h) const { return recs_[h]; }
     JB2_HD uint32_t slot_tbls(uint32_t c) const { return tbls_[c]; }
     JB2_HD const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
-    JB2_HD uint32_t natural(uint32_t i) const { return natural_[i]; }
     JB2_HD uint32_t word_handle(uint32_t i) const { return i; }
     JB2_HD uint32_t word(uint32_t h) const { return words_[h]; }
+    int16_t* coef_ = nullptr; // WRITE: first data unit of the restart segment
+    int16_t* dc_ = nullptr;
+    JB2_HD void put(uint32_t slot, int v) const
+    {
+        if ((slot & 63u) == 0) dc_[slot >> 6] = (int16_t)v;
+        else coef_[slot] = (int16_t)v;
+    }
     long* long_codes_ = nullptr; // optional statistics
     JB2_HD void note_long_code() const
     {

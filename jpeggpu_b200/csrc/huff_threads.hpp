@@ -35,18 +35,23 @@ JB2_HD uint32_t subs_in_segment(const SegDesc& seg)
 }
 
 // Decode subsequence i of a segment (policy M addresses words relative to the segment start)
-// from packed entry state `gs` (15 bits); returns {gs, exit state, slots advanced}.
+// from packed entry state `gs` (15 bits); returns {gs, exit state, slots advanced} and, in *mid,
+// the state at the middle of the subsequence | slots advanced before it << 16 (the write pass
+// splits every subsequence between two threads there).
 template <class Mem>
-JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t seg_bits, uint32_t i, uint16_t gs)
+JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t seg_bits, uint32_t i, uint16_t gs,
+                                     uint32_t* mid)
 {
     const uint32_t start = i * (uint32_t)kSubBits;
+    const uint32_t half = start + (uint32_t)kSubBits / 2u;
     const uint32_t sub_end = start + (uint32_t)kSubBits;
-    const uint32_t end = umin(sub_end, seg_bits);
     uint32_t p = start + (gs & 31u);
     uint32_t c = (gs >> 5) & 15u;
     const uint32_t z = (gs >> 9) & 63u;
     uint32_t q = z;
-    decode_span<false>(M, p, end, q, c, nullptr, nullptr, 0u);
+    decode_span<false>(M, p, umin(half, seg_bits), q, c, 0u);
+    *mid = pack_state(p > half ? p - half : 0u, c, q & 63u) | ((q - z) << 16);
+    decode_span<false>(M, p, umin(sub_end, seg_bits), q, c, 0u);
     const uint32_t o = p > sub_end ? p - sub_end : 0u;
     return pack_entry(gs, pack_state(o, c, q & 63u), q - z);
 }
@@ -58,19 +63,21 @@ JB2_HD bool boundary_ok(unsigned long long prev, unsigned long long cur)
 }
 
 // huff_link fallback: re-decode forward from subsequence j (entry = exit of j-1) until the
-// stored records agree again.  M addresses words relative to the segment start.  Returns the
-// number of records rewritten.
-template <class Mem, typename EntryPtr>
-JB2_HD uint32_t relink_from(const Mem& M, const SegDesc& seg, EntryPtr entries, uint32_t j)
+// stored records agree again.  M addresses words relative to the segment start; `lo` / `hi` are
+// the two words of every record (stride 2).  Returns the number of records rewritten.
+template <class Mem, typename WordPtr>
+JB2_HD uint32_t relink_from(const Mem& M, const SegDesc& seg, WordPtr rec_words, uint32_t j)
 {
     const uint32_t seg_bits = seg.nbytes * 8u;
     const uint32_t seg_end = seg.sub_off + subs_in_segment(seg);
-    uint16_t state = entry_x(entries[j - 1]);
+    uint16_t state = entry_x(rec_words[2 * (size_t)(j - 1)]);
     uint32_t rewritten = 0;
     for (uint32_t m = j; m < seg_end; ++m) {
-        if (m != j && (entry_g(entries[m]) & kStateMask) == state) break;
-        const unsigned long long e = decode_sub(M, seg_bits, m - seg.sub_off, state);
-        entries[m] = e;
+        if (m != j && (entry_g(rec_words[2 * (size_t)m]) & kStateMask) == state) break;
+        uint32_t mid;
+        const unsigned long long e = decode_sub(M, seg_bits, m - seg.sub_off, state, &mid);
+        rec_words[2 * (size_t)m + 1] = mid;
+        rec_words[2 * (size_t)m] = e;
         state = entry_x(e);
         ++rewritten;
     }
@@ -89,19 +96,21 @@ JB2_HD bool segment_extent(const ScanGeom& g, uint32_t k, uint32_t& first_du, ui
     return true;
 }
 
-// huff_write body: decode subsequence i of segment k from its verified record and place the
-// coefficients.  q0 = slot (segment relative) at which the subsequence starts.
+// huff_write body: decode one half (h = 0, 1) of subsequence i from its verified record and hand
+// the coefficients to the policy.  q0 = slot (segment relative) at which the subsequence starts.
 template <class Mem>
-JB2_HD void write_sub(const Mem& M, const ScanGeom& g, const SegDesc& seg, uint32_t k, uint32_t i,
-                      uint16_t gs, uint32_t q0, int16_t* coef, int16_t* dc)
+JB2_HD void write_half(const Mem& M, const SegDesc& seg, uint32_t i, uint32_t h,
+                       unsigned long long rec, uint32_t mid, uint32_t q0, uint32_t q_limit)
 {
-    uint32_t first_du, q_limit;
-    if (!segment_extent(g, k, first_du, q_limit)) return;
-    uint32_t q = q0;
+    const uint32_t start = i * (uint32_t)kSubBits;
+    const uint32_t half = start + (uint32_t)kSubBits / 2u;
+    const uint32_t seg_bits = seg.nbytes * 8u;
+    const uint32_t gs = h ? (mid & 0x7fffu) : (entry_g(rec) & kStateMask);
+    uint32_t q = h ? q0 + (mid >> 16) : q0;
     uint32_t c = (gs >> 5) & 15u;
-    uint32_t p = i * (uint32_t)kSubBits + (gs & 31u);
-    const uint32_t end = umin((i + 1u) * (uint32_t)kSubBits, seg.nbytes * 8u);
-    decode_span<true>(M, p, end, q, c, coef + (size_t)first_du * 64, dc + first_du, q_limit);
+    uint32_t p = (h ? half : start) + (gs & 31u);
+    const uint32_t end = umin(h ? start + (uint32_t)kSubBits : half, seg_bits);
+    decode_span<true>(M, p, end, q, c, q_limit);
 }
 
 } // namespace jb2

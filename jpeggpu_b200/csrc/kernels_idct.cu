@@ -17,6 +17,23 @@
 namespace jb2 {
 namespace {
 
+// zig-zag index -> raster index inside a data unit (T.81 Figure A.6), foldable at compile time
+__host__ __device__ constexpr int natural_of(int z)
+{
+    constexpr int t[64] = {JB2_NATURAL_ORDER};
+    return t[z];
+}
+struct ZigzagOf { // raster index -> zig-zag index
+    uint8_t v[64];
+};
+constexpr ZigzagOf make_zigzag_of()
+{
+    ZigzagOf r{};
+    for (int z = 0; z < 64; ++z) r.v[natural_of(z)] = (uint8_t)z;
+    return r;
+}
+__constant__ ZigzagOf c_zigzag_of = make_zigzag_of();
+
 __device__ __forceinline__ int unfixh(int x) { return (int)(short)((x + 0x8000) >> 16); }
 __device__ __forceinline__ int unfixo(int x) { return (x + 0x1000) >> 13; }
 
@@ -92,6 +109,8 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const OutPlanes 
     if (!locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos)) return;
     const int a = pos.comp;
     const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)pos.du * 64);
+    // the buffer holds every data unit in zig-zag order: un-zig-zag while loading (register
+    // indices are compile-time constants after unrolling)
     int v[8][8];
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
@@ -101,9 +120,10 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const OutPlanes 
         for (int k = 0; k < 4; ++k) {
             const int lo = (int)(short)(ww[k] & 0xffffu);
             const int hi = (int)(short)(ww[k] >> 16);
+            const int n0 = natural_of(r * 8 + 2 * k), n1 = natural_of(r * 8 + 2 * k + 1);
             // src/idct.cu:178-180: the product is stored as int16
-            v[r][2 * k] = (int)(short)(lo * s_q[a][r * 8 + 2 * k]);
-            v[r][2 * k + 1] = (int)(short)(hi * s_q[a][r * 8 + 2 * k + 1]);
+            v[n0 >> 3][n0 & 7] = (int)(short)(lo * s_q[a][n0]);
+            v[n1 >> 3][n1 & 7] = (int)(short)(hi * s_q[a][n1]);
         }
     }
 #pragma unroll
@@ -141,8 +161,8 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const OutPlanes 
     }
 }
 
-// Stand-alone transpose: coded order -> planar raster int16 (row length = plane stride).
-// One thread moves one 8-coefficient row (16 B), eight consecutive threads one DU.
+// Stand-alone transpose: coded order (zig-zag inside a DU) -> planar raster int16 (row length =
+// plane stride).  One thread gathers one 8-coefficient raster row, eight consecutive threads one DU.
 __global__ void __launch_bounds__(256)
 transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const CoefPlanes planes)
 {
@@ -150,10 +170,17 @@ transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const CoefP
     const uint32_t r = t & 7u;
     DuPos pos;
     if (!locate(g, t >> 3, pos)) return;
-    const uint4 w = reinterpret_cast<const uint4*>(coef + (size_t)pos.du * 64)[r];
+    const int16_t* du = coef + (size_t)pos.du * 64;
+    uint32_t px[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t lo = (uint16_t)du[c_zigzag_of.v[r * 8 + 2 * k]];
+        const uint32_t hi = (uint16_t)du[c_zigzag_of.v[r * 8 + 2 * k + 1]];
+        px[k] = lo | (hi << 16);
+    }
     int16_t* dst = planes.ptr[pos.comp] +
                    (size_t)(pos.by * 8 + (int)r) * planes.stride[pos.comp] + pos.bx * 8;
-    *reinterpret_cast<uint4*>(dst) = w;
+    *reinterpret_cast<uint4*>(dst) = make_uint4(px[0], px[1], px[2], px[3]);
 }
 
 } // namespace

@@ -109,13 +109,16 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     const uint32_t* words = reinterpret_cast<const uint32_t*>(dst.data());
     long long_codes = 0;
     auto mem_of = [&](const SegDesc& seg) {
-        return HostMem{pool.data(), recs, tbls, slow, kNat, words + (size_t)seg.sub_off * kSubWords,
-                       &long_codes};
+        HostMem m{pool.data(), recs, tbls, slow, words + (size_t)seg.sub_off * kSubWords};
+        m.long_codes_ = &long_codes;
+        return m;
     };
 
     // huff_sync: one "warp" per chunk, lanes emulated by arrays; chunks in launch order so the
     // left mailbox is always there (one valid schedule of the kernel)
-    std::vector<unsigned long long> entries(N);
+    std::vector<unsigned long long> entries(2 * (size_t)N); // two words per record
+    auto rec_lo = [&](uint32_t j) -> unsigned long long& { return entries[2 * (size_t)j]; };
+    auto rec_hi = [&](uint32_t j) -> unsigned long long& { return entries[2 * (size_t)j + 1]; };
     std::vector<uint32_t> seg_idx(N), qpos(N + 1);
     const uint32_t chunks = (N + kChunkSubs - 1) / kChunkSubs;
     std::vector<uint32_t> mailbox(chunks, 0);
@@ -128,19 +131,21 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         uint32_t k[32], i[32], seg_bits[32];
         uint16_t entry[32];
         unsigned long long rec[32];
+        uint32_t mid[32];
         for (int l = 0; l < 32; ++l) {
             const long long sub = (long long)chunk_first - kOverlapSubs + l;
             active[l] = sub >= 0 && sub < (long long)N;
             head[l] = false;
             entry[l] = 0;
             rec[l] = 0;
+            mid[l] = 0;
             if (!active[l]) continue;
             k[l] = find_segment(sp.segs.data(), g.num_segments, (uint32_t)sub);
             const SegDesc& seg = sp.segs[k[l]];
             i[l] = (uint32_t)sub - seg.sub_off;
             head[l] = i[l] == 0;
             seg_bits[l] = seg.nbytes * 8u;
-            rec[l] = decode_sub(mem_of(seg), seg_bits[l], i[l], 0);
+            rec[l] = decode_sub(mem_of(seg), seg_bits[l], i[l], 0, &mid[l]);
         }
         int chunk_passes = 1;
         auto iterate = [&](int frozen) {
@@ -162,7 +167,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                             ++diag[(d & 0x1f) ? 0 : (d & 0x7e00) ? 1 : 2]; // o differs / z differs / c only
                         }
                         entry[l] = want[l];
-                        rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l]);
+                        rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l], &mid[l]);
                     }
             }
             if (rounds >= 100 && getenv("EMUL_DIAG")) {
@@ -183,7 +188,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
             if ((uint16_t)(left & 0xffffu) != entry[kOverlapSubs]) {
                 const int l = kOverlapSubs;
                 entry[l] = (uint16_t)(left & 0xffffu);
-                rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l]);
+                rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l], &mid[l]);
                 ++relinked;
                 iterate(kOverlapSubs);
                 mailbox[chunk] = 0x80000000u | entry_x(rec[last_lane]);
@@ -193,8 +198,9 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         for (int l = kOverlapSubs; l < 32; ++l)
             if (active[l]) {
                 const uint32_t sub = chunk_first - kOverlapSubs + l;
-                entries[sub] = pack_entry((uint16_t)(entry[l] | (head[l] ? kStateHead : 0)),
-                                          entry_x(rec[l]), entry_n(rec[l]));
+                rec_lo(sub) = pack_entry((uint16_t)(entry[l] | (head[l] ? kStateHead : 0)),
+                                         entry_x(rec[l]), entry_n(rec[l]));
+                rec_hi(sub) = mid[l];
                 seg_idx[sub] = k[l];
             }
     }
@@ -209,14 +215,14 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     // huff_link: verify chunk boundaries, sequential fallback, segmented exclusive scan
     if (stats[7] == 12345) // test hook: corrupt some records to exercise the fallback
         for (uint32_t j = 3; j < N; j += 7)
-            if (!(entry_g(entries[j]) & kStateHead)) entries[j] = pack_entry(entry_g(entries[j]) ^ 0x21, entry_x(entries[j]) ^ 0x40, 5);
+            if (!(entry_g(rec_lo(j)) & kStateHead)) rec_lo(j) = pack_entry(entry_g(rec_lo(j)) ^ 0x21, entry_x(rec_lo(j)) ^ 0x40, 5);
     uint32_t stride = stats[7] == 12345 ? 1 : kChunkSubs;
     int slow_fix = 0, link_rounds = 0;
     for (;;) {
         std::vector<unsigned long long> snap(entries); // every thread decides from a snapshot
         uint32_t bad = 0;
         for (uint32_t j = stride; j < N; j += stride)
-            if (!boundary_ok(snap[j - 1], snap[j])) {
+            if (!boundary_ok(snap[2 * (size_t)j - 2], snap[2 * (size_t)j])) {
                 ++bad;
                 const SegDesc& seg = sp.segs[seg_idx[j]];
                 slow_fix += (int)relink_from(mem_of(seg), seg, entries.data(), j);
@@ -228,22 +234,27 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     stats[2] = slow_fix;
     stats[4] = link_rounds;
     for (uint32_t j = 1; j < N; ++j)
-        if (!boundary_ok(entries[j - 1], entries[j])) return -7; // inconsistent chain
+        if (!boundary_ok(rec_lo(j - 1), rec_lo(j))) return -7; // inconsistent chain
     uint32_t acc = 0;
     for (uint32_t j = 0; j < N; ++j) {
-        if (entry_g(entries[j]) & kStateHead) acc = 0;
+        if (entry_g(rec_lo(j)) & kStateHead) acc = 0;
         qpos[j] = acc;
-        acc += entry_n(entries[j]);
+        acc += entry_n(rec_lo(j));
     }
 
     // huff_write
     long_codes = 0;
-    memset(coef, 0, need * sizeof(int16_t));
+    std::vector<int16_t> zz(need, 0); // DU-major, zig-zag order inside a DU (the device layout)
     std::vector<int16_t> dc((size_t)g.total_mcus * g.dus_per_mcu, 0);
     for (uint32_t j = 0; j < N; ++j) {
         const SegDesc& seg = sp.segs[seg_idx[j]];
-        write_sub(mem_of(seg), g, seg, seg_idx[j], j - seg.sub_off,
-                  (uint16_t)(entry_g(entries[j]) & kStateMask), qpos[j], coef, dc.data());
+        uint32_t first_du, q_limit;
+        if (!segment_extent(g, seg_idx[j], first_du, q_limit)) continue;
+        HostMem m = mem_of(seg);
+        m.coef_ = zz.data() + (size_t)first_du * 64;
+        m.dc_ = dc.data() + first_du;
+        for (uint32_t h = 0; h < 2; ++h) // the two threads of a subsequence
+            write_half(m, seg, j - seg.sub_off, h, rec_lo(j), (uint32_t)rec_hi(j), qpos[j], q_limit);
     }
     if (getenv("EMUL_DIAG")) fprintf(stderr, "lut bits %d: long codes in the write pass %ld\n", kLutBits, long_codes);
     // DC: the contract of dc_tile_sums + dc_apply
@@ -255,10 +266,14 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                 if (g.slot_comp[s] == a) {
                     const size_t du = (size_t)m * g.dus_per_mcu + s;
                     pred += dc[du];
-                    coef[du * 64] = (int16_t)pred;
+                    zz[du * 64] = (int16_t)pred;
                 }
         }
     }
+    // the oracle's stream layout is raster order inside a DU: un-zig-zag (IDCT / transpose do
+    // this on the device)
+    for (size_t du = 0; du < need / 64; ++du)
+        for (int z = 0; z < 64; ++z) coef[du * 64 + kNat[z]] = zz[du * 64 + z];
     return 0;
 }
 
