@@ -57,3 +57,28 @@ def pillow_jpeg(w, h, seed, mode="YCbCr", subsampling=2, quality=85, restart_blo
         kw["restart_marker_blocks"] = restart_blocks
     im.save(buf, "JPEG", **kw)
     return buf.getvalue()
+
+
+# Named inputs of the golden fixtures (tests/golden/reference_digests.json, tools/make_golden.py).
+NAMED = {
+    "IMG_6510": lambda: img6510(),
+    "stb_4032x3024_s6510_q90": lambda: synth(4032, 3024, 6510, 90),
+    "stb_3008x2000_s1_q90": lambda: synth(3008, 2000, 1, 90),
+    "stb_3008x2000_s2_q95": lambda: synth(3008, 2000, 2, 95),
+    "stb_3001x1999_s3_q90": lambda: synth(3001, 1999, 3, 90),
+    "stb_1920x1080_s1_q90": lambda: synth(1920, 1080, 1, 90),
+    "pil_422_3008x2000": lambda: pillow_jpeg(w=3008, h=2000, seed=12, mode="YCbCr", subsampling=1),
+    "pil_444_1504x1000": lambda: pillow_jpeg(w=1504, h=1000, seed=11, mode="YCbCr", subsampling=0),
+    "pil_gray_3008x2000": lambda: pillow_jpeg(w=3008, h=2000, seed=14, mode="L"),
+    "pil_420_rst63_1008x752": lambda: pillow_jpeg(w=1008, h=752, seed=17, mode="YCbCr",
+                                                   subsampling=2, restart_blocks=63),
+    "pil_420_rst1_333x211": lambda: pillow_jpeg(w=333, h=211, seed=18, mode="YCbCr",
+                                                 subsampling=2, restart_blocks=1),
+    "pil_420_opt_1280x720": lambda: pillow_jpeg(w=1280, h=720, seed=19, mode="YCbCr",
+                                                 subsampling=2, optimize=True),
+}
+
+
+def read_named(name):
+    fn = NAMED.get(name)
+    return fn() if fn else None

@@ -126,9 +126,9 @@ def test_oracle_matches_reference_golden_digests():
         gold = json.load(f)
     checked = 0
     for name, entry in gold.items():
-        data = inputs.read_named(name) if hasattr(inputs, "read_named") else None
-        if data is None:
-            continue
+        data = inputs.read_named(name)
+        if data is None or hashlib.sha256(data).hexdigest() != entry["input_sha256"]:
+            continue  # input not reproducible byte-for-byte here (other encoder build)
         r = ob.decode(data)
         assert r["status"] == 0
         assert _digest(r["pixels"]) == entry["pixels_sha256"], name
