@@ -67,6 +67,38 @@ enum jpeggpu_status jpeggpu_b200_get_kernel_times(
     int launches[JPEGGPU_B200_MAX_KERNELS]);
 const char* jpeggpu_b200_kernel_name(int id);
 
+/* ---- batches (BASELINE config 5: many independent images on one GPU) -------------------------
+ * The reference has no batch entry point; its callers loop over the per-image protocol
+ * (benchmark/benchmark_jpeggpu.hpp:69-89).  This helper runs exactly that loop natively: one
+ * host thread, one decoder and one caller-owned scratch buffer per caller-owned stream ("lane");
+ * lane l decodes items l, l + num_lanes, l + 2 num_lanes, ...  Host parsing of one item overlaps
+ * the kernels of the previous ones; nothing synchronises with the device except a lane that runs
+ * more than four images ahead.  The call returns when every item has been ENQUEUED; the caller
+ * synchronises its streams.  All lanes use the device that is current in the calling thread. */
+struct jpeggpu_b200_batch_item {
+    const uint8_t* data;          /* in: JPEG bytes (pinned host memory recommended) */
+    size_t size;                  /* in */
+    struct jpeggpu_img img;       /* in: device planes; pitch[c] >= sizes_x[c] */
+    struct jpeggpu_img_info info; /* out */
+    enum jpeggpu_status status;   /* out: first failing step's status, or JPEGGPU_SUCCESS */
+};
+
+/* Returns JPEGGPU_SUCCESS if every item succeeded, else the status of the first failed item
+ * (remaining items are still attempted).  An item whose scratch requirement exceeds
+ * tmp_size[lane] fails with JPEGGPU_INTERNAL_ERROR. */
+enum jpeggpu_status jpeggpu_b200_decode_batch(
+    struct jpeggpu_b200_batch_item* items,
+    int num_items,
+    const cudaStream_t* streams,
+    void* const* d_tmp,
+    const size_t* tmp_size,
+    int num_lanes);
+
+/* Host-only: parse every item with `num_threads` threads and fill info / status (lets a caller
+ * size its output planes); *max_tmp_size (optional) receives the largest scratch requirement. */
+enum jpeggpu_status jpeggpu_b200_parse_batch(
+    struct jpeggpu_b200_batch_item* items, int num_items, int num_threads, size_t* max_tmp_size);
+
 #ifdef __cplusplus
 }
 #endif

@@ -32,6 +32,7 @@ API_SYMBOLS = [
     "jpeggpu_b200_get_coefficient_size", "jpeggpu_b200_decode_coefficients",
     "jpeggpu_b200_get_scan_stats", "jpeggpu_b200_get_transfer_size",
     "jpeggpu_b200_set_profiling", "jpeggpu_b200_get_kernel_times", "jpeggpu_b200_kernel_name",
+    "jpeggpu_b200_decode_batch", "jpeggpu_b200_parse_batch",
 ]
 
 MAX_KERNELS = 16
@@ -58,6 +59,12 @@ class ScanStats(C.Structure):
                 ("off_control", C.c_size_t), ("off_destuffed", C.c_size_t),
                 ("off_coefficients", C.c_size_t), ("off_sync_records", C.c_size_t),
                 ("off_slot_prefix", C.c_size_t)]
+
+
+class BatchItem(C.Structure):
+    """struct jpeggpu_b200_batch_item (include/jpeggpu_b200.h)"""
+    _fields_ = [("data", C.c_void_p), ("size", C.c_size_t), ("img", Img), ("info", ImgInfo),
+                ("status", C.c_int)]
 
 
 class JpegGpuError(RuntimeError):
@@ -110,6 +117,10 @@ def load_library(path=None):
                                                 C.POINTER(C.c_int * MAX_KERNELS)]
     L.jpeggpu_b200_kernel_name.restype = C.c_char_p
     L.jpeggpu_b200_kernel_name.argtypes = [C.c_int]
+    L.jpeggpu_b200_decode_batch.argtypes = [C.POINTER(BatchItem), C.c_int, C.POINTER(C.c_void_p),
+                                            C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int]
+    L.jpeggpu_b200_parse_batch.argtypes = [C.POINTER(BatchItem), C.c_int, C.c_int,
+                                           C.POINTER(C.c_size_t)]
     if path is None:
         _lib = L
     return L

@@ -49,9 +49,22 @@ struct jpeggpu_decoder {
     size_t upload_bytes = 0; // staging block size
     size_t total_bytes = 0;  // scratch requirement
     size_t transfer_bytes = 0;
-    uint8_t* staging = nullptr;
-    size_t staging_cap = 0;
-    bool staging_pinned = false;
+    // Ring of pinned staging blocks.  parse_header fills a block, transfer enqueues its copy and
+    // records an event behind it; the block is rewritten only after that event has completed,
+    // so a caller may run several images ahead of the device with ONE decoder object (the
+    // reference rewrites its pinned tables in place: SURVEY 8(b) "one image in flight").
+    static constexpr int kStagingSlots = 4;
+    struct StagingSlot {
+        uint8_t* ptr = nullptr;
+        size_t cap = 0;
+        bool pinned = false;
+        bool in_flight = false;
+        bool have_event = false;
+        int event_device = -1;
+        cudaEvent_t copied{};
+    } slots[kStagingSlots];
+    int cur_slot = 0;
+    uint8_t* staging = nullptr; // == slots[cur_slot].ptr
     struct LutCache {
         std::vector<uint8_t> key;
         std::vector<uint32_t> pool;
@@ -63,37 +76,74 @@ struct jpeggpu_decoder {
 
     ~jpeggpu_decoder()
     {
-        release_staging();
+        for (StagingSlot& sl : slots) {
+            if (sl.have_event) cudaEventDestroy(sl.copied);
+            release_slot(sl);
+        }
         if (timer.created)
             for (int i = 0; i < StageTimer::kMaxMarks; ++i) cudaEventDestroy(timer.ev[i]);
     }
 
-    void release_staging()
+    static void release_slot(StagingSlot& sl)
     {
-        if (staging) {
-            if (staging_pinned) cudaFreeHost(staging);
-            else free(staging);
+        if (sl.ptr) {
+            if (sl.pinned) cudaFreeHost(sl.ptr);
+            else free(sl.ptr);
         }
-        staging = nullptr;
-        staging_cap = 0;
+        sl.ptr = nullptr;
+        sl.cap = 0;
     }
 
+    // Pick the staging block for a freshly parsed image and make it at least `bytes` large.
     jpeggpu_status reserve_staging(size_t bytes)
     {
-        if (bytes <= staging_cap) return JPEGGPU_SUCCESS;
-        release_staging();
-        const size_t cap = align256(bytes + bytes / 2 + 65536);
-        void* p = nullptr;
-        if (cudaHostAlloc(&p, cap, cudaHostAllocDefault) == cudaSuccess) {
-            staging_pinned = true;
-        } else {
-            (void)cudaGetLastError(); // no device (CPU-only parse): pageable staging still works
-            p = malloc(cap);
-            staging_pinned = false;
-            if (!p) return JPEGGPU_OUT_OF_HOST_MEMORY;
+        if (slots[cur_slot].in_flight) cur_slot = (cur_slot + 1) % kStagingSlots;
+        StagingSlot& sl = slots[cur_slot];
+        if (sl.in_flight) { // the caller is kStagingSlots images ahead of the device: wait
+            if (cudaEventSynchronize(sl.copied) != cudaSuccess) {
+                (void)cudaGetLastError();
+                return JPEGGPU_INTERNAL_ERROR;
+            }
+            sl.in_flight = false;
         }
-        staging = static_cast<uint8_t*>(p);
-        staging_cap = cap;
+        if (bytes > sl.cap) {
+            release_slot(sl);
+            const size_t cap = align256(bytes + bytes / 2 + 65536);
+            void* p = nullptr;
+            if (cudaHostAlloc(&p, cap, cudaHostAllocDefault) == cudaSuccess) {
+                sl.pinned = true;
+            } else {
+                (void)cudaGetLastError(); // no device (CPU-only parse): pageable staging still works
+                p = malloc(cap);
+                sl.pinned = false;
+                if (!p) return JPEGGPU_OUT_OF_HOST_MEMORY;
+            }
+            sl.ptr = static_cast<uint8_t*>(p);
+            sl.cap = cap;
+        }
+        staging = sl.ptr;
+        return JPEGGPU_SUCCESS;
+    }
+
+    // Called by transfer after the copy out of the current staging block has been enqueued.
+    jpeggpu_status mark_staging_in_flight(cudaStream_t stream)
+    {
+        StagingSlot& sl = slots[cur_slot];
+        if (!sl.pinned) return JPEGGPU_SUCCESS; // pageable source: the copy call already staged it
+        int dev = -1;
+        if (cudaGetDevice(&dev) != cudaSuccess) return JPEGGPU_INTERNAL_ERROR;
+        if (sl.have_event && sl.event_device != dev) {
+            cudaEventDestroy(sl.copied);
+            sl.have_event = false;
+        }
+        if (!sl.have_event) {
+            if (cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming) != cudaSuccess)
+                return JPEGGPU_INTERNAL_ERROR;
+            sl.have_event = true;
+            sl.event_device = dev;
+        }
+        if (cudaEventRecord(sl.copied, stream) != cudaSuccess) return JPEGGPU_INTERNAL_ERROR;
+        sl.in_flight = true;
         return JPEGGPU_SUCCESS;
     }
 
@@ -367,6 +417,7 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
     uint8_t* base = static_cast<uint8_t*>(d_tmp);
     JB2_CUDA(cudaMemcpyAsync(base, decoder->staging, decoder->upload_bytes,
                              cudaMemcpyHostToDevice, stream));
+    if (decoder->mark_staging_in_flight(stream) != JPEGGPU_SUCCESS) return JPEGGPU_INTERNAL_ERROR;
     for (int s = 0; s < decoder->plan.num_scans; ++s) {
         const ScanPlan& sp = decoder->plan.scans[s];
         if (sp.geom.scan_bytes == 0) continue;

@@ -90,3 +90,21 @@ def test_img6510_emulated():
     assert np.array_equal(coef, ref["stream"][0])
     st, out = eb.parse(data)
     assert out[5] == 189 and out[7] == 2907282
+
+
+@pytest.mark.parametrize("case", [
+    dict(w=1200, h=900, seed=21, mode="YCbCr", subsampling=2),
+    dict(w=1200, h=900, seed=22, mode="YCbCr", subsampling=2, restart_blocks=75),
+    dict(w=800, h=600, seed=23, mode="L"),
+], ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items()))
+def test_link_repairs_damaged_records(case):
+    """huff_link's fallback (relink_from + re-verification): the emulator damages sync records
+    after the sync pass; the repaired decode must still equal the oracle and must have gone
+    through the slow path."""
+    data = inputs.pillow_jpeg(**case)
+    ref = ob.decode(data)
+    assert ref["status"] == 0
+    st, coef, stats, _ = eb.decode_scan(data, 0, ref["stream"][0].size, corrupt_records=True)
+    assert st == 0
+    assert stats[2] > 0, "the repair path did not run"
+    assert np.array_equal(coef, ref["stream"][0])
