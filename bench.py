@@ -144,9 +144,8 @@ def stage_table(kt_avg_ms, st):
         "huff_sync": Sd + 8 * N + 2 * Cc + 2 * D,   # reads the scan, zero-fills coefficients + DC array
         "huff_link": 8 * N + 4 * N,
         "huff_write": Sd + 12 * N + 2 * D,          # + the scattered non-zero coefficients
-        "dc_tile_sums": 2 * D,
-        "dc_apply": 4 * D,
-        "idct_kernel": 2 * Cc + P,
+        "dc_scan": 4 * D,                           # compact DC array, in place
+        "idct_kernel": 2 * Cc + 2 * D + P,
     }
     rows = {}
     for name, ms in kt_avg_ms.items():

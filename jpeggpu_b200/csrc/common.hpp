@@ -173,7 +173,10 @@ struct Control {
     uint32_t sync_iter_ns;
     uint32_t write_tiles_max; // most tiles any warp of huff_write assembled
     uint32_t write_tiles;     // tiles assembled by all warps
-    uint32_t pad[4];
+    uint32_t dc_ticket;       // dc_scan: tiles are numbered in the order their CTAs start
+    uint32_t write_ticket;    // huff_write: likewise
+    uint32_t sync_done;       // huff_sync CTAs that have finished (the last one verifies)
+    uint32_t pad[1];
 };
 
 // zig-zag -> natural order (T.81 Figure A.6; same table as src/defs.hpp:94-102)

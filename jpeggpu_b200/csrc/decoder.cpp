@@ -14,6 +14,8 @@
 #include <jpeggpu/jpeggpu.h>
 #include <jpeggpu_b200.h>
 
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -34,7 +36,7 @@ struct ScanLayout {
     size_t off_ctrl = 0, off_destuffed = 0, off_coef = 0, off_dc = 0;
     size_t off_entries = 0, off_qpos = 0, off_seg_idx = 0, off_dc_agg = 0;
     size_t coef_bytes = 0, dc_bytes = 0;
-    uint32_t num_chunks = 0;
+    uint32_t num_chunks = 0, dc_tiles = 0, flag_words = 0, write_ctas = 0;
     uint32_t destuffed_bytes = 0;
     uint32_t num_dus = 0;
 };
@@ -211,8 +213,11 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         L.num_dus = (uint32_t)g.total_mcus * (uint32_t)g.dus_per_mcu;
         L.destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
         L.num_chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
-        L.off_ctrl = o; // control block and sync mailboxes are cleared as one range
-        o += align256(sizeof(Control) + (size_t)L.num_chunks * 4);
+        L.off_ctrl = o; // control block, sync mailboxes and DC flags are cleared as one range
+        L.dc_tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
+        L.flag_words = (L.num_chunks + L.dc_tiles + 1u) & ~1u; // keeps the 64-bit words aligned
+        L.write_ctas = g.num_subs / 16u + 1u;                  // huff_write runs >= 16 subsequences per CTA
+        o += align256(sizeof(Control) + ((size_t)L.flag_words + 2u * L.write_ctas) * 4);
         L.off_destuffed = o;
         o += align256((size_t)g.num_subs * kSubBytes + 64);
         L.off_coef = o;
@@ -262,6 +267,9 @@ ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
     b.ctrl = reinterpret_cast<Control*>(base + L.off_ctrl);
     b.chunk_state = reinterpret_cast<uint32_t*>(base + L.off_ctrl + sizeof(Control));
     b.num_chunks = L.num_chunks;
+    b.dc_flags = b.chunk_state + L.num_chunks;
+    b.write_agg = reinterpret_cast<unsigned long long*>(b.chunk_state + L.flag_words);
+    b.clear_words = (uint32_t)(sizeof(Control) / 4) + L.flag_words + 2u * L.write_ctas;
     b.destuffed = reinterpret_cast<uint32_t*>(base + L.off_destuffed);
     b.coef = reinterpret_cast<int16_t*>(base + L.off_coef);
     b.coef_bytes = L.coef_bytes;
@@ -300,6 +308,8 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
             JB2_CUDA(cudaMemsetAsync(b.coef, 0, b.coef_bytes, stream));
             JB2_CUDA(cudaMemsetAsync(b.dc, 0, b.dc_bytes, stream));
         }
+        if (g.scan_bytes == 0) // destuff (which clears the control range) will not run either
+            JB2_CUDA(cudaMemsetAsync(b.ctrl, 0, (size_t)b.clear_words * 4, stream));
         JB2_CUDA(launch_destuff(g, b, stream, &timer));
         JB2_CUDA(launch_huffman(g, b, stream, &timer));
         JB2_CUDA(launch_dc(g, b, stream, &timer));
@@ -377,10 +387,22 @@ enum jpeggpu_status jpeggpu_decoder_parse_header(
 {
     if (!decoder || !img_info || !data) return JPEGGPU_INVALID_ARGUMENT;
     decoder->parsed = false;
+#ifdef JB2_PARSE_TIMING
+    const auto t0 = std::chrono::steady_clock::now();
+#endif
     jpeggpu_status st = parse_jpeg(data, size, decoder->plan, decoder->log);
     if (st != JPEGGPU_SUCCESS) return st;
+#ifdef JB2_PARSE_TIMING
+    const auto t1 = std::chrono::steady_clock::now();
+#endif
     try {
         st = decoder->plan_scratch();
+#ifdef JB2_PARSE_TIMING
+        const auto t2 = std::chrono::steady_clock::now();
+        fprintf(stderr, "parse_jpeg %.1f us plan_scratch %.1f us\n",
+                std::chrono::duration<double, std::micro>(t1 - t0).count(),
+                std::chrono::duration<double, std::micro>(t2 - t1).count());
+#endif
     } catch (const std::bad_alloc&) {
         st = JPEGGPU_OUT_OF_HOST_MEMORY;
     }
@@ -562,7 +584,7 @@ enum jpeggpu_status jpeggpu_b200_get_kernel_times(
 const char* jpeggpu_b200_kernel_name(int id)
 {
     static const char* names[kIdCount] = {
-        "destuff_kernel", "huff_sync", "huff_link", "huff_write", "dc_tile_sums", "dc_apply",
+        "destuff_kernel", "huff_sync", "huff_write", "dc_scan",
         "idct_kernel", "transpose_kernel"};
     return id >= 0 && id < kIdCount ? names[id] : "";
 }

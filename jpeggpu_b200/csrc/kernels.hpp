@@ -25,10 +25,14 @@ struct ScanBufs {
     Control* ctrl;             // zeroed by destuff
     uint32_t* chunk_state;     // zeroed by destuff: one mailbox per sync warp
     uint32_t num_chunks;
+    uint32_t* dc_flags;        // zeroed by destuff: "aggregate published" flag per DC tile
+    unsigned long long* write_agg; // zeroed by destuff: slot aggregate per huff_write CTA
+    uint32_t clear_words;      // Control + mailboxes + DC flags + write aggregates, contiguous
     uint32_t* destuffed;       // big-endian words, segment k at sub_off * kSubWords
     int16_t* coef;             // zeroed by huff_sync; DU-major coded order, 64 natural-order int16 per DU
     size_t coef_bytes;         // multiple of 16
-    int16_t* dc;               // zeroed by huff_sync; one DC difference per DU, coded order
+    int16_t* dc;               // zeroed by huff_sync; one DC value per DU, coded order: differences
+                               // after huff_write, absolute values after dc_scan
     size_t dc_bytes;           // multiple of 16
     SubEntry* entries;         // N
     uint32_t* qpos;            // N: first slot (segment relative) of every subsequence
@@ -39,7 +43,7 @@ struct ScanBufs {
 // Optional per-kernel timing (jpeggpu_b200_set_profiling): an event is recorded on the launching
 // stream before every kernel and one after the last; off by default and absent from timed runs.
 enum KernelId {
-    kIdDestuff = 0, kIdSync, kIdLink, kIdWrite, kIdDcSums, kIdDcApply, kIdIdct, kIdTranspose,
+    kIdDestuff = 0, kIdSync, kIdWrite, kIdDcScan, kIdIdct, kIdTranspose,
     kIdCount
 };
 

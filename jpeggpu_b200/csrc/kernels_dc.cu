@@ -6,11 +6,12 @@
 // into a tile of kDcTile MCUs is pure arithmetic over per-tile aggregates:
 // Input: the compact array of DC differences huff_write produced (one int16 per DU, coded
 // order: contiguous, unlike the reference's 128-byte-strided permutation iterator); output: the
-// absolute DC value stored into slot 0 of every DU of the coefficient buffer.
-//   dc_tile_sums : agg[t][a] = sum of component a's DC differences over the MCUs of tile t that
-//                  follow the last restart boundary inside t (whole tile if none)
-//   dc_apply     : carry = sum of agg over the tiles back to the one holding the segment start,
-//                  then a segmented block scan and the in-place write of absolute DC values.
+// absolute DC values in the same array.
+//   agg[t][a] = sum of component a's DC differences over the MCUs of tile t that follow the last
+//               restart boundary inside t (whole tile if none)
+//   carry     = sum of agg over the tiles back to the one holding the segment start; then the
+//               segmented block scan result is written back IN PLACE into the compact array
+//               (the IDCT / transpose pick the DC from there instead of coefficient slot 0).
 // Arithmetic is int32 truncated to int16 on store == the reference's int16 wrap-around sums.
 // Algorithmic bytes: 4 per DU (read + write one int16); touched sectors are 32 B each.
 #include "kernels.hpp"
@@ -91,45 +92,60 @@ __device__ __forceinline__ Dc4 block_segmented_scan(Dc4 val, bool head, Dc4* war
     return val;
 }
 
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// One launch: every CTA scans its tile, publishes the tile aggregate (sum after the tile's last
+// restart boundary) and then sums the aggregates of the tiles between the start of its restart
+// segment and itself.  Aggregates do not depend on other tiles, so there is no chain to wait
+// on: a CTA only waits for tiles that started before it (tile numbers are handed out by an
+// atomic ticket, so "earlier tile" == "already running or finished": no deadlock).
 __global__ void __launch_bounds__(kDcTile)
-dc_tile_sums(const ScanGeom g, const int16_t* __restrict__ dc, int* __restrict__ agg)
+dc_scan(const ScanGeom g, int16_t* __restrict__ dc, int* __restrict__ agg,
+        uint32_t* __restrict__ flags, uint32_t* __restrict__ ticket)
 {
     __shared__ Dc4 warp_val[kDcTile / 32];
     __shared__ uint32_t warp_flag[kDcTile / 32];
-    const uint32_t mcu = blockIdx.x * kDcTile + threadIdx.x;
+    __shared__ Dc4 s_red[kDcTile / 32];
+    __shared__ uint32_t s_tile;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t tile_mcu0 = tile * kDcTile;
+    const uint32_t ri = (uint32_t)g.restart_interval;
+    const uint32_t mcu = tile_mcu0 + threadIdx.x;
     const bool valid = mcu < (uint32_t)g.total_mcus;
     int diff[kMaxDuPerMcu];
     Dc4 tot;
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) tot.v[a] = 0;
     if (valid) load_mcu(g, dc, mcu, diff, tot);
-    const bool head = valid && (mcu % (uint32_t)g.restart_interval) == 0;
+    const bool head = valid && (mcu % ri) == 0;
     Dc4 tail;
-    block_segmented_scan(tot, head, warp_val, warp_flag, tail);
+    const Dc4 inc = block_segmented_scan(tot, head, warp_val, warp_flag, tail);
     if (threadIdx.x == 0) {
 #pragma unroll
-        for (int a = 0; a < kMaxComp; ++a) agg[blockIdx.x * kMaxComp + a] = tail.v[a];
+        for (int a = 0; a < kMaxComp; ++a) agg[tile * kMaxComp + a] = tail.v[a];
+        st_release(flags + tile, 1u);
     }
-}
-
-__global__ void __launch_bounds__(kDcTile)
-dc_apply(const ScanGeom g, const int16_t* __restrict__ dc, int16_t* __restrict__ coef,
-         const int* __restrict__ agg)
-{
-    __shared__ Dc4 warp_val[kDcTile / 32];
-    __shared__ uint32_t warp_flag[kDcTile / 32];
-    __shared__ Dc4 s_red[kDcTile / 32];
-    const uint32_t tile_mcu0 = blockIdx.x * kDcTile;
-    const uint32_t ri = (uint32_t)g.restart_interval;
-    // tiles [first_tile, blockIdx.x) carry into this one
+    // tiles [first_tile, tile) carry into this one
     const uint32_t seg_start = tile_mcu0 / ri * ri;
     const uint32_t first_tile = seg_start / kDcTile;
     Dc4 carry;
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) carry.v[a] = 0;
-    for (uint32_t t = first_tile + threadIdx.x; t < blockIdx.x; t += kDcTile) {
+    for (uint32_t t = first_tile + threadIdx.x; t < tile; t += kDcTile) {
+        while (ld_acquire(flags + t) == 0u) __nanosleep(40);
 #pragma unroll
-        for (int a = 0; a < kMaxComp; ++a) carry.v[a] += agg[t * kMaxComp + a];
+        for (int a = 0; a < kMaxComp; ++a) carry.v[a] += __ldcg(agg + t * kMaxComp + a);
     }
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) {
@@ -143,17 +159,6 @@ dc_apply(const ScanGeom g, const int16_t* __restrict__ dc, int16_t* __restrict__
         carry.v[a] = 0;
         for (int w = 0; w < kDcTile / 32; ++w) carry.v[a] += s_red[w].v[a];
     }
-
-    const uint32_t mcu = tile_mcu0 + threadIdx.x;
-    const bool valid = mcu < (uint32_t)g.total_mcus;
-    int diff[kMaxDuPerMcu];
-    Dc4 tot;
-#pragma unroll
-    for (int a = 0; a < kMaxComp; ++a) tot.v[a] = 0;
-    if (valid) load_mcu(g, dc, mcu, diff, tot);
-    const bool head = valid && (mcu % ri) == 0;
-    Dc4 tail;
-    const Dc4 inc = block_segmented_scan(tot, head, warp_val, warp_flag, tail);
     if (!valid) return;
     // the tile carry applies only while no restart boundary has been seen inside the tile
     const bool fresh = (mcu / ri * ri) >= tile_mcu0;
@@ -161,7 +166,7 @@ dc_apply(const ScanGeom g, const int16_t* __restrict__ dc, int16_t* __restrict__
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a)
         pred.v[a] = inc.v[a] - tot.v[a] + (fresh ? 0 : carry.v[a]);
-    int16_t* base = coef + (size_t)mcu * g.dus_per_mcu * 64;
+    int16_t* base = dc + (size_t)mcu * g.dus_per_mcu;
 #pragma unroll
     for (int s = 0; s < kMaxDuPerMcu; ++s) {
         if (s < g.dus_per_mcu) {
@@ -173,7 +178,7 @@ dc_apply(const ScanGeom g, const int16_t* __restrict__ dc, int16_t* __restrict__
                     pred.v[k] += diff[s];
                     value = pred.v[k];
                 }
-            base[s * 64] = (int16_t)value;
+            base[s] = (int16_t)value;
         }
     }
 }
@@ -185,14 +190,11 @@ cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream,
     if (g.total_mcus == 0) return cudaSuccess;
     static std::atomic<unsigned long long> configured{0};
     if (first_use_on_device(configured)) {
-        prefer_max_shared(dc_tile_sums);
-        prefer_max_shared(dc_apply);
+        prefer_max_shared(dc_scan);
     }
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
-    tm->mark(stream, kIdDcSums);
-    dc_tile_sums<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.dc_agg);
-    tm->mark(stream, kIdDcApply);
-    dc_apply<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.coef, b.dc_agg);
+    tm->mark(stream, kIdDcScan);
+    dc_scan<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.dc_agg, b.dc_flags, &b.ctrl->dc_ticket);
     return cudaGetLastError();
 }
 

@@ -136,8 +136,8 @@ cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     static std::atomic<unsigned long long> configured{0};
     if (first_use_on_device(configured)) prefer_max_shared(destuff_kernel);
     const uint32_t tiles = (g.scan_bytes + kDestuffTile - 1) / kDestuffTile;
-    // the control block and the mailboxes are contiguous (planner): one clear range
-    const uint32_t clear_words = (uint32_t)(sizeof(Control) / 4) + b.num_chunks;
+    // the control block, the mailboxes and the DC flags are contiguous (planner): one clear range
+    const uint32_t clear_words = b.clear_words;
     tm->mark(stream, kIdDestuff);
     destuff_kernel<<<tiles, kDestuffThreads, 0, stream>>>(
         b.scan_bytes, g.scan_bytes, b.tiles, b.segs, g.num_segments,

@@ -18,19 +18,17 @@
 //               corrected state (rare).  One 8-byte record {entry, exit, slots} per subsequence.
 //               The kernel also zero-fills the coefficient buffer (its load/store units are idle
 //               while the warps decode).
-//   huff_link   one CTA: verifies every chunk boundary (exit of the left record == entry of the
-//               right one).  If all agree, every record is exact by induction from the segment
-//               starts.  Otherwise it repairs sequentially (degenerates to a serial decode on
-//               adversarial streams, like the reference's TODO at src/decode_huffman.cu:475).
-//               Then a segmented exclusive scan of the slot counts gives the first output slot of
-//               every subsequence (replaces the CUB ExclusiveScanByKey + assign_sinfo_n,
-//               src/decode_huffman.cu:827-869).
+//               The CTA that finishes last verifies every chunk boundary (exit of the left
+//               record == entry of the right one); if all agree, every record is exact by
+//               induction from the segment starts, otherwise it repairs sequentially.
 //   huff_write  decode from the verified entry states, two threads per subsequence (the record
-//               holds the state at its middle).  A warp assembles the data units that lie
-//               entirely inside its slots in a shared-memory buffer and flushes them with
-//               coalesced 16-byte stores; data units shared with a neighbouring warp are scattered
-//               into the zero-filled global buffer.  Coefficients keep their zig-zag index (the
-//               IDCT un-zig-zags in registers); DC differences also go to a compact per-DU array
+//               holds the state at its middle).  The first output slot of every subsequence is
+//               a segmented prefix sum of the records' slot counts, computed inside this kernel
+//               with a look-back over per-CTA aggregates (replaces the reference's CUB
+//               ExclusiveScanByKey + assign_sinfo_n, src/decode_huffman.cu:827-869).  Non-zero
+//               coefficients are collected in per-thread lists in shared memory and scattered
+//               afterwards into the zero-filled buffer, zig-zag index kept (the IDCT un-zig-zags
+//               in registers); DC differences go to a compact per-DU array
 //               (src/decode_huffman.cu:627-682).
 #include "huff_threads.hpp"
 #include "kernels.hpp"
@@ -44,17 +42,12 @@ constexpr int kSyncWinSubs = kSyncUseful + kOverlapSubs;        // subsequences 
 constexpr int kWinMargin = 4;                                   // words past the last subsequence
 constexpr int kSyncWinWords = kSyncWinSubs * kSubWords + kWinMargin;
 constexpr int kWriteThreads = 320;  // at most; two threads per subsequence
-constexpr int kTileDus = 32;        // data units a warp assembles at a time
 // non-zero coefficients one thread can meet in half a subsequence: each takes >= 2 bits, plus the
 // symbol that straddles the end
 constexpr int kListCap = kSubBits / 4 + 2;
 constexpr int kListStride = kListCap | 1;                          // words between the lanes' lists
 constexpr int kWarpListBytes = (32 * kListStride * 4 + 15) & ~15;
-#if defined(JB2_WRITE_TILES)
-constexpr int kWarpSmem = kWarpListBytes + kTileDus * 128;         // lists + tile of one warp
-#else
-constexpr int kWarpSmem = kWarpListBytes;
-#endif
+constexpr int kWarpSmem = kWarpListBytes;                          // shared memory per write warp
 static_assert(kSubBytes <= 128, "slot offsets inside half a subsequence must fit 16 bits");
 static_assert(kSyncWinWords % 4 == 0 && kSubWords % 4 == 0, "window must be uint4 sized");
 
@@ -206,22 +199,13 @@ __device__ __forceinline__ void zero_fill(void* base, size_t bytes)
     for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) p[i] = z;
 }
 
-__global__ void __launch_bounds__(kHuffThreads, 1)
-huff_sync(const ScanGeom g, const ScanBufs b)
+// The warp's share of huff_sync: fix-point iteration over its chunk, mailbox exchange with the
+// chunk on its left, one record per owned subsequence.
+__device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
+                                           long long win_sub0, uint32_t chunk, int lane)
 {
-    __shared__ SharedTables st;
-    const unsigned long long t0 = now_ns();
-    const long long win_sub0 = (long long)blockIdx.x * kSyncUseful - kOverlapSubs;
-    stage(g, b, st, win_sub0 * kSubWords, kSyncWinWords);
-    const unsigned long long t1 = now_ns();
-    zero_fill(b.coef, b.coef_bytes);
-    zero_fill(b.dc, b.dc_bytes);
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t chunk = blockIdx.x * kSyncWarps + warp;
     const long long sub = (long long)chunk * kChunkSubs - kOverlapSubs + lane;
     const uint32_t chunk_first = chunk * (uint32_t)kChunkSubs;
-    if (chunk_first >= g.num_subs) return; // whole warp
     const bool active = sub >= 0 && sub < (long long)g.num_subs;
 
     uint32_t k = 0, i = 0, seg_bits = 0;
@@ -280,10 +264,6 @@ huff_sync(const ScanGeom g, const ScanBufs b)
             if (lane == last_lane) mailbox[chunk] = 0x80000000u | entry_x(rec);
         }
     }
-    if (lane == 0) {
-        atomicMax(&b.ctrl->sync_stage_ns, (uint32_t)(t1 - t0));
-        atomicMax(&b.ctrl->sync_iter_ns, (uint32_t)(now_ns() - t1));
-    }
     if (active && lane >= kOverlapSubs) {
         reinterpret_cast<ulonglong2*>(b.entries)[sub] = make_ulonglong2(
             pack_entry((uint16_t)(entry | (head ? kStateHead : 0)), entry_x(rec), entry_n(rec)),
@@ -292,165 +272,204 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     }
 }
 
-constexpr int kLinkThreads = 1024;
-
-__global__ void __launch_bounds__(kLinkThreads, 1)
-huff_link(const ScanGeom g, const ScanBufs b)
+// Runs in the CTA of huff_sync that finishes last: verify every chunk boundary (exit of the left
+// record == entry of the right one).  If all agree, every record is exact by induction from the
+// segment starts.  Otherwise repair sequentially from each break until the stored records agree
+// again, and re-verify every boundary (concurrent repairs may interleave).  A mismatch is
+// possible only when a mailbox wait timed out or a left neighbour re-published after it was
+// read, so this is a few hundred loads in practice; on adversarial streams it degenerates to a
+// serial decode, like the reference's TODO at src/decode_huffman.cu:475.
+__device__ __forceinline__ void verify_and_repair(const ScanGeom& g, const ScanBufs& b, SharedTables& st)
 {
-    __shared__ SharedTables st;
-    __shared__ uint32_t s_sum[kLinkThreads / 32], s_flag[kLinkThreads / 32];
     volatile unsigned long long* entries = reinterpret_cast<volatile unsigned long long*>(b.entries);
     const uint32_t N = g.num_subs;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned long long t_start = 0, t_verified = 0;
-    if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-
-    // ---- verify (and, rarely, repair) ------------------------------------------------------
     uint32_t stride = (uint32_t)kChunkSubs; // first round: only chunk boundaries can disagree
     uint32_t rounds = 0, slow_total = 0;
-    bool staged = false;
     for (;;) {
         uint32_t bad = 0;
-        for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kLinkThreads)
+        for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kHuffThreads)
             bad |= boundary_ok(entries[2 * (size_t)j - 2], entries[2 * (size_t)j]) ? 0u : 1u;
         if (!__syncthreads_or((int)bad)) break;
-        if (!staged) { // tables are only needed on this path
-            const uint32_t lut_vec = (g.lut_pool_words + 3) / 4;
-            for (uint32_t v = threadIdx.x; v < lut_vec; v += kLinkThreads)
-                s_dyn[v] = __ldg(reinterpret_cast<const uint4*>(b.lut_pool) + v);
-            if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(s_dyn));
-            staged = true;
-            __syncthreads();
-        }
         uint32_t rewritten = 0;
-        for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kLinkThreads) {
+        for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kHuffThreads) {
             if (boundary_ok(entries[2 * (size_t)j - 2], entries[2 * (size_t)j])) continue;
-            const SegDesc seg = b.segs[b.seg_idx[j]];
+            const SegDesc seg = b.segs[*(volatile uint32_t*)(b.seg_idx + j)];
             const GlobalMem M{&st, b.slow, smem_addr(st.recs),
                               b.destuffed + (size_t)seg.sub_off * kSubWords};
             rewritten += relink_from(M, seg, entries, j);
         }
         slow_total += rewritten;
         ++rounds;
-        stride = 1; // concurrent repairs may interleave: from now on check every boundary
+        stride = 1;
+        __threadfence();
         __syncthreads();
-    }
-
-    if (threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_verified));
-    // ---- segmented exclusive scan of the slot counts ---------------------------------------
-    // Tiles of 4 records per thread: 64 contiguous bytes loaded and 16 bytes stored per thread
-    // (a strided per-thread run made every load its own sector and took 10x longer on one SM).
-    __shared__ uint32_t s_carry, s_excl[kLinkThreads / 32];
-    if (threadIdx.x == 0) s_carry = 0;
-    __syncthreads();
-    const unsigned long long* ent = reinterpret_cast<const unsigned long long*>(b.entries);
-    constexpr uint32_t kPer = 4, kTile = kLinkThreads * kPer;
-    for (uint32_t base = 0; base < N; base += kTile) {
-        const uint32_t j0 = base + threadIdx.x * kPer;
-        unsigned long long e[kPer];
-        if (j0 + kPer <= N) {
-            const ulonglong2* rp = reinterpret_cast<const ulonglong2*>(ent) + j0;
-#pragma unroll
-            for (uint32_t i = 0; i < kPer; ++i) e[i] = __ldcg(rp + i).x;
-        } else {
-#pragma unroll
-            for (uint32_t i = 0; i < kPer; ++i) e[i] = j0 + i < N ? __ldcg(ent + 2 * (size_t)(j0 + i)) : 0ull;
-        }
-        uint32_t sum = 0, flag = 0;
-#pragma unroll
-        for (uint32_t i = 0; i < kPer; ++i) {
-            if (entry_g(e[i]) & kStateHead) sum = 0, flag = 1;
-            sum += entry_n(e[i]);
-        }
-        // inclusive segmented scan over threads of (sum, flag)
-        uint32_t inc = sum, f = flag;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
-            const uint32_t upf = __shfl_up_sync(0xffffffffu, f, d);
-            if (lane >= d) {
-                if (!f) inc += up;
-                f |= upf;
-            }
-        }
-        if (lane == 31) s_sum[warp] = inc, s_flag[warp] = f;
-        __syncthreads();
-        if (warp == 0) { // second level: segmented scan of the 32 warp aggregates
-            uint32_t v = s_sum[lane], gf = s_flag[lane];
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t up = __shfl_up_sync(0xffffffffu, v, d);
-                const uint32_t upg = __shfl_up_sync(0xffffffffu, gf, d);
-                if (lane >= d) {
-                    if (!gf) v += up;
-                    gf |= upg;
-                }
-            }
-            const uint32_t tile_carry = s_carry;
-            const uint32_t incl = gf ? v : v + tile_carry; // running value after warp `lane`
-            uint32_t excl = __shfl_up_sync(0xffffffffu, incl, 1);
-            if (lane == 0) excl = tile_carry;
-            s_excl[lane] = excl;
-            if (lane == 31) s_carry = incl; // every lane read tile_carry before the shuffles
-        }
-        __syncthreads();
-        // running value before this thread's records
-        uint32_t acc = __shfl_up_sync(0xffffffffu, inc, 1);
-        const uint32_t fex = __shfl_up_sync(0xffffffffu, f, 1);
-        if (lane == 0) acc = s_excl[warp];
-        else if (!fex) acc += s_excl[warp];
-        uint32_t out[kPer];
-#pragma unroll
-        for (uint32_t i = 0; i < kPer; ++i) {
-            if (entry_g(e[i]) & kStateHead) acc = 0;
-            out[i] = acc;
-            acc += entry_n(e[i]);
-        }
-        if (j0 + kPer <= N) {
-            *reinterpret_cast<uint4*>(b.qpos + j0) = make_uint4(out[0], out[1], out[2], out[3]);
-        } else {
-#pragma unroll
-            for (uint32_t i = 0; i < kPer; ++i)
-                if (j0 + i < N) b.qpos[j0 + i] = out[i];
-        }
-        // no barrier here: s_sum / s_excl are rewritten only behind the next tile's barriers
     }
     if (slow_total) atomicAdd(&b.ctrl->slow_repairs, slow_total);
-    if (threadIdx.x == 0) {
-        unsigned long long t_end;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
-        b.ctrl->link_rounds = rounds;
-        b.ctrl->link_verify_ns = (uint32_t)(t_verified - t_start);
-        b.ctrl->link_scan_ns = (uint32_t)(t_end - t_verified);
+    if (threadIdx.x == 0) b.ctrl->link_rounds = rounds;
+}
+
+__global__ void __launch_bounds__(kHuffThreads, 1)
+huff_sync(const ScanGeom g, const ScanBufs b)
+{
+    __shared__ SharedTables st;
+    __shared__ uint32_t s_last;
+    const unsigned long long t0 = now_ns();
+    const long long win_sub0 = (long long)blockIdx.x * kSyncUseful - kOverlapSubs;
+    stage(g, b, st, win_sub0 * kSubWords, kSyncWinWords);
+    const unsigned long long t1 = now_ns();
+    zero_fill(b.coef, b.coef_bytes);
+    zero_fill(b.dc, b.dc_bytes);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t chunk = blockIdx.x * kSyncWarps + warp;
+    if (chunk * (uint32_t)kChunkSubs < g.num_subs) sync_chunk(g, b, st, win_sub0, chunk, lane); // warp-uniform
+    const unsigned long long t2 = now_ns();
+
+    // last CTA out verifies the records of the whole scan
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&b.ctrl->sync_done, 1u) == gridDim.x - 1u ? 1u : 0u;
+    __syncthreads();
+    if (s_last) {
+        __threadfence();
+        verify_and_repair(g, b, st);
     }
+    if (lane == 0) {
+        atomicMax(&b.ctrl->sync_stage_ns, (uint32_t)(t1 - t0));
+        atomicMax(&b.ctrl->sync_iter_ns, (uint32_t)(t2 - t1));
+        if (s_last) b.ctrl->link_verify_ns = (uint32_t)(now_ns() - t2);
+    }
+}
+
+__device__ __forceinline__ unsigned long long ld_acquire64(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release64(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// First output slot (segment relative) of the CTA's subsequences == segmented exclusive prefix sum
+// of the slot counts of all records before them (replaces the reference's CUB ExclusiveScanByKey +
+// assign_sinfo_n, src/decode_huffman.cu:827-869, and a whole kernel of ours).  Every CTA scans
+// its own records, publishes {slots after its last segment head, has-head} in one 64-bit word and
+// adds up the words of the CTAs before it, back to the nearest one that holds a segment head.
+// The published words do not depend on other CTAs, so nothing chains; CTAs are numbered by an
+// atomic ticket, so a CTA only ever waits for CTAs that are already running.
+// value: slot count (even threads: the record's n, odd threads: 0); returns the exclusive prefix.
+__device__ __forceinline__ uint32_t cta_slot_prefix(uint32_t cta, uint32_t n, bool head,
+                                                    unsigned long long* agg)
+{
+    __shared__ uint32_t s_sum[kWriteThreads / 32], s_flag[kWriteThreads / 32];
+    __shared__ uint32_t s_excl[kWriteThreads / 32], s_seen[kWriteThreads / 32];
+    __shared__ uint32_t s_min[kWriteThreads / 32], s_add[kWriteThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    // inclusive segmented scan over the threads of the CTA
+    uint32_t inc = n, f = head ? 1u : 0u; // sum of n from the nearest head (inclusive) to here
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+        const uint32_t upf = __shfl_up_sync(0xffffffffu, f, d);
+        if (lane >= d) {
+            if (!f) inc += up;
+            f |= upf;
+        }
+    }
+    if (lane == 31) s_sum[warp] = inc, s_flag[warp] = f;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = lane < warps ? s_sum[lane] : 0u, gf = lane < warps ? s_flag[lane] : 0u;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, v, d);
+            const uint32_t upg = __shfl_up_sync(0xffffffffu, gf, d);
+            if (lane >= d) {
+                if (!gf) v += up;
+                gf |= upg;
+            }
+        }
+        // exclusive over warps: value and "a head was seen" before warp `lane`
+        const uint32_t ev = __shfl_up_sync(0xffffffffu, v, 1), eg = __shfl_up_sync(0xffffffffu, gf, 1);
+        if (lane < warps) {
+            s_excl[lane] = lane == 0 ? 0u : ev;
+            s_seen[lane] = lane == 0 ? 0u : eg;
+        }
+        if (lane == warps - 1) // CTA aggregate: slots after the last head, has-head, ready
+            st_release64(agg + cta, ((unsigned long long)v << 2) | (gf ? 2ull : 0ull) | 1ull);
+    }
+    __syncthreads();
+    // inclusive value / head-seen flag up to and including this thread, inside the CTA
+    const uint32_t local_inc = f ? inc : inc + s_excl[warp];
+    const bool local_seen = f != 0 || s_seen[warp] != 0;
+
+    // look back over the CTAs before this one
+    uint32_t carry = 0;
+    for (uint32_t base = 0; base < cta; base += blockDim.x) {
+        const uint32_t t = base + threadIdx.x;
+        unsigned long long w = 0;
+        if (t < cta) {
+            const unsigned long long* src = agg + (cta - 1u - t);
+            while (((w = ld_acquire64(src)) & 1ull) == 0) __nanosleep(40);
+        }
+        const uint32_t mine = (w & 2ull) ? t : 0xffffffffu;
+        const uint32_t wmin = __reduce_min_sync(0xffffffffu, mine);
+        if (lane == 0) s_min[warp] = wmin;
+        __syncthreads();
+        uint32_t tmin = 0xffffffffu;
+        for (int k = 0; k < warps; ++k) tmin = umin(tmin, s_min[k]);
+        const uint32_t part = __reduce_add_sync(0xffffffffu, (t < cta && t <= tmin) ? (uint32_t)(w >> 2) : 0u);
+        if (lane == 0) s_add[warp] = part;
+        __syncthreads();
+        for (int k = 0; k < warps; ++k) carry += s_add[k];
+        if (tmin != 0xffffffffu) break; // uniform
+    }
+    const uint32_t incl = local_seen ? local_inc : local_inc + carry;
+    return head ? 0u : incl - n;
 }
 
 __global__ void __launch_bounds__(kWriteThreads, 1)
 huff_write(const ScanGeom g, const ScanBufs b)
 {
     __shared__ SharedTables st;
+    __shared__ uint32_t s_cta;
     const unsigned long long t0 = now_ns();
+    if (threadIdx.x == 0) s_cta = atomicAdd(&b.ctrl->write_ticket, 1u);
+    __syncthreads();
+    const uint32_t cta = s_cta;
     const uint32_t subs_per_cta = blockDim.x / 2;
     const int win_words = (int)(subs_per_cta * kSubWords + kWinMargin);
-    const uint32_t sub0 = blockIdx.x * subs_per_cta;
-    stage(g, b, st, (long long)sub0 * kSubWords, win_words);
-    const unsigned long long t1 = now_ns();
+    const uint32_t sub0 = cta * subs_per_cta;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t j = sub0 + (threadIdx.x >> 1), h = threadIdx.x & 1u;
 
-    // this thread's half subsequence: record, placement, slot range [qs, qe)
-    bool has = false;
+    // this thread's record; the CTA's slot prefix is published before the tables are staged, so
+    // that the CTAs after this one never wait for it
     unsigned long long rec = 0;
-    uint32_t mid = 0, q0 = 0, first_du = 0, q_limit = 0, qs = 0, qe = 0, i = 0;
-    SegDesc seg = {0, 0, 0, 0};
+    uint32_t mid = 0, k = 0;
     if (j < g.num_subs) {
-        const ulonglong2 r = __ldg(reinterpret_cast<const ulonglong2*>(b.entries) + j);
+        const ulonglong2 r = __ldcg(reinterpret_cast<const ulonglong2*>(b.entries) + j);
         rec = r.x;
         mid = (uint32_t)r.y;
-        const uint32_t k = b.seg_idx[j];
+        k = __ldcg(b.seg_idx + j);
+    }
+    const bool is_head = j < g.num_subs && (entry_g(rec) & kStateHead) != 0;
+    uint32_t q0 = cta_slot_prefix(cta, h == 0 ? entry_n(rec) : 0u, h == 0 && is_head, b.write_agg);
+    q0 = __shfl_sync(0xffffffffu, q0, lane & ~1); // the odd thread of the pair takes the even one's
+    if (h == 0 && j < g.num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
+
+    stage(g, b, st, (long long)sub0 * kSubWords, win_words);
+    const unsigned long long t1 = now_ns();
+
+    // this thread's half subsequence: placement, slot range [qs, qe)
+    bool has = false;
+    uint32_t first_du = 0, q_limit = 0, qs = 0, qe = 0, i = 0;
+    SegDesc seg = {0, 0, 0, 0};
+    if (j < g.num_subs) {
         seg = b.segs[k];
         i = j - seg.sub_off;
-        q0 = b.qpos[j];
         if (segment_extent(g, k, first_du, q_limit)) {
             qs = h ? q0 + (mid >> 16) : q0;
             qe = umin(h ? q0 + entry_n(rec) : q0 + (mid >> 16), q_limit);
@@ -472,108 +491,23 @@ huff_write(const ScanGeom g, const ScanBufs b)
         write_half(M, seg, i, h, rec, mid, q0, q_limit);
         list_end = M.list_ptr;
     }
-    __syncwarp();
     const unsigned long long t2 = now_ns();
 
-    // ---- lists -> data units --------------------------------------------------------------
-    // The warp's slots [gmin, gmax) are contiguous up to gaps at restart boundaries.  Data units
-    // that lie entirely inside belong to this warp alone: they are assembled in the tile (zeros
-    // included) and stored with coalesced 16-byte stores.  The first / last data unit may be
-    // shared with the neighbouring warp: only their non-zero coefficients are stored, into the
-    // buffer huff_sync zero-filled.
+    // Every thread scatters its own list straight into the buffers huff_sync zero-filled: AC
+    // values at their zig-zag slot, DC differences into the compact per-DU array.  (Assembling
+    // whole data units in shared memory and storing 16-byte vectors was 15% slower: ~3000 more
+    // warp instructions per warp and, through its shared-memory tiles, one wave more of CTAs.)
     const uint32_t gs0 = first_du * 64u + qs; // global slot of this thread's first coefficient
-    const uint32_t gmin = __reduce_min_sync(0xffffffffu, has ? gs0 : 0xffffffffu);
-    const uint32_t gmax = __reduce_max_sync(0xffffffffu, has ? first_du * 64u + qe : 0u);
-    uint32_t tiles = 0;
-#if !defined(JB2_WRITE_TILES)
-    // Every thread scatters its own list straight into the zero-filled buffers.  (The tile
-    // assembly below stores coalesced 16-byte vectors instead, but its ~3000 extra warp
-    // instructions per warp and its shared-memory tiles (one wave fewer CTAs per SM) made the
-    // kernel 15% slower on B200 than these 2-byte stores into L2-resident lines.)
     for (uint32_t at = list_addr; at != list_end; at += 4u) {
         const uint32_t e = lds32(at);
         const uint32_t slot = gs0 + (e >> 16);
         if ((slot & 63u) == 0) b.dc[slot >> 6] = (int16_t)(e & 0xffffu);
         else b.coef[slot] = (int16_t)(e & 0xffffu);
     }
-    if (false) {
-#else
-    if (gmax > 0) {
-#endif
-        const uint32_t own_lo = (gmin + 63u) >> 6, own_hi = gmax >> 6; // owned: [own_lo, own_hi)
-        uint16_t* tile = reinterpret_cast<uint16_t*>(warp_mem + kWarpListBytes);
-        uint4* tile_vec = reinterpret_cast<uint4*>(tile);
-        uint32_t rd = list_addr;
-        for (;; ++tiles) {
-            // next tile = the one holding the smallest pending slot (empty stretches of the
-            // warp's range, e.g. flat image areas, stay as huff_sync zero-filled them)
-            const uint32_t pending = rd != list_end ? gs0 + (lds32(rd) >> 16) : 0xffffffffu;
-            const uint32_t first = __reduce_min_sync(0xffffffffu, pending);
-            if (first == 0xffffffffu) break;
-            const uint32_t du0 = first >> 6;
-#pragma unroll
-            for (int v = 0; v < kTileDus * 8 / 32; ++v) tile_vec[v * 32 + lane] = make_uint4(0u, 0u, 0u, 0u);
-            __syncwarp();
-            const uint32_t tile_slot0 = du0 * 64u, tile_slots = kTileDus * 64u;
-            // lists with entries in this tile, one list at a time, a batch of 32 entries per step
-            // (a lane walking its own list alone would serialise the whole tile behind the lane
-            // with the longest list)
-            uint32_t todo = __ballot_sync(0xffffffffu, pending - tile_slot0 < tile_slots);
-            while (todo) {
-                const int src = __ffs((int)todo) - 1;
-                todo &= todo - 1u;
-                const uint32_t src_rd = __shfl_sync(0xffffffffu, rd, src);
-                const uint32_t src_end = __shfl_sync(0xffffffffu, list_end, src);
-                const uint32_t src_gs0 = __shfl_sync(0xffffffffu, gs0, src);
-                uint32_t consumed = 0;
-                for (uint32_t at = src_rd + (uint32_t)lane * 4u;; at += 128u) {
-                    bool in = false;
-                    if (at < src_end) {
-                        const uint32_t e = lds32(at);
-                        const uint32_t rel = src_gs0 + (e >> 16) - tile_slot0;
-                        in = rel < tile_slots; // entries are sorted: the hits form a prefix
-                        if (in) tile[rel] = (uint16_t)e;
-                    }
-                    const uint32_t hits = __popc(__ballot_sync(0xffffffffu, in));
-                    consumed += hits;
-                    if (hits < 32u) break;
-                }
-                if (lane == src) rd += consumed * 4u;
-            }
-            __syncwarp();
-#pragma unroll
-            for (int v = 0; v < kTileDus * 8 / 32; ++v) {
-                const uint32_t idx = (uint32_t)v * 32u + (uint32_t)lane; // 16-byte vector of the tile
-                const uint32_t du = du0 + (idx >> 3);
-                const uint4 val = tile_vec[idx];
-                // eight consecutive lanes hold one data unit: all-zero data units are not stored
-                const uint32_t nz = __ballot_sync(0xffffffffu, (val.x | val.y | val.z | val.w) != 0);
-                if (((nz >> (lane & 24)) & 0xffu) == 0) continue;
-                if (du >= own_lo && du < own_hi) {
-                    reinterpret_cast<uint4*>(b.coef)[(size_t)du * 8 + (idx & 7u)] = val;
-                    if ((idx & 7u) == 0) b.dc[du] = (int16_t)(val.x & 0xffffu); // input of the DC scan
-                } else if (du * 64u < gmax && du >= (gmin >> 6)) { // shared data unit
-                    const uint32_t w[4] = {val.x, val.y, val.z, val.w};
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const uint16_t c16 = (uint16_t)(w[k >> 1] >> (16 * (k & 1)));
-                        const uint32_t slot = du * 64u + (idx & 7u) * 8u + (uint32_t)k;
-                        if (c16 != 0) {
-                            if ((slot & 63u) == 0) b.dc[du] = (int16_t)c16;
-                            else b.coef[slot] = (int16_t)c16;
-                        }
-                    }
-                }
-            }
-            __syncwarp();
-        }
-    }
     if (lane == 0) {
         atomicMax(&b.ctrl->write_stage_ns, (uint32_t)(t1 - t0));
         atomicMax(&b.ctrl->write_decode_ns, (uint32_t)(t2 - t1));
         atomicMax(&b.ctrl->write_flush_ns, (uint32_t)(now_ns() - t2));
-        atomicMax(&b.ctrl->write_tiles_max, tiles);
-        atomicAdd(&b.ctrl->write_tiles, tiles);
     }
 }
 
@@ -587,17 +521,14 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     if (first_use_on_device(configured)) {
         const int max_smem = 226 * 1024; // 227 KiB per CTA minus the static part
         prefer_max_shared(huff_sync, max_smem);
-        prefer_max_shared(huff_link, max_smem);
         prefer_max_shared(huff_write, max_smem);
     }
     const uint32_t chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
     tm->mark(stream, kIdSync);
     huff_sync<<<(chunks + kSyncWarps - 1) / kSyncWarps, kHuffThreads,
                 kSyncWinWords * 4 + lut_bytes, stream>>>(g, b);
-    tm->mark(stream, kIdLink);
-    huff_link<<<1, kLinkThreads, lut_bytes, stream>>>(g, b);
     // as many warps per CTA as the shared memory left by the LUT pool allows (each warp needs
-    // its coefficient lists and one tile)
+    // its coefficient lists)
     const size_t budget = 225 * 1024;
     int warps = kWriteThreads / 32;
     auto write_smem = [&](int w) {

@@ -99,7 +99,8 @@ __device__ __forceinline__ bool locate(const ScanGeom& g, uint32_t t, DuPos& pos
 constexpr int kIdctThreads = 128;
 
 __global__ void __launch_bounds__(kIdctThreads)
-idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const OutPlanes out)
+idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
+            const OutPlanes out)
 {
     __shared__ int s_q[kMaxComp][64];
     for (int i = threadIdx.x; i < kMaxComp * 64; i += kIdctThreads)
@@ -126,6 +127,7 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const OutPlanes 
             v[n1 >> 3][n1 & 7] = (int)(short)(hi * s_q[a][n1]);
         }
     }
+    v[0][0] = (int)(short)((int)dc[pos.du] * s_q[a][0]); // absolute DC lives in the compact array
 #pragma unroll
     for (int x = 0; x < 8; ++x)
         idct8(v[0][x], v[1][x], v[2][x], v[3][x], v[4][x], v[5][x], v[6][x], v[7][x]);
@@ -164,7 +166,8 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const OutPlanes 
 // Stand-alone transpose: coded order (zig-zag inside a DU) -> planar raster int16 (row length =
 // plane stride).  One thread gathers one 8-coefficient raster row, eight consecutive threads one DU.
 __global__ void __launch_bounds__(256)
-transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const CoefPlanes planes)
+transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef,
+                 const int16_t* __restrict__ dc, const CoefPlanes planes)
 {
     const uint32_t t = blockIdx.x * 256 + threadIdx.x;
     const uint32_t r = t & 7u;
@@ -178,6 +181,7 @@ transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const CoefP
         const uint32_t hi = (uint16_t)du[c_zigzag_of.v[r * 8 + 2 * k + 1]];
         px[k] = lo | (hi << 16);
     }
+    if (r == 0) px[0] = (px[0] & 0xffff0000u) | (uint16_t)dc[pos.du];
     int16_t* dst = planes.ptr[pos.comp] +
                    (size_t)(pos.by * 8 + (int)r) * planes.stride[pos.comp] + pos.bx * 8;
     *reinterpret_cast<uint4*>(dst) = make_uint4(px[0], px[1], px[2], px[3]);
@@ -193,7 +197,7 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
     static std::atomic<unsigned long long> configured{0};
     if (first_use_on_device(configured)) prefer_max_shared(idct_kernel);
     tm->mark(stream, kIdIdct);
-    idct_kernel<<<(total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0, stream>>>(g, b.coef, out);
+    idct_kernel<<<(total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0, stream>>>(g, b.coef, b.dc, out);
     return cudaGetLastError();
 }
 
@@ -205,7 +209,7 @@ cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPla
     static std::atomic<unsigned long long> configured{0};
     if (first_use_on_device(configured)) prefer_max_shared(transpose_kernel);
     tm->mark(stream, kIdTranspose);
-    transpose_kernel<<<(total + 255) / 256, 256, 0, stream>>>(g, b.coef, planes);
+    transpose_kernel<<<(total + 255) / 256, 256, 0, stream>>>(g, b.coef, b.dc, planes);
     return cudaGetLastError();
 }
 
@@ -213,8 +217,8 @@ int count_launches(const ScanGeom& g, bool with_transpose)
 {
     int n = 0;
     if (g.scan_bytes) n += 1;
-    if (g.num_subs) n += 3;
-    if (g.total_mcus) n += 2;
+    if (g.num_subs) n += 2;
+    if (g.total_mcus) n += 1;
     n += 1; // idct
     if (with_transpose) n += 1;
     return n;

@@ -259,6 +259,8 @@ const uint8_t* find_marker_sse2(const uint8_t* p, const uint8_t* lim, uint64_t* 
     return find_marker_scalar(p, lim, ffs);
 }
 
+constexpr int kWalkPrefetch = 4096;
+
 __attribute__((target("avx2,popcnt"))) const uint8_t* find_marker_avx2(const uint8_t* p,
                                                                       const uint8_t* lim,
                                                                       uint64_t* ffs)
@@ -267,6 +269,7 @@ __attribute__((target("avx2,popcnt"))) const uint8_t* find_marker_avx2(const uin
     const __m256i vff = _mm256_set1_epi8((char)0xff), vz = _mm256_setzero_si256();
     uint64_t n = 0;
     while (p + 64 <= lim) {
+        _mm_prefetch((const char*)p + kWalkPrefetch, _MM_HINT_T0);
         const __m256i a0 = _mm256_loadu_si256((const __m256i*)p);
         const __m256i a1 = _mm256_loadu_si256((const __m256i*)(p + 32));
         const __m256i b0 = _mm256_loadu_si256((const __m256i*)(p + 1));
@@ -288,9 +291,50 @@ __attribute__((target("avx2,popcnt"))) const uint8_t* find_marker_avx2(const uin
     return find_marker_sse2(p, lim, ffs);
 }
 
+// 128 bytes per iteration with mask registers: two loads, the "followed by 0x00" mask is derived
+// from the zero masks of the same two vectors (+ one scalar byte), no overlapping loads.
+__attribute__((target("avx512f,avx512bw,popcnt,avx2"))) const uint8_t* find_marker_avx512(
+    const uint8_t* p, const uint8_t* lim, uint64_t* ffs)
+{
+    const __m512i vff = _mm512_set1_epi8((char)0xff);
+    uint64_t n = 0;
+    while (p + 128 <= lim) { // p[128] is readable: lim <= end - 1
+        // The previous image's H2D copy (a DMA read) leaves these lines out of the core's caches;
+        // prefetching 4 KB ahead cut the in-flow walk of a 1.4 MB scan from 60 to 42 us on the
+        // B200 host.  (Prefetches past the buffer end do not fault.)
+        _mm_prefetch((const char*)p + kWalkPrefetch, _MM_HINT_T0);
+        _mm_prefetch((const char*)p + kWalkPrefetch + 64, _MM_HINT_T0);
+        const __m512i a0 = _mm512_loadu_si512((const void*)p);
+        const __m512i a1 = _mm512_loadu_si512((const void*)(p + 64));
+        const uint64_t mf0 = _mm512_cmpeq_epi8_mask(a0, vff);
+        const uint64_t mf1 = _mm512_cmpeq_epi8_mask(a1, vff);
+        const uint64_t z0 = _mm512_testn_epi8_mask(a0, a0);
+        const uint64_t z1 = _mm512_testn_epi8_mask(a1, a1);
+        const uint64_t zn0 = (z0 >> 1) | (z1 << 63);
+        const uint64_t zn1 = (z1 >> 1) | ((uint64_t)(p[128] == 0) << 63);
+        const uint64_t o0 = mf0 & ~zn0, o1 = mf1 & ~zn1;
+        if (__builtin_expect((o0 | o1) != 0, 0)) {
+            if (o0) {
+                const unsigned i = (unsigned)__builtin_ctzll(o0);
+                *ffs += n + (uint64_t)__builtin_popcountll(mf0 & ((1ull << i) - 1ull));
+                return p + i;
+            }
+            const unsigned i = (unsigned)__builtin_ctzll(o1);
+            *ffs += n + (uint64_t)__builtin_popcountll(mf0) +
+                    (uint64_t)__builtin_popcountll(mf1 & ((1ull << i) - 1ull));
+            return p + 64 + i;
+        }
+        n += (uint64_t)__builtin_popcountll(mf0) + (uint64_t)__builtin_popcountll(mf1);
+        p += 128;
+    }
+    *ffs += n;
+    return find_marker_avx2(p, lim, ffs);
+}
+
 FindFn pick_find_marker()
 {
     __builtin_cpu_init();
+    if (__builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512f")) return find_marker_avx512;
     return __builtin_cpu_supports("avx2") ? find_marker_avx2 : find_marker_sse2;
 }
 #else
