@@ -94,6 +94,44 @@ inline void prefer_max_shared(Kernel* k, int max_dynamic_bytes = 0)
         cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dynamic_bytes);
 }
 
+// Programmatic dependent launch (sm_90+): every kernel after the first of a scan is launched
+// with the programmatic-stream-serialization attribute, so its CTAs may start while the previous
+// kernel is still draining.  Device side, a kernel does what needs no input from its predecessor
+// (tables into shared memory, zero-fill), then grid_dependency_wait() - which returns once the
+// predecessor grid has completed and its writes are visible - and only THEN
+// grid_dependency_trigger(), which lets its own successor start its prologue.  Triggering after
+// the wait makes completion transitive: a prologue never runs before the grand-predecessor is
+// done.  Every thread of every kernel executes the wait.
+#if defined(__CUDACC__)
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dependency_trigger()
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_dependent(void (*kernel)(KArgs...), unsigned grid, unsigned block,
+                                    size_t smem, cudaStream_t stream, Args&&... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#define JB2_LAUNCH(expr)                          \
+    do {                                          \
+        const cudaError_t jb2_e_ = (expr);        \
+        if (jb2_e_ != cudaSuccess) return jb2_e_; \
+    } while (0)
+
 // Kernel launches issued per scan by each stage (for bench.py's gpu_launches claim).
 int count_launches(const ScanGeom& g, bool with_transpose);
 

@@ -116,6 +116,8 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, int* __restrict__ agg,
     __shared__ uint32_t warp_flag[kDcTile / 32];
     __shared__ Dc4 s_red[kDcTile / 32];
     __shared__ uint32_t s_tile;
+    grid_dependency_wait();
+    grid_dependency_trigger();
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
@@ -194,8 +196,8 @@ cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream,
     }
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
     tm->mark(stream, kIdDcScan);
-    dc_scan<<<tiles, kDcTile, 0, stream>>>(g, b.dc, b.dc_agg, b.dc_flags, &b.ctrl->dc_ticket);
-    return cudaGetLastError();
+    return launch_dependent(dc_scan, tiles, kDcTile, 0, stream, g, b.dc, b.dc_agg, b.dc_flags,
+                            &b.ctrl->dc_ticket);
 }
 
 } // namespace jb2

@@ -86,6 +86,10 @@ destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __re
     __shared__ uint8_t stage[kDestuffTile];
     __shared__ uint16_t seg_delta[kDestuffTile];
 
+    // first kernel of a scan (launched behind the upload copies): let huff_sync start its
+    // prologue (tables, zero-fill of the coefficient buffer) right away
+    grid_dependency_wait();
+    grid_dependency_trigger();
     for (uint32_t i = blockIdx.x * kDestuffThreads + threadIdx.x; i < clear_words;
          i += gridDim.x * kDestuffThreads)
         clear[i] = 0u;

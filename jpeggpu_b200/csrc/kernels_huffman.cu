@@ -108,8 +108,20 @@ __device__ __forceinline__ void make_device_recs(const ScanGeom& g, SharedTables
 
 // Stage the LUT pool, the slot records and words [first_word, first_word + win_words) of the
 // destuffed scan (zero outside [0, total_words)).
-__device__ __forceinline__ void stage(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
-                                      long long first_word, const int WIN_WORDS)
+// Staging in two steps so that the first can run before the producer of the destuffed scan has
+// finished (programmatic dependent launch): the decode tables come from the upload block...
+__device__ __forceinline__ void stage_tables(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
+                                             const int WIN_WORDS)
+{
+    const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
+    const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
+    uint4* ldst = s_dyn + WIN_WORDS / 4;
+    for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
+    if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(ldst));
+}
+// ...the window of the scan from the destuff kernel's output.  Ends with a barrier.
+__device__ __forceinline__ void stage_window(const ScanGeom& g, const ScanBufs& b,
+                                             long long first_word, const int WIN_WORDS)
 {
     uint32_t* win = reinterpret_cast<uint32_t*>(s_dyn);
     const long long total_words = (long long)g.num_subs * kSubWords;
@@ -120,16 +132,9 @@ __device__ __forceinline__ void stage(const ScanGeom& g, const ScanBufs& b, Shar
         if (w >= 0 && w + 4 <= total_words) v = __ldg(src + (w >> 2));
         reinterpret_cast<uint4*>(win)[i] = v;
     }
-    const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
-    const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
-    uint4* ldst = s_dyn + WIN_WORDS / 4;
-    for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
-    if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(ldst));
     __syncthreads();
 }
 
-// Device memory policy of decode_span over the staged window: every handle is a shared-memory
-// byte address.  `win_addr` = address of the window word that holds segment-relative word 0.
 struct DevMem {
     const SharedTables* st;
     const HuffSlow* slow_;
@@ -315,10 +320,14 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     __shared__ uint32_t s_last;
     const unsigned long long t0 = now_ns();
     const long long win_sub0 = (long long)blockIdx.x * kSyncUseful - kOverlapSubs;
-    stage(g, b, st, win_sub0 * kSubWords, kSyncWinWords);
-    const unsigned long long t1 = now_ns();
+    // before the destuff kernel is done: tables into shared memory, zero-fill of the output
+    stage_tables(g, b, st, kSyncWinWords);
     zero_fill(b.coef, b.coef_bytes);
     zero_fill(b.dc, b.dc_bytes);
+    grid_dependency_wait();
+    grid_dependency_trigger();
+    stage_window(g, b, win_sub0 * kSubWords, kSyncWinWords);
+    const unsigned long long t1 = now_ns();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t chunk = blockIdx.x * kSyncWarps + warp;
@@ -436,11 +445,15 @@ huff_write(const ScanGeom g, const ScanBufs b)
     __shared__ SharedTables st;
     __shared__ uint32_t s_cta;
     const unsigned long long t0 = now_ns();
-    if (threadIdx.x == 0) s_cta = atomicAdd(&b.ctrl->write_ticket, 1u);
-    __syncthreads();
-    const uint32_t cta = s_cta;
     const uint32_t subs_per_cta = blockDim.x / 2;
     const int win_words = (int)(subs_per_cta * kSubWords + kWinMargin);
+    // before huff_sync is done (the control block was cleared two kernels ago): ticket, tables
+    if (threadIdx.x == 0) s_cta = atomicAdd(&b.ctrl->write_ticket, 1u);
+    stage_tables(g, b, st, win_words);
+    grid_dependency_wait();
+    grid_dependency_trigger();
+    __syncthreads();
+    const uint32_t cta = s_cta;
     const uint32_t sub0 = cta * subs_per_cta;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t j = sub0 + (threadIdx.x >> 1), h = threadIdx.x & 1u;
@@ -460,7 +473,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
     q0 = __shfl_sync(0xffffffffu, q0, lane & ~1); // the odd thread of the pair takes the even one's
     if (h == 0 && j < g.num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
 
-    stage(g, b, st, (long long)sub0 * kSubWords, win_words);
+    stage_window(g, b, (long long)sub0 * kSubWords, win_words);
     const unsigned long long t1 = now_ns();
 
     // this thread's half subsequence: placement, slot range [qs, qe)
@@ -525,8 +538,8 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     }
     const uint32_t chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
     tm->mark(stream, kIdSync);
-    huff_sync<<<(chunks + kSyncWarps - 1) / kSyncWarps, kHuffThreads,
-                kSyncWinWords * 4 + lut_bytes, stream>>>(g, b);
+    JB2_LAUNCH(launch_dependent(huff_sync, (chunks + kSyncWarps - 1) / kSyncWarps, kHuffThreads,
+                                kSyncWinWords * 4 + lut_bytes, stream, g, b));
     // as many warps per CTA as the shared memory left by the LUT pool allows (each warp needs
     // its coefficient lists)
     const size_t budget = 225 * 1024;
@@ -537,8 +550,8 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     while (warps > 1 && write_smem(warps) + 1024 > budget) --warps;
     const uint32_t subs_per_cta = (uint32_t)warps * 16u;
     tm->mark(stream, kIdWrite);
-    huff_write<<<(g.num_subs + subs_per_cta - 1) / subs_per_cta, warps * 32, write_smem(warps), stream>>>(g, b);
-    return cudaGetLastError();
+    return launch_dependent(huff_write, (g.num_subs + subs_per_cta - 1) / subs_per_cta, warps * 32,
+                            write_smem(warps), stream, g, b);
 }
 
 } // namespace jb2

@@ -105,6 +105,8 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
     __shared__ int s_q[kMaxComp][64];
     for (int i = threadIdx.x; i < kMaxComp * 64; i += kIdctThreads)
         s_q[i >> 6][i & 63] = out.q[i >> 6][i & 63];
+    grid_dependency_wait();
+    grid_dependency_trigger();
     __syncthreads();
     DuPos pos;
     if (!locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos)) return;
@@ -169,6 +171,8 @@ __global__ void __launch_bounds__(256)
 transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef,
                  const int16_t* __restrict__ dc, const CoefPlanes planes)
 {
+    grid_dependency_wait();
+    grid_dependency_trigger();
     const uint32_t t = blockIdx.x * 256 + threadIdx.x;
     const uint32_t r = t & 7u;
     DuPos pos;
@@ -197,8 +201,8 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
     static std::atomic<unsigned long long> configured{0};
     if (first_use_on_device(configured)) prefer_max_shared(idct_kernel);
     tm->mark(stream, kIdIdct);
-    idct_kernel<<<(total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0, stream>>>(g, b.coef, b.dc, out);
-    return cudaGetLastError();
+    return launch_dependent(idct_kernel, (total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0,
+                            stream, g, b.coef, b.dc, out);
 }
 
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
@@ -209,8 +213,8 @@ cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPla
     static std::atomic<unsigned long long> configured{0};
     if (first_use_on_device(configured)) prefer_max_shared(transpose_kernel);
     tm->mark(stream, kIdTranspose);
-    transpose_kernel<<<(total + 255) / 256, 256, 0, stream>>>(g, b.coef, b.dc, planes);
-    return cudaGetLastError();
+    return launch_dependent(transpose_kernel, (total + 255) / 256, 256, 0, stream, g, b.coef, b.dc,
+                            planes);
 }
 
 int count_launches(const ScanGeom& g, bool with_transpose)
