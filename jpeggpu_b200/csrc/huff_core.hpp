@@ -157,8 +157,15 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
         bool more;
         do {
             const uint32_t nx = M.word(wn); // not needed before the window slides
-            const uint32_t skip = entry_skip(e);
-            const uint32_t qn = qq + entry_adv(e);
+            uint32_t skip = entry_skip(e);
+            uint32_t qn = qq + entry_adv(e);
+            if (!WRITE) {
+                // state-only pass: take the second symbol of a pair entry along if the first one
+                // stays inside its data unit and the second one starts before `end`
+                const bool pair = ((qn ^ qq) & 64u) == 0 && pp + skip < end;
+                qn += pair ? entry_adv2(e) : 0u;
+                skip += pair ? entry_skip2(e) : 0u;
+            }
             if (WRITE) {
                 // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
                 // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers)

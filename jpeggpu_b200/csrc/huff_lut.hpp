@@ -87,6 +87,21 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, Huf
                 if (first + j < lut2_size) lut2[first + j] = e;
         }
     }
+    // Pair fields (AC tables): if the index bits behind a complete first symbol hold another
+    // complete symbol of the same table, record its length and advance.  The first symbol must
+    // not be an end-of-block (the next symbol would be a DC symbol of another table).
+    if (!is_dc) {
+        for (uint32_t i = 0; i < first_long_prefix; ++i) {
+            const uint32_t e1 = lut1[i];
+            if (e1 < kEntryMarkerLimit) continue;
+            const uint32_t s1 = entry_skip(e1);
+            if (s1 >= (uint32_t)kLutBits || entry_adv(e1) == 64u) continue;
+            const uint32_t rem = (uint32_t)kLutBits - s1;
+            const uint32_t e2 = lut1[(i << s1) & ((uint32_t)kLut1Size - 1u)]; // base fields only
+            if (e2 < kEntryMarkerLimit || entry_skip(e2) > rem) continue;
+            lut1[i] = with_pair(e1, entry_skip(e2), entry_adv(e2));
+        }
+    }
     // short codes that fall inside the long region's prefixes cannot exist (canonical order puts
     // every short code numerically below every long code), so the two levels never conflict.
     return (uint32_t)(header_at + kLutHeader);
