@@ -88,23 +88,20 @@ JB2_HD uint32_t funnel_left_wrap(uint32_t hi, uint32_t lo, uint32_t shift)
 }
 
 // Window slide: when the bit position crosses a word boundary the window moves one word on.
-JB2_HD void slide_window(uint32_t& w0, uint32_t& w1, uint32_t& wn, uint32_t nx, uint32_t pp,
-                         uint32_t pn, uint32_t step)
+// The window holds the two words being decoded (w0, w1) and the one after them (w2), which is
+// loaded at slide time for the NEXT slide - at least 32 bits of symbols later - so the load
+// latency never sits on the symbol-to-symbol dependency chain.  Policies provide
+// slide(w0, w1, w2, wn, pp, pn); this is the portable form.
+template <class Mem>
+JB2_HD void slide_window_generic(const Mem& M, uint32_t& w0, uint32_t& w1, uint32_t& w2,
+                                 uint32_t& wn, uint32_t pp, uint32_t pn)
 {
-#if defined(__CUDA_ARCH__)
-    // one LOP3 with predicate output + three predicated moves (the compiler's own lowering of
-    // the C below took eleven instructions)
-    asm("{\n\t.reg .pred s;\n\t.reg .b32 t;\n\t"
-        "xor.b32 t, %3, %4;\n\tand.b32 t, t, 32;\n\tsetp.ne.u32 s, t, 0;\n\t"
-        "@s mov.b32 %0, %1;\n\t@s mov.b32 %1, %5;\n\t@s add.u32 %2, %2, %6;\n\t}"
-        : "+r"(w0), "+r"(w1), "+r"(wn)
-        : "r"(pn), "r"(pp), "r"(nx), "r"(step));
-#else
-    const bool slide = ((pn ^ pp) & 32u) != 0;
-    w0 = slide ? w1 : w0;
-    w1 = slide ? nx : w1;
-    wn += slide ? step : 0u;
-#endif
+    if (((pn ^ pp) & 32u) != 0) {
+        w0 = w1;
+        w1 = w2;
+        w2 = M.word(wn);
+        wn += Mem::kWordStep;
+    }
 }
 
 // End of a data unit (EOB / slot 63; advance <= 64, so at most one boundary is crossed): the
@@ -139,8 +136,9 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
     uint32_t ch = M.slot_handle(c);
     SlotRec r = M.rec(ch);
     uint32_t tbl = (qq & 63u) == 0 ? (r.w & 0xffffffu) : r.x;
-    uint32_t wn = M.word_handle((pp >> 5) + 2u);
-    uint32_t w0 = M.word(wn - 2u * Mem::kWordStep), w1 = M.word(wn - Mem::kWordStep);
+    uint32_t wn = M.word_handle((pp >> 5) + 3u);
+    uint32_t w0 = M.word(wn - 3u * Mem::kWordStep), w1 = M.word(wn - 2u * Mem::kWordStep);
+    uint32_t w2 = M.word(wn - Mem::kWordStep);
     uint32_t peek = funnel_left_wrap(w0, w1, pp);
     uint32_t e = M.lut(tbl, peek >> (32 - kLutBits));
 
@@ -156,7 +154,6 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
         }
         bool more;
         do {
-            const uint32_t nx = M.word(wn); // not needed before the window slides
             uint32_t skip = entry_skip(e);
             uint32_t qn = qq + entry_adv(e);
             if (!WRITE) {
@@ -177,7 +174,7 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
                 }
             }
             const uint32_t pn = pp + skip;
-            slide_window(w0, w1, wn, nx, pp, pn, Mem::kWordStep);
+            M.slide(w0, w1, w2, wn, pp, pn);
             pp = pn;
             advance_unit(qq, qn, ch, tbl, r);
             peek = funnel_left_wrap(w0, w1, pp);
@@ -221,6 +218,10 @@ struct HostMem {
     JB2_HD const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     JB2_HD uint32_t word_handle(uint32_t i) const { return i; }
     JB2_HD uint32_t word(uint32_t h) const { return words_[h]; }
+    JB2_HD void slide(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t pp, uint32_t pn) const
+    {
+        slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
+    }
     int16_t* coef_ = nullptr; // WRITE: first data unit of the restart segment
     int16_t* dc_ = nullptr;
     JB2_HD void put(uint32_t slot, int v) const

@@ -74,14 +74,6 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr)
     asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
     return v;
 }
-// volatile: keeps the load where it is written (the compiler otherwise sinks the window prefetch
-// under the slide predicate, which exposes its latency)
-__device__ __forceinline__ uint32_t lds32_pinned(uint32_t addr)
-{
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
-}
 __device__ __forceinline__ SlotRec lds_rec(uint32_t addr)
 {
     SlotRec r;
@@ -150,7 +142,18 @@ struct DevMem {
     __device__ __forceinline__ uint32_t slot_tbls(uint32_t c) const { return st->tbls[c]; }
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t word_handle(uint32_t i) const { return win_addr + i * 4u; }
-    __device__ __forceinline__ uint32_t word(uint32_t h) const { return lds32_pinned(h); }
+    __device__ __forceinline__ uint32_t word(uint32_t h) const { return lds32(h); }
+    // one LOP3 with predicate output + predicated moves and the predicated look-ahead load
+    __device__ __forceinline__ void slide(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
+                                          uint32_t pp, uint32_t pn) const
+    {
+        asm volatile("{\n\t.reg .pred s;\n\t.reg .b32 t;\n\t"
+                     "xor.b32 t, %4, %5;\n\tand.b32 t, t, 32;\n\tsetp.ne.u32 s, t, 0;\n\t"
+                     "@s mov.b32 %0, %1;\n\t@s mov.b32 %1, %2;\n\t@s ld.shared.u32 %2, [%3];\n\t"
+                     "@s add.u32 %3, %3, 4;\n\t}"
+                     : "+r"(w0), "+r"(w1), "+r"(w2), "+r"(wn)
+                     : "r"(pn), "r"(pp));
+    }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
 };
@@ -188,6 +191,11 @@ struct GlobalMem {
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t word_handle(uint32_t i) const { return i; }
     __device__ __forceinline__ uint32_t word(uint32_t h) const { return __ldg(words + h); }
+    __device__ __forceinline__ void slide(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
+                                          uint32_t pp, uint32_t pn) const
+    {
+        slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
+    }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
 };
