@@ -92,10 +92,12 @@ __device__ __forceinline__ Dc4 block_segmented_scan(Dc4 val, bool head, Dc4* war
     return val;
 }
 
-__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p)
+// polling load: relaxed (an acquire load invalidates the L1 on every poll); the data reads that
+// follow go to L2 (ld.cg), which the releasing store has already reached
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p)
 {
     uint32_t v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_release(uint32_t* p, uint32_t v)
@@ -145,7 +147,8 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, int* __restrict__ agg,
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) carry.v[a] = 0;
     for (uint32_t t = first_tile + threadIdx.x; t < tile; t += kDcTile) {
-        while (ld_acquire(flags + t) == 0u) __nanosleep(40);
+        while (ld_relaxed(flags + t) == 0u) __nanosleep(20);
+        __threadfence(); // orders the aggregate reads behind the flag (pairs with st.release)
 #pragma unroll
         for (int a = 0; a < kMaxComp; ++a) carry.v[a] += __ldcg(agg + t * kMaxComp + a);
     }

@@ -361,7 +361,8 @@ huff_sync(const ScanGeom g, const ScanBufs b)
 __device__ __forceinline__ unsigned long long ld_acquire64(const unsigned long long* p)
 {
     unsigned long long v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    // relaxed: the word itself carries the payload, nothing else is read behind it
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void st_release64(unsigned long long* p, unsigned long long v)

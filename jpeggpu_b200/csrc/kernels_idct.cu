@@ -68,6 +68,15 @@ __device__ __forceinline__ void idct8(int& v0, int& v1, int& v2, int& v3, int& v
     v7 = unfixh(tmp20 - tmp50);
 }
 
+// bytes {sat(p0), sat(p1), sat(p2), sat(p3)}, p0 lowest, each saturated to 0..255
+__device__ __forceinline__ uint32_t pack_sat_u8(int p0, int p1, int p2, int p3)
+{
+    uint32_t hi, d;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(p3), "r"(p2), "r"(0));
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(p1), "r"(p0), "r"(hi));
+    return d;
+}
+
 // Position of a plane-order thread: scan component, block coordinates and coded DU index.
 struct DuPos {
     int comp, bx, by;
@@ -97,8 +106,11 @@ __device__ __forceinline__ bool locate(const ScanGeom& g, uint32_t t, DuPos& pos
 }
 
 constexpr int kIdctThreads = 128;
+#ifndef JB2_IDCT_MIN_CTAS
+#define JB2_IDCT_MIN_CTAS 6
+#endif
 
-__global__ void __launch_bounds__(kIdctThreads)
+__global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
 idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
             const OutPlanes out)
 {
@@ -145,22 +157,20 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
 #pragma unroll
     for (int y = 0; y < 8; ++y) {
         if (y0 + y >= size_y) break;
-        uint32_t px[8];
+        int s[8];
 #pragma unroll
-        for (int x = 0; x < 8; ++x) {
-            const int s = (int)(short)(v[y][x] + 128); // src/idct.cu:216
-            px[x] = (uint32_t)min(max(s, 0), 255);
-        }
+        for (int x = 0; x < 8; ++x) s[x] = (int)(short)(v[y][x] + 128); // src/idct.cu:216
         uint8_t* row = dst + (size_t)y * out.pitch[a];
         if (full_row) {
+            // clamp(s, 0, 255) and byte packing in one instruction per two samples
             uint2 pk;
-            pk.x = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
-            pk.y = px[4] | (px[5] << 8) | (px[6] << 16) | (px[7] << 24);
+            pk.x = pack_sat_u8(s[0], s[1], s[2], s[3]);
+            pk.y = pack_sat_u8(s[4], s[5], s[6], s[7]);
             *reinterpret_cast<uint2*>(row) = pk;
         } else {
 #pragma unroll
             for (int x = 0; x < 8; ++x)
-                if (x0 + x < size_x) row[x] = (uint8_t)px[x];
+                if (x0 + x < size_x) row[x] = (uint8_t)min(max(s[x], 0), 255);
         }
     }
 }
