@@ -141,9 +141,9 @@ def stage_table(kt_avg_ms, st):
     P = W * H + 2 * ((W + 1) // 2) * ((H + 1) // 2)
     bytes_of = {
         "destuff_kernel": Sb + Sd,
-        "huff_sync": Sd + 8 * N + 2 * Cc + 2 * D,   # reads the scan, zero-fills coefficients + DC array
-        "huff_link": 8 * N + 4 * N,
-        "huff_write": Sd + 12 * N + 2 * D,          # + the scattered non-zero coefficients
+        "huff_sync": Sd + 20 * N + 2 * Cc + 2 * D,  # reads the scan, writes 16 B records + segment
+                                                    # ids, zero-fills coefficients + DC array
+        "huff_write": Sd + 24 * N + 2 * D,          # + the scattered non-zero coefficients
         "dc_scan": 4 * D,                           # compact DC array, in place
         "idct_kernel": 2 * Cc + 2 * D + P,
     }
@@ -153,6 +153,20 @@ def stage_table(kt_avg_ms, st):
         rows[name] = {"ms": round(ms, 5), "bytes": b,
                       "gbs": round(b / (ms * 1e-3) / 1e9, 2) if ms > 0 else None}
     return rows
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of `kernel` per launch from the committed
+    `ncu --set full` capture of this workload (profiles/r1_ncu_full_summary.json), else None."""
+    try:
+        rows = json.load(open(os.path.join(ROOT, "profiles", "r1_ncu_full_summary.json")))
+        for r in rows:
+            if r["kernel"] == kernel:
+                m = r["metrics"]
+                return int((float(m["dram__bytes_read.sum"]) + float(m["dram__bytes_write.sum"])) * 1e6)
+    except Exception:
+        pass
+    return None
 
 
 def cpu_baseline_port(data, budget_s=10.0):
@@ -311,8 +325,10 @@ def run_ours(args):
         "gpu_launches": launches * args.steps,
         "launches_per_image": launches,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": None,
+                     "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": ncu_traffic(top),
                      "peak_source": peak_src,
+                     "traffic_source": "profiles/r1_ncu_full_summary.json (ncu --set full, cold caches; the "
+                                       "zero-fill stays in L2)",
                      "note": "Huffman kernels are issue/latency bound (bit-serial); see stages"},
         "stages": rows,
         "sum_kernel_ms": round(total_kernel_ms, 5),
