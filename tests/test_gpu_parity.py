@@ -119,3 +119,65 @@ def test_decoder_reuse_and_determinism():
             for c, t in enumerate(planes):
                 assert np.array_equal(t.cpu().numpy()[:, : info.sizes_x[c]], ref["pixels"][c])
     sess.close()
+
+
+@pytest.mark.parametrize("fill", [0x00, 0xFF, 0xA5, "random"])
+def test_scratch_contents_do_not_matter(fill):
+    """The library owns no device memory and clears what it needs itself: whatever the caller's
+    scratch buffer holds before transfer (a previous image, garbage), the result is the same.
+    Also repeats the decode several times on the same transfer (bench.py's device-only loop)."""
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    data = inputs.pillow_jpeg(w=1000, h=750, seed=51, mode="YCbCr", subsampling=2, restart_blocks=9)
+    ref = ob.decode(data)
+    sess = DecodeSession()
+    host = pinned_bytes(data)
+    info = sess.parse(host)
+    if fill == "random":
+        g = torch.Generator(device="cuda").manual_seed(7)
+        sess.scratch.copy_(torch.randint(0, 256, (sess.scratch.numel(),), dtype=torch.uint8,
+                                         device="cuda", generator=g))
+    else:
+        sess.scratch.fill_(fill)
+    sess.transfer()
+    planes = sess.alloc_planes()
+    for rep in range(4):
+        for p in planes:
+            p.fill_(0x5A)
+        sess.decode(planes)
+        torch.cuda.synchronize()
+        for c, t in enumerate(planes):
+            assert np.array_equal(t.cpu().numpy()[:, : info.sizes_x[c]], ref["pixels"][c]), (fill, rep, c)
+    sess.close()
+
+
+def test_many_streams_concurrently():
+    """Independent decoders on independent streams of one device (the batch protocol): kernels
+    of different images overlap on the GPU, look-back tickets and mailboxes are per scratch."""
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    files = [inputs.pillow_jpeg(w=1000 + 16 * i, h=700, seed=60 + i, mode="YCbCr", subsampling=2,
+                                restart_blocks=(0, 5, 63)[i % 3]) for i in range(6)]
+    refs = [ob.decode(d) for d in files]
+    streams = [torch.cuda.Stream() for _ in files]
+    sessions, outs = [], []
+    for data in files:
+        s = DecodeSession()
+        s.parse(pinned_bytes(data))
+        sessions.append(s)
+    torch.cuda.synchronize()
+    for rep in range(3):
+        outs = []
+        for s, st in zip(sessions, streams):
+            with torch.cuda.stream(st):
+                planes = s.alloc_planes()
+            st.synchronize()
+            s.transfer(st)
+            s.decode(planes, st)
+            outs.append(planes)
+        torch.cuda.synchronize()
+        for s, planes, ref in zip(sessions, outs, refs):
+            for c, t in enumerate(planes):
+                assert np.array_equal(t.cpu().numpy()[:, : s.info.sizes_x[c]], ref["pixels"][c])
+    for s in sessions:
+        s.close()
