@@ -34,7 +34,7 @@ struct ScanLayout {
     size_t off_bytes = 0;
     // work area (shared by all scans of the image; scans run back to back on one stream)
     size_t off_ctrl = 0, off_destuffed = 0, off_coef = 0, off_dc = 0;
-    size_t off_entries = 0, off_qpos = 0, off_seg_idx = 0, off_dc_agg = 0;
+    size_t off_entries = 0, off_qpos = 0, off_seg_idx = 0;
     size_t coef_bytes = 0, dc_bytes = 0;
     uint32_t num_chunks = 0, dc_tiles = 0, flag_words = 0, write_ctas = 0;
     uint32_t destuffed_bytes = 0;
@@ -215,9 +215,9 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         L.num_chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
         L.off_ctrl = o; // control block, sync mailboxes and DC flags are cleared as one range
         L.dc_tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
-        L.flag_words = (L.num_chunks + L.dc_tiles + 1u) & ~1u; // keeps the 64-bit words aligned
-        L.write_ctas = g.num_subs / 16u + 1u;                  // huff_write runs >= 16 subsequences per CTA
-        o += align256(sizeof(Control) + ((size_t)L.flag_words + 2u * L.write_ctas) * 4);
+        L.flag_words = (L.num_chunks + 1u) & ~1u; // keeps the 64-bit words behind it aligned
+        L.write_ctas = g.num_subs / 16u + 1u;     // huff_write runs >= 16 subsequences per CTA
+        o += align256(sizeof(Control) + ((size_t)L.flag_words + 4u * L.dc_tiles + 2u * L.write_ctas) * 4);
         L.off_destuffed = o;
         o += align256((size_t)g.num_subs * kSubBytes + 64);
         L.off_coef = o;
@@ -232,8 +232,6 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         o += align256(((size_t)g.num_subs + 1) * 4);
         L.off_seg_idx = o;
         o += align256((size_t)g.num_subs * 4);
-        L.off_dc_agg = o;
-        o += align256(((size_t)g.total_mcus / kDcTile + 1) * kMaxComp * sizeof(int));
         if (o > work_end) work_end = o;
     }
     total_bytes = work_end;
@@ -267,9 +265,9 @@ ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
     b.ctrl = reinterpret_cast<Control*>(base + L.off_ctrl);
     b.chunk_state = reinterpret_cast<uint32_t*>(base + L.off_ctrl + sizeof(Control));
     b.num_chunks = L.num_chunks;
-    b.dc_flags = b.chunk_state + L.num_chunks;
-    b.write_agg = reinterpret_cast<unsigned long long*>(b.chunk_state + L.flag_words);
-    b.clear_words = (uint32_t)(sizeof(Control) / 4) + L.flag_words + 2u * L.write_ctas;
+    b.dc_agg = reinterpret_cast<unsigned long long*>(b.chunk_state + L.flag_words);
+    b.write_agg = b.dc_agg + 2u * (size_t)L.dc_tiles;
+    b.clear_words = (uint32_t)(sizeof(Control) / 4) + L.flag_words + 4u * L.dc_tiles + 2u * L.write_ctas;
     b.destuffed = reinterpret_cast<uint32_t*>(base + L.off_destuffed);
     b.coef = reinterpret_cast<int16_t*>(base + L.off_coef);
     b.coef_bytes = L.coef_bytes;
@@ -278,7 +276,6 @@ ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
     b.entries = reinterpret_cast<SubEntry*>(base + L.off_entries);
     b.qpos = reinterpret_cast<uint32_t*>(base + L.off_qpos);
     b.seg_idx = reinterpret_cast<uint32_t*>(base + L.off_seg_idx);
-    b.dc_agg = reinterpret_cast<int*>(base + L.off_dc_agg);
     return b;
 }
 

@@ -25,7 +25,7 @@ struct ScanBufs {
     Control* ctrl;             // zeroed by destuff
     uint32_t* chunk_state;     // zeroed by destuff: one mailbox per sync warp
     uint32_t num_chunks;
-    uint32_t* dc_flags;        // zeroed by destuff: "aggregate published" flag per DC tile
+    unsigned long long* dc_agg; // zeroed by destuff: two flagged aggregate words per DC tile
     unsigned long long* write_agg; // zeroed by destuff: slot aggregate per huff_write CTA
     uint32_t clear_words;      // Control + mailboxes + DC flags + write aggregates, contiguous
     uint32_t* destuffed;       // big-endian words, segment k at sub_off * kSubWords
@@ -37,7 +37,6 @@ struct ScanBufs {
     SubEntry* entries;         // N
     uint32_t* qpos;            // N: first slot (segment relative) of every subsequence
     uint32_t* seg_idx;         // N
-    int* dc_agg;               // 4 per DC tile
 };
 
 // Optional per-kernel timing (jpeggpu_b200_set_profiling): an event is recorded on the launching

@@ -92,18 +92,20 @@ __device__ __forceinline__ Dc4 block_segmented_scan(Dc4 val, bool head, Dc4* war
     return val;
 }
 
-// polling load: relaxed (an acquire load invalidates the L1 on every poll); the data reads that
-// follow go to L2 (ld.cg), which the releasing store has already reached
-__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p)
+// Tile aggregates travel in two 64-bit words, each {valid:1 | sum of component 2k+1:16 | sum of
+// component 2k:16}: DC arithmetic is modulo 2^16 (the reference accumulates in int16), so the
+// payload fits the flagged word itself and neither a fence nor a second load is needed.
+__device__ __forceinline__ unsigned long long ld_relaxed64(const unsigned long long* p)
 {
-    uint32_t v;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release(uint32_t* p, uint32_t v)
+__device__ __forceinline__ void st_relaxed64(unsigned long long* p, unsigned long long v)
 {
-    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+constexpr unsigned long long kDcValid = 1ull << 32;
 
 // One launch: every CTA scans its tile, publishes the tile aggregate (sum after the tile's last
 // restart boundary) and then sums the aggregates of the tiles between the start of its restart
@@ -111,8 +113,8 @@ __device__ __forceinline__ void st_release(uint32_t* p, uint32_t v)
 // on: a CTA only waits for tiles that started before it (tile numbers are handed out by an
 // atomic ticket, so "earlier tile" == "already running or finished": no deadlock).
 __global__ void __launch_bounds__(kDcTile)
-dc_scan(const ScanGeom g, int16_t* __restrict__ dc, int* __restrict__ agg,
-        uint32_t* __restrict__ flags, uint32_t* __restrict__ ticket)
+dc_scan(const ScanGeom g, int16_t* __restrict__ dc, unsigned long long* __restrict__ agg,
+        uint32_t* __restrict__ ticket)
 {
     __shared__ Dc4 warp_val[kDcTile / 32];
     __shared__ uint32_t warp_flag[kDcTile / 32];
@@ -135,10 +137,11 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, int* __restrict__ agg,
     const bool head = valid && (mcu % ri) == 0;
     Dc4 tail;
     const Dc4 inc = block_segmented_scan(tot, head, warp_val, warp_flag, tail);
-    if (threadIdx.x == 0) {
-#pragma unroll
-        for (int a = 0; a < kMaxComp; ++a) agg[tile * kMaxComp + a] = tail.v[a];
-        st_release(flags + tile, 1u);
+    if (threadIdx.x < 2) {
+        const int k = threadIdx.x * 2;
+        st_relaxed64(agg + 2 * (size_t)tile + threadIdx.x,
+                     kDcValid | ((unsigned long long)(tail.v[k + 1] & 0xffff) << 16) |
+                         (unsigned long long)(tail.v[k] & 0xffff));
     }
     // tiles [first_tile, tile) carry into this one
     const uint32_t seg_start = tile_mcu0 / ri * ri;
@@ -147,10 +150,13 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, int* __restrict__ agg,
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) carry.v[a] = 0;
     for (uint32_t t = first_tile + threadIdx.x; t < tile; t += kDcTile) {
-        while (ld_relaxed(flags + t) == 0u) __nanosleep(20);
-        __threadfence(); // orders the aggregate reads behind the flag (pairs with st.release)
-#pragma unroll
-        for (int a = 0; a < kMaxComp; ++a) carry.v[a] += __ldcg(agg + t * kMaxComp + a);
+        unsigned long long w0, w1;
+        while (((w0 = ld_relaxed64(agg + 2 * (size_t)t)) & kDcValid) == 0) __nanosleep(20);
+        while (((w1 = ld_relaxed64(agg + 2 * (size_t)t + 1)) & kDcValid) == 0) __nanosleep(20);
+        carry.v[0] += (int)(w0 & 0xffffu);
+        carry.v[1] += (int)((w0 >> 16) & 0xffffu);
+        carry.v[2] += (int)(w1 & 0xffffu);
+        carry.v[3] += (int)((w1 >> 16) & 0xffffu);
     }
 #pragma unroll
     for (int a = 0; a < kMaxComp; ++a) {
@@ -199,8 +205,7 @@ cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream,
     }
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
     tm->mark(stream, kIdDcScan);
-    return launch_dependent(dc_scan, tiles, kDcTile, 0, stream, g, b.dc, b.dc_agg, b.dc_flags,
-                            &b.ctrl->dc_ticket);
+    return launch_dependent(dc_scan, tiles, kDcTile, 0, stream, g, b.dc, b.dc_agg, &b.ctrl->dc_ticket);
 }
 
 } // namespace jb2
