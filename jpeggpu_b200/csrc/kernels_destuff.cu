@@ -117,6 +117,39 @@ destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __re
     __syncthreads();
 
     const uint32_t tile_kept = tile_total & 0xffffu;
+    if ((tile_total >> 16) == 0u && (int)seg_base < num_segments) {
+        // No restart marker inside the tile (every tile of a scan without DRI, most tiles
+        // otherwise): one segment, one contiguous run of output bytes.  Whole big-endian words
+        // are assembled from the staged bytes and stored with 4-byte stores; only the run's
+        // unaligned head and tail go byte by byte.
+        const SegDesc sd = segs[seg_base];
+        const uint32_t r0 = kept_base - sd.kept_before;               // index inside the segment
+        const uint32_t d0 = r0 + sd.sub_off * (uint32_t)kSubBytes;    // output position of stage[0]
+        const uint32_t d_end = d0 + tile_kept;
+        const uint32_t w_begin = (d0 + 3u) & ~3u, w_end = d_end & ~3u; // whole words [w_begin, w_end)
+        if (w_begin < w_end) {
+            uint32_t* words = reinterpret_cast<uint32_t*>(dst);
+            for (uint32_t w = w_begin + 4u * threadIdx.x; w < w_end; w += 4u * kDestuffThreads) {
+                const uint32_t o = w - d0;
+                words[w >> 2] = ((uint32_t)stage[o] << 24) | ((uint32_t)stage[o + 1] << 16) |
+                                ((uint32_t)stage[o + 2] << 8) | (uint32_t)stage[o + 3];
+            }
+        }
+        // head [d0, min(w_begin, d_end)) and tail [max(w_end, head end), d_end): < 8 bytes
+        const uint32_t head_end = w_begin < d_end ? w_begin : d_end;
+        const uint32_t tail_begin = w_end > head_end ? w_end : head_end;
+        const uint32_t edge = (head_end - d0) + (d_end - tail_begin);
+        if (threadIdx.x < edge) {
+            const uint32_t d = threadIdx.x < head_end - d0 ? d0 + threadIdx.x
+                                                           : tail_begin + (threadIdx.x - (head_end - d0));
+            dst[d ^ 3u] = stage[d - d0];
+        }
+        if (tile_kept != 0u && r0 + tile_kept == sd.nbytes) { // the segment ends in this tile: pad
+            const uint32_t pad_end = (d_end - 1u + (uint32_t)kSubBytes) / (uint32_t)kSubBytes * (uint32_t)kSubBytes;
+            for (uint32_t z = d_end + threadIdx.x; z < pad_end; z += kDestuffThreads) dst[z ^ 3u] = 0;
+        }
+        return;
+    }
     for (uint32_t o = threadIdx.x; o < tile_kept; o += kDestuffThreads) {
         const uint32_t s = seg_base + seg_delta[o];
         if ((int)s >= num_segments) continue; // cannot happen: host and device rules agree
