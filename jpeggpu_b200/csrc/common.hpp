@@ -108,13 +108,24 @@ struct SegDesc {          // one per restart segment, built by the host walk
     uint32_t src_begin;   // stuffed offset (relative to scan start) of the first byte
 };
 
-struct SubEntry { // per-subsequence sync record: two 8-byte words
+// Threads that share one subsequence in the write pass; the sync pass records the decoder
+// state at the kWriteParts - 1 inner boundaries ("mid states").
+#ifndef JB2_WRITE_PARTS
+#define JB2_WRITE_PARTS 2
+#endif
+constexpr int kWriteParts = JB2_WRITE_PARTS;
+static_assert(kWriteParts == 2 || kWriteParts == 4, "two or four threads per subsequence");
+constexpr int kRecWords = kWriteParts == 2 ? 2 : 4; // 64-bit words per sync record
+
+struct SubEntry { // per-subsequence sync record: kRecWords 8-byte words
     uint16_t g;   // packed entry state (bit 15: first subsequence of a restart segment)
     uint16_t x;   // packed exit state given g
     uint32_t n;   // slots advanced inside the subsequence given g
-    uint16_t gm;  // packed state at the middle of the subsequence (entry of its second half)
-    uint16_t nm;  // slots advanced inside the first half
-    uint32_t pad;
+    // mid[k]: packed state at inner boundary k | slots advanced before it << 16; two per word
+    uint32_t mid[2 * (kRecWords - 1)];
+};
+struct Mids {
+    uint32_t v[kWriteParts - 1];
 };
 constexpr uint16_t kStateHead = 0x8000u;
 constexpr uint16_t kStateMask = 0x7fffu;

@@ -216,7 +216,7 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         L.off_ctrl = o; // control block, sync mailboxes and DC flags are cleared as one range
         L.dc_tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
         L.flag_words = (L.num_chunks + 1u) & ~1u; // keeps the 64-bit words behind it aligned
-        L.write_ctas = g.num_subs / 16u + 1u;     // huff_write runs >= 16 subsequences per CTA
+        L.write_ctas = g.num_subs / (32u / kWriteParts) + 1u; // huff_write runs >= one warp of subsequences per CTA
         o += align256(sizeof(Control) + ((size_t)L.flag_words + 4u * L.dc_tiles + 2u * L.write_ctas) * 4);
         L.off_destuffed = o;
         o += align256((size_t)g.num_subs * kSubBytes + 64);

@@ -35,25 +35,41 @@ JB2_HD uint32_t subs_in_segment(const SegDesc& seg)
 }
 
 // Decode subsequence i of a segment (policy M addresses words relative to the segment start)
-// from packed entry state `gs` (15 bits); returns {gs, exit state, slots advanced} and, in *mid,
-// the state at the middle of the subsequence | slots advanced before it << 16 (the write pass
-// splits every subsequence between two threads there).
+// from packed entry state `gs` (15 bits); returns {gs, exit state, slots advanced} and, in *mids,
+// the state at every inner part boundary | slots advanced before it << 16 (the write pass
+// splits every subsequence between kWriteParts threads there).
 template <class Mem>
 JB2_HD unsigned long long decode_sub(const Mem& M, uint32_t seg_bits, uint32_t i, uint16_t gs,
-                                     uint32_t* mid)
+                                     Mids* mids)
 {
     const uint32_t start = i * (uint32_t)kSubBits;
-    const uint32_t half = start + (uint32_t)kSubBits / 2u;
     const uint32_t sub_end = start + (uint32_t)kSubBits;
     uint32_t p = start + (gs & 31u);
     uint32_t c = (gs >> 5) & 15u;
     const uint32_t z = (gs >> 9) & 63u;
     uint32_t q = z;
-    decode_span<false>(M, p, umin(half, seg_bits), q, c, 0u);
-    *mid = pack_state(p > half ? p - half : 0u, c, q & 63u) | ((q - z) << 16);
+#pragma unroll
+    for (int k = 1; k < kWriteParts; ++k) {
+        const uint32_t edge = start + (uint32_t)(k * (kSubBits / kWriteParts));
+        decode_span<false>(M, p, umin(edge, seg_bits), q, c, 0u);
+        mids->v[k - 1] = pack_state(p > edge ? p - edge : 0u, c, q & 63u) | ((q - z) << 16);
+    }
     decode_span<false>(M, p, umin(sub_end, seg_bits), q, c, 0u);
     const uint32_t o = p > sub_end ? p - sub_end : 0u;
     return pack_entry(gs, pack_state(o, c, q & 63u), q - z);
+}
+
+// The 64-bit words 1.. of a record
+JB2_HD unsigned long long mids_word(const Mids& m, int w)
+{
+    const int k = 2 * w;
+    unsigned long long v = m.v[k];
+    if (k + 1 < kWriteParts - 1) v |= (unsigned long long)m.v[k + 1] << 32;
+    return v;
+}
+JB2_HD uint32_t mid_of(const unsigned long long* rec_words, int k) // rec_words: words 1.. of a record
+{
+    return (uint32_t)(rec_words[k >> 1] >> (32 * (k & 1)));
 }
 
 // huff_link: does the record of subsequence j start where its predecessor stopped?
@@ -63,21 +79,22 @@ JB2_HD bool boundary_ok(unsigned long long prev, unsigned long long cur)
 }
 
 // huff_link fallback: re-decode forward from subsequence j (entry = exit of j-1) until the
-// stored records agree again.  M addresses words relative to the segment start; `lo` / `hi` are
-// the two words of every record (stride 2).  Returns the number of records rewritten.
+// stored records agree again.  M addresses words relative to the segment start; rec_words holds
+// kRecWords 64-bit words per record.  Returns the number of records rewritten.
 template <class Mem, typename WordPtr>
 JB2_HD uint32_t relink_from(const Mem& M, const SegDesc& seg, WordPtr rec_words, uint32_t j)
 {
     const uint32_t seg_bits = seg.nbytes * 8u;
     const uint32_t seg_end = seg.sub_off + subs_in_segment(seg);
-    uint16_t state = entry_x(rec_words[2 * (size_t)(j - 1)]);
+    uint16_t state = entry_x(rec_words[kRecWords * (size_t)(j - 1)]);
     uint32_t rewritten = 0;
     for (uint32_t m = j; m < seg_end; ++m) {
-        if (m != j && (entry_g(rec_words[2 * (size_t)m]) & kStateMask) == state) break;
-        uint32_t mid;
-        const unsigned long long e = decode_sub(M, seg_bits, m - seg.sub_off, state, &mid);
-        rec_words[2 * (size_t)m + 1] = mid;
-        rec_words[2 * (size_t)m] = e;
+        if (m != j && (entry_g(rec_words[kRecWords * (size_t)m]) & kStateMask) == state) break;
+        Mids mids;
+        const unsigned long long e = decode_sub(M, seg_bits, m - seg.sub_off, state, &mids);
+        for (int w = 0; 2 * w < kWriteParts - 1; ++w)
+            rec_words[kRecWords * (size_t)m + 1 + w] = mids_word(mids, w);
+        rec_words[kRecWords * (size_t)m] = e;
         state = entry_x(e);
         ++rewritten;
     }
@@ -96,20 +113,21 @@ JB2_HD bool segment_extent(const ScanGeom& g, uint32_t k, uint32_t& first_du, ui
     return true;
 }
 
-// huff_write body: decode one half (h = 0, 1) of subsequence i from its verified record and hand
-// the coefficients to the policy.  q0 = slot (segment relative) at which the subsequence starts.
+// huff_write body: decode part h (0 .. kWriteParts-1) of subsequence i from its verified record
+// and hand the coefficients to the policy.  q0 = slot (segment relative) at which the
+// subsequence starts; mid = the record's state at the part's start (ignored for h == 0).
 template <class Mem>
-JB2_HD void write_half(const Mem& M, const SegDesc& seg, uint32_t i, uint32_t h,
+JB2_HD void write_part(const Mem& M, const SegDesc& seg, uint32_t i, uint32_t h,
                        unsigned long long rec, uint32_t mid, uint32_t q0, uint32_t q_limit)
 {
-    const uint32_t start = i * (uint32_t)kSubBits;
-    const uint32_t half = start + (uint32_t)kSubBits / 2u;
+    const uint32_t part_bits = (uint32_t)(kSubBits / kWriteParts);
+    const uint32_t begin = i * (uint32_t)kSubBits + h * part_bits;
     const uint32_t seg_bits = seg.nbytes * 8u;
     const uint32_t gs = h ? (mid & 0x7fffu) : (entry_g(rec) & kStateMask);
     uint32_t q = h ? q0 + (mid >> 16) : q0;
     uint32_t c = (gs >> 5) & 15u;
-    uint32_t p = (h ? half : start) + (gs & 31u);
-    const uint32_t end = umin(h ? start + (uint32_t)kSubBits : half, seg_bits);
+    uint32_t p = begin + (gs & 31u);
+    const uint32_t end = umin(begin + part_bits, seg_bits);
     decode_span<true>(M, p, end, q, c, q_limit);
 }
 

@@ -41,10 +41,11 @@ constexpr int kSyncUseful = kSyncWarps * kChunkSubs;            // records writt
 constexpr int kSyncWinSubs = kSyncUseful + kOverlapSubs;        // subsequences staged per CTA
 constexpr int kWinMargin = 4;                                   // words past the last subsequence
 constexpr int kSyncWinWords = kSyncWinSubs * kSubWords + kWinMargin;
-constexpr int kWriteThreads = 320;  // at most; two threads per subsequence
+constexpr int kWriteThreads = 160 * kWriteParts; // at most; kWriteParts threads per subsequence
+constexpr int kSubsPerWarp = 32 / kWriteParts;
 // non-zero coefficients one thread can meet in half a subsequence: each takes >= 2 bits, plus the
 // symbol that straddles the end
-constexpr int kListCap = kSubBits / 4 + 2;
+constexpr int kListCap = kSubBits / (2 * kWriteParts) + 2;
 constexpr int kListStride = kListCap | 1;                          // words between the lanes' lists
 constexpr int kWarpListBytes = (32 * kListStride * 4 + 15) & ~15;
 constexpr int kWarpSmem = kWarpListBytes;                          // shared memory per write warp
@@ -235,8 +236,10 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
 
     // fix-point iteration inside the warp; lanes <= frozen keep their entry state
     uint16_t entry = 0; // cold state == state at a segment start
-    uint32_t mid = 0;
-    unsigned long long rec = active ? decode_sub(M, seg_bits, i, entry, &mid) : 0ull;
+    Mids mids;
+#pragma unroll
+    for (int k = 0; k < kWriteParts - 1; ++k) mids.v[k] = 0;
+    unsigned long long rec = active ? decode_sub(M, seg_bits, i, entry, &mids) : 0ull;
     auto iterate = [&](int frozen) {
         for (;;) {
             const uint16_t px = (uint16_t)__shfl_up_sync(0xffffffffu, (uint32_t)entry_x(rec), 1);
@@ -245,7 +248,7 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
             if (!__any_sync(0xffffffffu, changed)) break;
             if (changed) {
                 entry = want;
-                rec = decode_sub(M, seg_bits, i, entry, &mid);
+                rec = decode_sub(M, seg_bits, i, entry, &mids);
             }
         }
     };
@@ -270,7 +273,7 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
         if (left != 0 && (uint16_t)(left & 0xffffu) != assumed) { // warp-uniform
             if (lane == kOverlapSubs) {
                 entry = (uint16_t)(left & 0xffffu);
-                rec = decode_sub(M, seg_bits, i, entry, &mid);
+                rec = decode_sub(M, seg_bits, i, entry, &mids);
                 atomicAdd(&b.ctrl->relinked, 1u);
             }
             iterate(kOverlapSubs);
@@ -278,9 +281,11 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
         }
     }
     if (active && lane >= kOverlapSubs) {
-        reinterpret_cast<ulonglong2*>(b.entries)[sub] = make_ulonglong2(
+        ulonglong2* out = reinterpret_cast<ulonglong2*>(b.entries) + (size_t)sub * (kRecWords / 2);
+        out[0] = make_ulonglong2(
             pack_entry((uint16_t)(entry | (head ? kStateHead : 0)), entry_x(rec), entry_n(rec)),
-            (unsigned long long)mid);
+            mids_word(mids, 0));
+        if (kRecWords == 4) out[kRecWords / 2 - 1] = make_ulonglong2(mids_word(mids, kWriteParts == 4 ? 1 : 0), 0ull);
         b.seg_idx[sub] = k;
     }
 }
@@ -301,11 +306,11 @@ __device__ __forceinline__ void verify_and_repair(const ScanGeom& g, const ScanB
     for (;;) {
         uint32_t bad = 0;
         for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kHuffThreads)
-            bad |= boundary_ok(entries[2 * (size_t)j - 2], entries[2 * (size_t)j]) ? 0u : 1u;
+            bad |= boundary_ok(entries[kRecWords * (size_t)(j - 1)], entries[kRecWords * (size_t)j]) ? 0u : 1u;
         if (!__syncthreads_or((int)bad)) break;
         uint32_t rewritten = 0;
         for (uint32_t j = stride * (1u + threadIdx.x); j < N; j += stride * kHuffThreads) {
-            if (boundary_ok(entries[2 * (size_t)j - 2], entries[2 * (size_t)j])) continue;
+            if (boundary_ok(entries[kRecWords * (size_t)(j - 1)], entries[kRecWords * (size_t)j])) continue;
             const SegDesc seg = b.segs[*(volatile uint32_t*)(b.seg_idx + j)];
             const GlobalMem M{&st, b.slow, smem_addr(st.recs),
                               b.destuffed + (size_t)seg.sub_off * kSubWords};
@@ -454,7 +459,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
     __shared__ SharedTables st;
     __shared__ uint32_t s_cta;
     const unsigned long long t0 = now_ns();
-    const uint32_t subs_per_cta = blockDim.x / 2;
+    const uint32_t subs_per_cta = blockDim.x / kWriteParts;
     const int win_words = (int)(subs_per_cta * kSubWords + kWinMargin);
     // before huff_sync is done (the control block was cleared two kernels ago): ticket, tables
     if (threadIdx.x == 0) s_cta = atomicAdd(&b.ctrl->write_ticket, 1u);
@@ -465,21 +470,35 @@ huff_write(const ScanGeom g, const ScanBufs b)
     const uint32_t cta = s_cta;
     const uint32_t sub0 = cta * subs_per_cta;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t j = sub0 + (threadIdx.x >> 1), h = threadIdx.x & 1u;
+    const uint32_t j = sub0 + threadIdx.x / kWriteParts, h = threadIdx.x % kWriteParts;
 
     // this thread's record; the CTA's slot prefix is published before the tables are staged, so
     // that the CTAs after this one never wait for it
     unsigned long long rec = 0;
-    uint32_t mid = 0, k = 0;
+    uint32_t mid = 0, mid_next = 0, k = 0; // state at this part's start / at its end (h < last)
     if (j < g.num_subs) {
-        const ulonglong2 r = __ldcg(reinterpret_cast<const ulonglong2*>(b.entries) + j);
+        const ulonglong2* rp = reinterpret_cast<const ulonglong2*>(b.entries) + (size_t)j * (kRecWords / 2);
+        const ulonglong2 r = __ldcg(rp);
         rec = r.x;
-        mid = (uint32_t)r.y;
+        unsigned long long w[kRecWords - 1];
+        w[0] = r.y;
+        if (kRecWords == 4) {
+            const ulonglong2 r2 = __ldcg(rp + 1);
+            w[1] = r2.x;
+            w[kRecWords - 2] = r2.y;
+        }
+        // boundary states by select (a dynamically indexed array would live in local memory)
+#pragma unroll
+        for (int kk = 0; kk < kWriteParts - 1; ++kk) {
+            const uint32_t m = mid_of(w, kk);
+            mid = h == (uint32_t)kk + 1u ? m : mid;
+            mid_next = h == (uint32_t)kk ? m : mid_next;
+        }
         k = __ldcg(b.seg_idx + j);
     }
     const bool is_head = j < g.num_subs && (entry_g(rec) & kStateHead) != 0;
     uint32_t q0 = cta_slot_prefix(cta, h == 0 ? entry_n(rec) : 0u, h == 0 && is_head, b.write_agg);
-    q0 = __shfl_sync(0xffffffffu, q0, lane & ~1); // the odd thread of the pair takes the even one's
+    q0 = __shfl_sync(0xffffffffu, q0, lane & ~(kWriteParts - 1)); // the sub's first thread has it
     if (h == 0 && j < g.num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
 
     stage_window(g, b, (long long)sub0 * kSubWords, win_words);
@@ -494,7 +513,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
         i = j - seg.sub_off;
         if (segment_extent(g, k, first_du, q_limit)) {
             qs = h ? q0 + (mid >> 16) : q0;
-            qe = umin(h ? q0 + entry_n(rec) : q0 + (mid >> 16), q_limit);
+            qe = umin(h + 1 < (uint32_t)kWriteParts ? q0 + (mid_next >> 16) : q0 + entry_n(rec), q_limit);
             has = qe > qs;
         }
     }
@@ -510,7 +529,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
         M.win_addr = smem_addr(s_dyn) + (uint32_t)((int)((long long)seg.sub_off - (long long)sub0) * kSubBytes);
         M.list_ptr = list_addr;
         M.slot0 = qs;
-        write_half(M, seg, i, h, rec, mid, q0, q_limit);
+        write_part(M, seg, i, h, rec, mid, q0, q_limit);
         list_end = M.list_ptr;
     }
     const unsigned long long t2 = now_ns();
@@ -554,10 +573,10 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     const size_t budget = 225 * 1024;
     int warps = kWriteThreads / 32;
     auto write_smem = [&](int w) {
-        return (size_t)(w * 16 * kSubWords + kWinMargin) * 4 + lut_bytes + (size_t)w * kWarpSmem;
+        return (size_t)(w * kSubsPerWarp * kSubWords + kWinMargin) * 4 + lut_bytes + (size_t)w * kWarpSmem;
     };
     while (warps > 1 && write_smem(warps) + 1024 > budget) --warps;
-    const uint32_t subs_per_cta = (uint32_t)warps * 16u;
+    const uint32_t subs_per_cta = (uint32_t)warps * (uint32_t)kSubsPerWarp;
     tm->mark(stream, kIdWrite);
     return launch_dependent(huff_write, (g.num_subs + subs_per_cta - 1) / subs_per_cta, warps * 32,
                             write_smem(warps), stream, g, b);

@@ -116,9 +116,8 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
 
     // huff_sync: one "warp" per chunk, lanes emulated by arrays; chunks in launch order so the
     // left mailbox is always there (one valid schedule of the kernel)
-    std::vector<unsigned long long> entries(2 * (size_t)N); // two words per record
-    auto rec_lo = [&](uint32_t j) -> unsigned long long& { return entries[2 * (size_t)j]; };
-    auto rec_hi = [&](uint32_t j) -> unsigned long long& { return entries[2 * (size_t)j + 1]; };
+    std::vector<unsigned long long> entries(kRecWords * (size_t)N); // kRecWords words per record
+    auto rec_lo = [&](uint32_t j) -> unsigned long long& { return entries[kRecWords * (size_t)j]; };
     std::vector<uint32_t> seg_idx(N), qpos(N + 1);
     const uint32_t chunks = (N + kChunkSubs - 1) / kChunkSubs;
     std::vector<uint32_t> mailbox(chunks, 0);
@@ -131,14 +130,14 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         uint32_t k[32], i[32], seg_bits[32];
         uint16_t entry[32];
         unsigned long long rec[32];
-        uint32_t mid[32];
+        Mids mid[32];
         for (int l = 0; l < 32; ++l) {
             const long long sub = (long long)chunk_first - kOverlapSubs + l;
             active[l] = sub >= 0 && sub < (long long)N;
             head[l] = false;
             entry[l] = 0;
             rec[l] = 0;
-            mid[l] = 0;
+            mid[l] = Mids{};
             if (!active[l]) continue;
             k[l] = find_segment(sp.segs.data(), g.num_segments, (uint32_t)sub);
             const SegDesc& seg = sp.segs[k[l]];
@@ -200,7 +199,8 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                 const uint32_t sub = chunk_first - kOverlapSubs + l;
                 rec_lo(sub) = pack_entry((uint16_t)(entry[l] | (head[l] ? kStateHead : 0)),
                                          entry_x(rec[l]), entry_n(rec[l]));
-                rec_hi(sub) = mid[l];
+                for (int w = 0; 2 * w < kWriteParts - 1; ++w)
+                    entries[kRecWords * (size_t)sub + 1 + w] = mids_word(mid[l], w);
                 seg_idx[sub] = k[l];
             }
     }
@@ -222,7 +222,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         std::vector<unsigned long long> snap(entries); // every thread decides from a snapshot
         uint32_t bad = 0;
         for (uint32_t j = stride; j < N; j += stride)
-            if (!boundary_ok(snap[2 * (size_t)j - 2], snap[2 * (size_t)j])) {
+            if (!boundary_ok(snap[kRecWords * (size_t)(j - 1)], snap[kRecWords * (size_t)j])) {
                 ++bad;
                 const SegDesc& seg = sp.segs[seg_idx[j]];
                 slow_fix += (int)relink_from(mem_of(seg), seg, entries.data(), j);
@@ -253,8 +253,9 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         HostMem m = mem_of(seg);
         m.coef_ = zz.data() + (size_t)first_du * 64;
         m.dc_ = dc.data() + first_du;
-        for (uint32_t h = 0; h < 2; ++h) // the two threads of a subsequence
-            write_half(m, seg, j - seg.sub_off, h, rec_lo(j), (uint32_t)rec_hi(j), qpos[j], q_limit);
+        for (uint32_t h = 0; h < (uint32_t)kWriteParts; ++h) // the threads of a subsequence
+            write_part(m, seg, j - seg.sub_off, h, rec_lo(j),
+                       h ? mid_of(&entries[kRecWords * (size_t)j + 1], (int)h - 1) : 0u, qpos[j], q_limit);
     }
     if (getenv("EMUL_DIAG")) fprintf(stderr, "lut bits %d: long codes in the write pass %ld\n", kLutBits, long_codes);
     // DC: the contract of dc_tile_sums + dc_apply
