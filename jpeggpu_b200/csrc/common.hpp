@@ -180,17 +180,16 @@ struct CoefPlanes {
 // Control block at the front of the per-scan work area (zeroed every decode).
 struct Control {
     uint32_t relinked;    // warp-boundary mismatches healed inside huff_sync
-    uint32_t slow_repairs; // records rewritten by huff_link's sequential fallback
+    uint32_t slow_repairs; // records rewritten by the sequential repair in huff_sync's last CTA
     uint32_t link_rounds;
-    uint32_t link_verify_ns; // device-side phase times of huff_link (diagnostics)
-    uint32_t link_scan_ns;
+    uint32_t link_verify_ns; // tail of the last huff_sync CTA: verification (+ repair) (diagnostics)
+    uint32_t reserved0;
     uint32_t write_stage_ns;  // slowest CTA of huff_write: staging / decode / flush (diagnostics)
     uint32_t write_decode_ns;
     uint32_t write_flush_ns;
     uint32_t sync_stage_ns;   // slowest CTA of huff_sync: staging / fix-point iteration
     uint32_t sync_iter_ns;
-    uint32_t write_tiles_max; // most tiles any warp of huff_write assembled
-    uint32_t write_tiles;     // tiles assembled by all warps
+    uint32_t reserved1[2];
     uint32_t dc_ticket;       // dc_scan: tiles are numbered in the order their CTAs start
     uint32_t write_ticket;    // huff_write: likewise
     uint32_t sync_done;       // huff_sync CTAs that have finished (the last one verifies)

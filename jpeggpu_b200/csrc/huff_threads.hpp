@@ -72,13 +72,14 @@ JB2_HD uint32_t mid_of(const unsigned long long* rec_words, int k) // rec_words:
     return (uint32_t)(rec_words[k >> 1] >> (32 * (k & 1)));
 }
 
-// huff_link: does the record of subsequence j start where its predecessor stopped?
+// verification (last CTA of huff_sync): does the record of subsequence j start where its
+// predecessor stopped?
 JB2_HD bool boundary_ok(unsigned long long prev, unsigned long long cur)
 {
     return (entry_g(cur) & kStateHead) != 0 || (entry_g(cur) & kStateMask) == entry_x(prev);
 }
 
-// huff_link fallback: re-decode forward from subsequence j (entry = exit of j-1) until the
+// repair: re-decode forward from subsequence j (entry = exit of j-1) until the
 // stored records agree again.  M addresses words relative to the segment start; rec_words holds
 // kRecWords 64-bit words per record.  Returns the number of records rewritten.
 template <class Mem, typename WordPtr>

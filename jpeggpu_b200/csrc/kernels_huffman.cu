@@ -21,7 +21,7 @@
 //               The CTA that finishes last verifies every chunk boundary (exit of the left
 //               record == entry of the right one); if all agree, every record is exact by
 //               induction from the segment starts, otherwise it repairs sequentially.
-//   huff_write  decode from the verified entry states, two threads per subsequence (the record
+//   huff_write  decode from the verified entry states, kWriteParts (2) threads per subsequence (the record
 //               holds the state at its middle).  The first output slot of every subsequence is
 //               a segmented prefix sum of the records' slot counts, computed inside this kernel
 //               with a look-back over per-CTA aggregates (replaces the reference's CUB
@@ -174,7 +174,7 @@ struct WriteMem : DevMem {
     }
 };
 
-// Fallback policy of huff_link: tables in shared memory (LUT pool at s_dyn), the scan read from
+// Policy of the repair path: tables in shared memory (LUT pool at s_dyn), the scan read from
 // global memory.
 struct GlobalMem {
     const SharedTables* st;

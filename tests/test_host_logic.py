@@ -108,3 +108,30 @@ def test_link_repairs_damaged_records(case):
     assert st == 0
     assert stats[2] > 0, "the repair path did not run"
     assert np.array_equal(coef, ref["stream"][0])
+
+
+@pytest.mark.parametrize("defs", ["-DJB2_WRITE_PARTS=4", "-DJB2_SUB_BYTES=128 -DJB2_OVERLAP_SUBS=4"])
+def test_emulated_pipeline_tuning_variants(defs):
+    """The compile-time tunables (threads per subsequence in the write pass, subsequence size,
+    overlap) keep the pipeline bit-exact: emulator rebuilt with the definitions in a subprocess."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, numpy as np\n"
+        "import emul_bindings as eb, inputs, oracle_bindings as ob\n"
+        "for kw in (dict(w=643, h=477, seed=3, mode='YCbCr', subsampling=2),\n"
+        "           dict(w=500, h=375, seed=7, mode='YCbCr', subsampling=2, restart_blocks=7),\n"
+        "           dict(w=320, h=240, seed=5, mode='CMYK')):\n"
+        "    data = inputs.pillow_jpeg(**kw)\n"
+        "    ref = ob.decode(data)\n"
+        "    for s in range(ref['info'].num_scans):\n"
+        "        st, coef, stats, _ = eb.decode_scan(data, s, ref['stream'][s].size)\n"
+        "        assert st == 0 and np.array_equal(coef, ref['stream'][s]), (kw, s)\n"
+        "print('ok')\n")
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, JB2_DEFS=defs,
+               PYTHONPATH=os.pathsep.join([here, os.path.join(os.path.dirname(here), "tools"),
+                                           os.path.dirname(here)]))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
