@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <mutex>
 
 namespace jb2 {
 
@@ -70,17 +71,26 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
                              cudaStream_t stream, StageTimer* tm);
 
-// True the first time it is called for the current device with this mask: launch wrappers set
-// their kernel attributes once per device.
-inline bool first_use_on_device(std::atomic<unsigned long long>& mask)
-{
-    int dev = 0;
-    cudaGetDevice(&dev);
-    const unsigned long long bit = 1ull << (dev & 63);
-    if (mask.load(std::memory_order_relaxed) & bit) return false;
-    mask.fetch_or(bit);
-    return true;
-}
+// Runs `f` once per device (launch wrappers set their kernel attributes there).  Concurrent first
+// calls - the host threads of jpeggpu_b200_decode_batch all start at once - wait until the
+// attributes are set: a thread that merely saw "somebody has started" could launch a kernel
+// with 210 KB of dynamic shared memory before the opt-in has happened.
+struct PerDeviceOnce {
+    std::atomic<unsigned long long> done{0};
+    std::mutex lock;
+    template <class F>
+    void run(F&& f)
+    {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        const unsigned long long bit = 1ull << (dev & 63);
+        if (done.load(std::memory_order_acquire) & bit) return;
+        std::lock_guard<std::mutex> guard(lock);
+        if (done.load(std::memory_order_relaxed) & bit) return;
+        f();
+        done.fetch_or(bit, std::memory_order_release);
+    }
+};
 
 // Every kernel of the library asks for the same shared-memory carveout: when consecutive
 // kernels prefer different L1/shared splits the SMs are drained and reconfigured between them,

@@ -199,10 +199,8 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, unsigned long long* __restri
 cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.total_mcus == 0) return cudaSuccess;
-    static std::atomic<unsigned long long> configured{0};
-    if (first_use_on_device(configured)) {
-        prefer_max_shared(dc_scan);
-    }
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(dc_scan); });
     const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
     tm->mark(stream, kIdDcScan);
     return launch_dependent(dc_scan, tiles, kDcTile, 0, stream, g, b.dc, b.dc_agg, &b.ctrl->dc_ticket);

@@ -170,8 +170,8 @@ destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __re
 cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.scan_bytes == 0) return cudaSuccess;
-    static std::atomic<unsigned long long> configured{0};
-    if (first_use_on_device(configured)) prefer_max_shared(destuff_kernel);
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(destuff_kernel); });
     const uint32_t tiles = (g.scan_bytes + kDestuffTile - 1) / kDestuffTile;
     // the control block, the mailboxes and the DC flags are contiguous (planner): one clear range
     const uint32_t clear_words = b.clear_words;

@@ -558,12 +558,12 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
 {
     if (g.num_subs == 0) return cudaSuccess;
     const size_t lut_bytes = (size_t)((g.lut_pool_words + 3) / 4) * 16;
-    static std::atomic<unsigned long long> configured{0};
-    if (first_use_on_device(configured)) {
+    static PerDeviceOnce configured;
+    configured.run([] {
         const int max_smem = 226 * 1024; // 227 KiB per CTA minus the static part
         prefer_max_shared(huff_sync, max_smem);
         prefer_max_shared(huff_write, max_smem);
-    }
+    });
     const uint32_t chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
     tm->mark(stream, kIdSync);
     JB2_LAUNCH(launch_dependent(huff_sync, (chunks + kSyncWarps - 1) / kSyncWarps, kHuffThreads,

@@ -208,8 +208,8 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
 {
     const uint32_t total = g.du_prefix[g.num_comp];
     if (total == 0) return cudaSuccess;
-    static std::atomic<unsigned long long> configured{0};
-    if (first_use_on_device(configured)) prefer_max_shared(idct_kernel);
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(idct_kernel); });
     tm->mark(stream, kIdIdct);
     return launch_dependent(idct_kernel, (total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0,
                             stream, g, b.coef, b.dc, out);
@@ -220,8 +220,8 @@ cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPla
 {
     const uint32_t total = g.du_prefix[g.num_comp] * 8u;
     if (total == 0) return cudaSuccess;
-    static std::atomic<unsigned long long> configured{0};
-    if (first_use_on_device(configured)) prefer_max_shared(transpose_kernel);
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(transpose_kernel); });
     tm->mark(stream, kIdTranspose);
     return launch_dependent(transpose_kernel, (total + 255) / 256, 256, 0, stream, g, b.coef, b.dc,
                             planes);
