@@ -139,7 +139,7 @@ struct jpeggpu_decoder {
             sl.have_event = false;
         }
         if (!sl.have_event) {
-            if (cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming) != cudaSuccess)
+            if (cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming | cudaEventBlockingSync) != cudaSuccess)
                 return JPEGGPU_INTERNAL_ERROR;
             sl.have_event = true;
             sl.event_device = dev;
