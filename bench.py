@@ -220,6 +220,51 @@ def e2e_loop(step_fn, flush_fn, steps, warmup):
     return times
 
 
+def nvjpeg_leg(host, nbytes, flush_fn, steps, warmup):
+    """nvJPEG (local toolkit) on the same file and box: the decoupled OUTPUT_UNCHANGED protocol of
+    the reference's own nvJPEG benchmark (benchmark/benchmark_nvjpeg.hpp:75-185) — stream parse +
+    host phase + transfer + device phase + sync, wall clock, pinned input, L2 flushed between
+    steps.  One entry per backend; a backend nvJPEG refuses is recorded as unavailable."""
+    import torch
+    try:
+        import nvjpeg_bindings as nb
+        if not nb.available():
+            return {"unavailable": "oracle/_ref/libnvjpeg_harness.so not built"}
+    except Exception as e:  # pragma: no cover
+        return {"unavailable": repr(e)}
+    out = {}
+    s = torch.cuda.current_stream().cuda_stream
+    for backend in ("gpu_hybrid", "hybrid", "hardware"):
+        try:
+            nj = nb.NvJpeg(backend)
+        except Exception as e:
+            out[backend] = {"unavailable": str(e)}
+            continue
+        try:
+            ch, ws, hs = nj.info(host.data_ptr(), nbytes)
+            planes = [torch.zeros((hs[c], ws[c]), dtype=torch.uint8, device="cuda") for c in range(ch)]
+            ptrs = [p.data_ptr() for p in planes]
+            pitches = [p.stride(0) for p in planes]
+
+            def step():
+                st = nj.decode(host.data_ptr(), nbytes, ptrs, pitches, s, True)
+                if st:
+                    raise RuntimeError(f"nvjpeg decode status {st}")
+
+            n = steps if backend == "gpu_hybrid" else max(5, min(steps, 10))
+            times = e2e_loop(step, flush_fn, n, warmup)
+            total = sum(times)
+            out[backend] = {"value": round(n * MEGAPIXELS / total, 1), "unit": "MP/s",
+                            "ms_per_image": round(total / n * 1e3, 4), "steps": n}
+        except Exception as e:
+            out[backend] = {"unavailable": str(e)}
+        finally:
+            nj.close()
+    out["protocol"] = ("nvjpegJpegStreamParse+DecodeJpegHost+TransferToDevice+DecodeJpegDevice+sync, "
+                       "NVJPEG_OUTPUT_UNCHANGED, wall clock")
+    return out
+
+
 def run_ours(args):
     import torch
     from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
@@ -450,6 +495,7 @@ def run_reference(args):
     clocks = sampler.stop()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev) / args.steps
     rd.close()
+    nvj = nvjpeg_leg(host, len(data), lambda: flush.fill_(1), args.steps, args.warmup)
     total = sum(times)
     value = args.steps * MEGAPIXELS / total
     cpu = {"value": round(value, 1), "unit": "MP/s", "cores": 1, "kind": "reference",
@@ -468,7 +514,7 @@ def run_reference(args):
                  "e2e": {"value": round(value, 1), "unit": "MP/s", "h2d_bytes_per_step": len(data) + 4 * 64 + 4 * 7168,
                          "d2h_bytes_per_step": 4096,
                          "protocol": "parse_header+get_buffer_size+transfer+decode+4KiB D2H+sync, wall clock"},
-                 "cpu_baseline": cpu, "clocks": clocks})
+                 "cpu_baseline": cpu, "nvjpeg": nvj, "clocks": clocks})
     print(json.dumps(base))
 
 
