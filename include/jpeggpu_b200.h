@@ -56,6 +56,15 @@ enum jpeggpu_status jpeggpu_b200_get_scan_stats(
 /* Bytes jpeggpu_decoder_transfer copies host-to-device for the last parsed image. */
 enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, size_t* bytes);
 
+/* Deferred entropy walk (on by default).  For a file that is one interleaved scan of all frame
+ * components without DRI and that ends with EOI, jpeggpu_decoder_parse_header stops at the scan
+ * header (its cost no longer grows with the file), jpeggpu_decoder_get_buffer_size answers from
+ * upper bounds (<= 0.1 % above the exact plan), and jpeggpu_decoder_transfer enqueues the upload of
+ * the scan bytes first and walks them on the host while the DMA is in flight.  Statuses the walk
+ * can produce are then returned by transfer instead of parse_header.  The reference walks inside
+ * parse_header (src/reader.cpp:443-489); `on` = 0 restores that order. */
+enum jpeggpu_status jpeggpu_b200_set_deferred_walk(jpeggpu_decoder_t decoder, int on);
+
 /* Per-kernel device times. With profiling on, jpeggpu_decoder_decode records a CUDA event on the
  * caller's stream before every kernel; after the caller has synchronised the stream,
  * get_kernel_times returns the milliseconds and launch count per kernel id of the last decode.

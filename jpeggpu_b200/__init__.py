@@ -32,7 +32,7 @@ API_SYMBOLS = [
     "jpeggpu_b200_get_coefficient_size", "jpeggpu_b200_decode_coefficients",
     "jpeggpu_b200_get_scan_stats", "jpeggpu_b200_get_transfer_size",
     "jpeggpu_b200_set_profiling", "jpeggpu_b200_get_kernel_times", "jpeggpu_b200_kernel_name",
-    "jpeggpu_b200_decode_batch", "jpeggpu_b200_parse_batch",
+    "jpeggpu_b200_decode_batch", "jpeggpu_b200_parse_batch", "jpeggpu_b200_set_deferred_walk",
 ]
 
 MAX_KERNELS = 16
@@ -113,6 +113,7 @@ def load_library(path=None):
     L.jpeggpu_b200_get_scan_stats.argtypes = [dec, C.c_int, C.POINTER(ScanStats), C.POINTER(C.c_int)]
     L.jpeggpu_b200_get_transfer_size.argtypes = [dec, C.POINTER(C.c_size_t)]
     L.jpeggpu_b200_set_profiling.argtypes = [dec, C.c_int]
+    L.jpeggpu_b200_set_deferred_walk.argtypes = [dec, C.c_int]
     L.jpeggpu_b200_get_kernel_times.argtypes = [dec, C.POINTER(C.c_float * MAX_KERNELS),
                                                 C.POINTER(C.c_int * MAX_KERNELS)]
     L.jpeggpu_b200_kernel_name.restype = C.c_char_p
@@ -198,6 +199,10 @@ class Decoder:
         _check(self.lib.jpeggpu_b200_get_transfer_size(self.handle, C.byref(n)),
                "jpeggpu_b200_get_transfer_size")
         return n.value
+
+    def set_deferred_walk(self, on):
+        """Deferred entropy walk (include/jpeggpu_b200.h); on by default."""
+        _check(self.lib.jpeggpu_b200_set_deferred_walk(self.handle, int(on)), "jpeggpu_b200_set_deferred_walk")
 
     def set_profiling(self, on):
         _check(self.lib.jpeggpu_b200_set_profiling(self.handle, int(on)), "jpeggpu_b200_set_profiling")

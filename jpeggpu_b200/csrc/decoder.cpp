@@ -149,7 +149,15 @@ struct jpeggpu_decoder {
         return JPEGGPU_SUCCESS;
     }
 
+    // Deferred entropy walk (parser.hpp): parse_header stops at the scan header of a single-scan
+    // file and plans from upper bounds; transfer enqueues the upload of the scan bytes FIRST and
+    // walks them on the host while the DMA runs, then uploads the directories.  Anything that
+    // needs exact counts earlier (scan statistics) just runs the walk on the spot.
+    bool defer_walk = true;
     jpeggpu_status plan_scratch();
+    void derive_counts(int s);
+    jpeggpu_status finish_walk();
+    void fill_directories(int s);
     ScanBufs bufs(int s, void* d_tmp) const;
     jpeggpu_status run(jpeggpu_img* img, int16_t* const* coef_planes, void* d_tmp, size_t tmp_size,
                        cudaStream_t stream);
@@ -193,7 +201,7 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         L.off_segs = off;
         off += align256(sizeof(SegDesc) * (size_t)g.num_segments);
         L.off_tiles = off;
-        off += align256(sizeof(TileDesc) * plan.scans[s].tiles.size());
+        off += align256(sizeof(TileDesc) * (((size_t)g.scan_bytes + kDestuffTile - 1) / kDestuffTile));
     }
     upload_bytes = off;
     transfer_bytes = upload_bytes;
@@ -210,13 +218,9 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         const ScanGeom& g = plan.scans[s].geom;
         const ScanPlan& sp = plan.scans[s];
         size_t o = work_begin;
-        L.num_dus = (uint32_t)g.total_mcus * (uint32_t)g.dus_per_mcu;
-        L.destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
-        L.num_chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
+        (void)sp;
+        derive_counts(s); // from bounds when the walk is deferred: the offsets below only grow
         L.off_ctrl = o; // control block, sync mailboxes and DC flags are cleared as one range
-        L.dc_tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
-        L.flag_words = (L.num_chunks + 1u) & ~1u; // keeps the 64-bit words behind it aligned
-        L.write_ctas = g.num_subs / (32u / kWriteParts) + 1u; // huff_write runs >= one warp of subsequences per CTA
         o += align256(sizeof(Control) + ((size_t)L.flag_words + 4u * L.dc_tiles + 2u * L.write_ctas) * 4);
         L.off_destuffed = o;
         o += align256((size_t)g.num_subs * kSubBytes + 64);
@@ -244,11 +248,49 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         const LutCache& lc = lut_cache[s];
         memcpy(staging + L.off_lut, lc.pool.data(), (size_t)sp.geom.lut_pool_words * 4);
         memcpy(staging + L.off_slow, lc.slow, sizeof(HuffSlow) * (size_t)sp.geom.num_tables);
-        if (!sp.segs.empty())
-            memcpy(staging + L.off_segs, sp.segs.data(), sizeof(SegDesc) * sp.segs.size());
-        if (!sp.tiles.empty())
-            memcpy(staging + L.off_tiles, sp.tiles.data(), sizeof(TileDesc) * sp.tiles.size());
+        if (!plan.walk_pending) fill_directories(s);
     }
+    return JPEGGPU_SUCCESS;
+}
+
+// Counts that follow from the number of subsequences / MCUs of scan s (no offsets).
+void jpeggpu_decoder::derive_counts(int s)
+{
+    ScanLayout& L = layout[s];
+    const ScanPlan& sp = plan.scans[s];
+    const ScanGeom& g = sp.geom;
+    L.num_dus = (uint32_t)g.total_mcus * (uint32_t)g.dus_per_mcu;
+    L.destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
+    L.num_chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
+    L.dc_tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
+    L.flag_words = (L.num_chunks + 1u) & ~1u; // keeps the 64-bit words behind it aligned
+    L.write_ctas = g.num_subs / (32u / kWriteParts) + 1u; // huff_write runs >= one warp of subsequences per CTA
+}
+
+void jpeggpu_decoder::fill_directories(int s)
+{
+    const ScanLayout& L = layout[s];
+    const ScanPlan& sp = plan.scans[s];
+    if (!sp.segs.empty())
+        memcpy(staging + L.off_segs, sp.segs.data(), sizeof(SegDesc) * sp.segs.size());
+    if (!sp.tiles.empty())
+        memcpy(staging + L.off_tiles, sp.tiles.data(), sizeof(TileDesc) * sp.tiles.size());
+}
+
+// Runs the deferred walk (if one is pending): exact geometry into scans[0], counts re-derived
+// inside the offsets planned from the bounds, directories into the staging block.
+jpeggpu_status jpeggpu_decoder::finish_walk()
+{
+    if (!plan.walk_pending) return JPEGGPU_SUCCESS;
+    const uint32_t planned_bytes = plan.scans[0].geom.scan_bytes;
+    const jpeggpu_status st = finish_deferred_walk(plan, log);
+    if (st != JPEGGPU_SUCCESS) {
+        parsed = false;
+        return st;
+    }
+    transfer_bytes -= planned_bytes - plan.scans[0].geom.scan_bytes;
+    derive_counts(0);
+    fill_directories(0);
     return JPEGGPU_SUCCESS;
 }
 
@@ -294,6 +336,7 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
                                     size_t tmp_size, cudaStream_t stream)
 {
     if (!parsed) return JPEGGPU_INVALID_ARGUMENT;
+    if (plan.walk_pending) return JPEGGPU_INVALID_ARGUMENT; // decode without transfer
     if (!d_tmp || tmp_size < total_bytes) return JPEGGPU_INTERNAL_ERROR; // src/util.hpp:66-68
     if ((reinterpret_cast<uintptr_t>(d_tmp) & 255u) != 0) return JPEGGPU_INVALID_ARGUMENT;
     timer.n = 0;
@@ -387,7 +430,7 @@ enum jpeggpu_status jpeggpu_decoder_parse_header(
 #ifdef JB2_PARSE_TIMING
     const auto t0 = std::chrono::steady_clock::now();
 #endif
-    jpeggpu_status st = parse_jpeg(data, size, decoder->plan, decoder->log);
+    jpeggpu_status st = parse_jpeg(data, size, decoder->plan, decoder->log, decoder->defer_walk);
     if (st != JPEGGPU_SUCCESS) return st;
 #ifdef JB2_PARSE_TIMING
     const auto t1 = std::chrono::steady_clock::now();
@@ -434,6 +477,18 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
     if (!d_tmp || tmp_size < decoder->total_bytes) return JPEGGPU_INTERNAL_ERROR;
     const Logger& log = decoder->log;
     uint8_t* base = static_cast<uint8_t*>(d_tmp);
+    if (decoder->plan.walk_pending) {
+        // the big copy goes first; the host walks the same bytes while the DMA engine reads them
+        const ScanPlan& sp = decoder->plan.scans[0];
+        JB2_CUDA(cudaMemcpyAsync(base + decoder->layout[0].off_bytes, decoder->plan.file + sp.begin,
+                                 sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream));
+        const jpeggpu_status st = decoder->finish_walk();
+        if (st != JPEGGPU_SUCCESS) return st;
+        JB2_CUDA(cudaMemcpyAsync(base, decoder->staging, decoder->upload_bytes,
+                                 cudaMemcpyHostToDevice, stream));
+        if (decoder->mark_staging_in_flight(stream) != JPEGGPU_SUCCESS) return JPEGGPU_INTERNAL_ERROR;
+        return JPEGGPU_SUCCESS;
+    }
     JB2_CUDA(cudaMemcpyAsync(base, decoder->staging, decoder->upload_bytes,
                              cudaMemcpyHostToDevice, stream));
     if (decoder->mark_staging_in_flight(stream) != JPEGGPU_SUCCESS) return JPEGGPU_INTERNAL_ERROR;
@@ -511,6 +566,10 @@ enum jpeggpu_status jpeggpu_b200_get_scan_stats(
     jpeggpu_decoder_t decoder, int scan, struct jpeggpu_b200_scan_stats* stats, int* num_scans)
 {
     if (!decoder || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    {
+        const jpeggpu_status st = decoder->finish_walk(); // exact counts need the walk
+        if (st != JPEGGPU_SUCCESS) return st;
+    }
     if (num_scans) *num_scans = decoder->plan.num_scans;
     if (!stats) return JPEGGPU_SUCCESS;
     if (scan < 0 || scan >= decoder->plan.num_scans) return JPEGGPU_INVALID_ARGUMENT;
@@ -538,7 +597,18 @@ enum jpeggpu_status jpeggpu_b200_get_scan_stats(
 enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, size_t* bytes)
 {
     if (!decoder || !bytes || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    {
+        const jpeggpu_status st = decoder->finish_walk();
+        if (st != JPEGGPU_SUCCESS) return st;
+    }
     *bytes = decoder->transfer_bytes;
+    return JPEGGPU_SUCCESS;
+}
+
+enum jpeggpu_status jpeggpu_b200_set_deferred_walk(jpeggpu_decoder_t decoder, int on)
+{
+    if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
+    decoder->defer_walk = on != 0;
     return JPEGGPU_SUCCESS;
 }
 

@@ -37,12 +37,6 @@ struct Cursor {
     }
 };
 
-struct ParseState {
-    bool found_sof = false;
-    HuffSpec huff[kMaxTables]; // index = th * 2 + class, persists across scans (T.81 B.2.4.2)
-    bool comp_coded[kMaxComp] = {};
-};
-
 int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 const char* marker_name(unsigned m)
@@ -412,7 +406,8 @@ jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp)
 }
 
 // Scan header + geometry. Statuses follow src/reader.cpp:305-441.
-jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logger& log)
+jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logger& log,
+                        bool allow_defer)
 {
     if (!st.found_sof) return JPEGGPU_INVALID_JPEG;
     if (cur.left() < 3) return JPEGGPU_INVALID_JPEG;
@@ -506,23 +501,26 @@ jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logg
     cur.u8();
     cur.u8();
     ++plan.num_scans;
+    // Deferred walk (parser.hpp): the one scan of the file, no DRI, EOI at the very end.
+    const size_t left = cur.left();
+    if (allow_defer && plan.num_scans == 1 && ns == plan.num_comp && plan.restart_interval == 0 &&
+        left >= kDeferMinBytes + 2 && left - 2 < (1ull << 31) - 4096 && cur.end[-2] == 0xff &&
+        cur.end[-1] == 0xd9) {
+        sp.begin = (size_t)(cur.p - cur.begin);
+        sp.end = (size_t)(cur.end - 2 - cur.begin);
+        g.scan_bytes = (uint32_t)(sp.end - sp.begin);
+        g.num_segments = 1 + kDeferSegSlack;
+        g.num_subs = (g.scan_bytes + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes + (uint32_t)kDeferSegSlack;
+        plan.walk_pending = true;
+        return JPEGGPU_SUCCESS;
+    }
     return walk_scan(cur, sp);
 }
 
-jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log)
+// The marker loop from the current position to EOI (or to a deferred scan).
+jpeggpu_status marker_loop(Cursor& cur, ImagePlan& plan, const Logger& log, bool allow_defer)
 {
-    Cursor cur{data, data, data + size};
-    ParseState st;
-    plan.width = plan.height = plan.num_comp = 0;
-    plan.restart_interval = 0;
-    plan.num_scans = 0;
-    memset(plan.q_defined, 0, sizeof(plan.q_defined));
-    plan.file = data;
-    plan.file_size = size;
-
-    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
-    if (cur.u8() != 0xff || cur.u8() != 0xd8) return JPEGGPU_INVALID_JPEG;
-    log.log("marker SOI\n");
+    ParseState& st = plan.st;
     for (;;) {
         if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
         if (cur.u8() != 0xff) return JPEGGPU_INVALID_JPEG;
@@ -542,7 +540,8 @@ jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, con
         } else if (m == 0xd9) {
             break;
         } else if (m == 0xda) {
-            s = read_sos(cur, plan, st, log);
+            s = read_sos(cur, plan, st, log, allow_defer);
+            if (s == JPEGGPU_SUCCESS && plan.walk_pending) return s; // resumed by finish_deferred_walk
         } else if (m == 0xdb) {
             s = read_dqt(cur, plan, log);
         } else if (m == 0xdd) {
@@ -561,13 +560,59 @@ jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, con
     return JPEGGPU_SUCCESS;
 }
 
+jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
+                          bool allow_defer)
+{
+    Cursor cur{data, data, data + size};
+    plan.st = ParseState{};
+    plan.walk_pending = false;
+    plan.width = plan.height = plan.num_comp = 0;
+    plan.restart_interval = 0;
+    plan.num_scans = 0;
+    memset(plan.q_defined, 0, sizeof(plan.q_defined));
+    plan.file = data;
+    plan.file_size = size;
+
+    if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
+    if (cur.u8() != 0xff || cur.u8() != 0xd8) return JPEGGPU_INVALID_JPEG;
+    log.log("marker SOI\n");
+    return marker_loop(cur, plan, log, allow_defer);
+}
+
+jpeggpu_status finish_impl(ImagePlan& plan, const Logger& log)
+{
+    ScanPlan& sp = plan.scans[0];
+    const ScanGeom bound = sp.geom;
+    Cursor cur{plan.file + sp.begin, plan.file, plan.file + plan.file_size};
+    plan.walk_pending = false;
+    jpeggpu_status s = walk_scan(cur, sp);
+    if (s != JPEGGPU_SUCCESS) return s;
+    // the scratch plan was sized from the bounds
+    if (sp.geom.scan_bytes > bound.scan_bytes || sp.geom.num_subs > bound.num_subs ||
+        sp.geom.num_segments > bound.num_segments)
+        return JPEGGPU_INVALID_JPEG; // more stray restart markers than the slack allows
+    return marker_loop(cur, plan, log, false);
+}
+
 } // namespace
 
-jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log)
+jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
+                          bool allow_defer)
 {
     try {
-        return parse_impl(data, size, plan, log);
+        return parse_impl(data, size, plan, log, allow_defer);
     } catch (const std::bad_alloc&) {
+        return JPEGGPU_OUT_OF_HOST_MEMORY;
+    }
+}
+
+jpeggpu_status finish_deferred_walk(ImagePlan& plan, const Logger& log)
+{
+    if (!plan.walk_pending) return JPEGGPU_SUCCESS;
+    try {
+        return finish_impl(plan, log);
+    } catch (const std::bad_alloc&) {
+        plan.walk_pending = false;
         return JPEGGPU_OUT_OF_HOST_MEMORY;
     }
 }

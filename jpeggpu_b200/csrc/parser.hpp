@@ -34,6 +34,19 @@ struct ScanPlan {
     int qidx[kMaxComp] = {};     // quantisation table of each scan component
 };
 
+// Marker-parser state that outlives one marker: kept in the plan so that a deferred entropy walk
+// (below) can resume the marker loop where parse_header left it.
+struct ParseState {
+    bool found_sof = false;
+    HuffSpec huff[kMaxTables]; // index = th * 2 + class, persists across scans (T.81 B.2.4.2)
+    bool comp_coded[kMaxComp] = {};
+};
+
+// Deferred walk: capacities planned for a scan whose entropy-coded bytes have not been walked yet
+// (the walk may find fewer bytes / subsequences, never more without failing the image).
+constexpr size_t kDeferMinBytes = 64 * 1024; // below this the walk is too cheap to be worth it
+constexpr int kDeferSegSlack = 16;           // stray RSTn markers tolerated in a scan without DRI
+
 struct ImagePlan {
     int width = 0, height = 0, num_comp = 0;
     int ss_max_x = 0, ss_max_y = 0;
@@ -45,6 +58,10 @@ struct ImagePlan {
     ScanPlan scans[kMaxScans];
     const uint8_t* file = nullptr; // borrowed (include/jpeggpu/jpeggpu.h:83 contract)
     size_t file_size = 0;
+    ParseState st;
+    // true: scans[0] holds an upper-bound geometry (scan_bytes, num_subs, num_segments) and empty
+    // directories; finish_deferred_walk() must run before the directories are used.
+    bool walk_pending = false;
 };
 
 struct Logger {
@@ -53,7 +70,17 @@ struct Logger {
 };
 
 // Parses the whole file. Never throws; allocation failure -> JPEGGPU_OUT_OF_HOST_MEMORY.
-jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log);
+// allow_defer: when the file is one interleaved scan of all frame components without DRI and
+// ends with EOI, stop after the scan header with plan.walk_pending set: the scan is taken to run
+// to the EOI at the end of the file, its geometry holds upper bounds, and the byte walk (the only
+// part of the parse whose cost grows with the file) is left to finish_deferred_walk(), which the
+// decoder runs inside jpeggpu_decoder_transfer while the upload of those bytes is in flight.
+jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
+                          bool allow_defer = false);
+
+// Walks the deferred scan, replaces the bounds in scans[0] by the exact values and resumes the
+// marker loop behind the scan (same statuses as the eager parse).  No-op unless walk_pending.
+jpeggpu_status finish_deferred_walk(ImagePlan& plan, const Logger& log);
 
 } // namespace jb2
 #endif

@@ -105,3 +105,56 @@ def test_parse_statuses(lib):
     assert status(good) == jb.SUCCESS
     assert lib.jpeggpu_decoder_get_buffer_size(d.handle, C.byref(n)) == jb.SUCCESS
     d.cleanup()
+
+
+def _stats_tuple(st):
+    return (st.num_components, st.num_segments, st.dus_per_mcu, st.total_mcus, st.scan_bytes,
+            st.destuffed_bytes, st.num_subsequences, st.num_data_units)
+
+
+@pytest.mark.parametrize("tail", [b"", b"\x00" * 7], ids=["ends_with_eoi", "trailing_bytes"])
+def test_deferred_walk_plans_from_bounds(lib, tail):
+    """include/jpeggpu_b200.h jpeggpu_b200_set_deferred_walk: a single-scan file without DRI that
+    ends with EOI is planned from upper bounds at parse time; the exact counts (after the walk
+    that transfer or a statistics call triggers) equal those of the eager parse.  A file with
+    bytes behind EOI is not eligible and behaves exactly as before."""
+    data = inputs.pillow_jpeg(w=1600, h=1200, seed=5, mode="YCbCr", subsampling=2) + tail
+    assert len(data) > 96 * 1024
+    buf = np.frombuffer(data, dtype=np.uint8)
+    eager, lazy = jb.Decoder(lib), jb.Decoder(lib)
+    eager.set_deferred_walk(False)
+    ie = eager.parse_header(buf.ctypes.data, len(data), keepalive=buf)
+    il = lazy.parse_header(buf.ctypes.data, len(data), keepalive=buf)
+    assert bytes(ie) == bytes(il)
+    exact, bound = eager.get_buffer_size(), lazy.get_buffer_size()
+    if tail:
+        assert bound == exact
+    else:
+        assert exact <= bound <= exact * 1.01
+    assert _stats_tuple(lazy.scan_stats(0)) == _stats_tuple(eager.scan_stats(0))
+    assert abs(lazy.transfer_size() - eager.transfer_size()) <= 4096  # directory capacity slack
+    assert lazy.get_buffer_size() == bound  # the plan does not move after the walk
+    eager.cleanup()
+    lazy.cleanup()
+
+
+def test_deferred_walk_reports_late_errors(lib):
+    """A marker in the middle of the entropy data of an otherwise eligible file: the eager parse
+    sees what follows the scan at parse time, the deferred one when the walk runs."""
+    data = bytearray(inputs.pillow_jpeg(w=1600, h=1200, seed=6, mode="YCbCr", subsampling=2))
+    mid = len(data) // 2
+    data[mid:mid + 2] = b"\xff\xc2"  # SOF2 where entropy data should be
+    buf = np.frombuffer(bytes(data), dtype=np.uint8)
+    eager, lazy = jb.Decoder(lib), jb.Decoder(lib)
+    eager.set_deferred_walk(False)
+    info = jb.ImgInfo()
+    st_e = lib.jpeggpu_decoder_parse_header(eager.handle, C.byref(info), buf.ctypes.data, len(buf))
+    assert st_e != jb.SUCCESS
+    st_l = lib.jpeggpu_decoder_parse_header(lazy.handle, C.byref(info), buf.ctypes.data, len(buf))
+    assert st_l == jb.SUCCESS
+    stats = jb.ScanStats()
+    assert lib.jpeggpu_b200_get_scan_stats(lazy.handle, 0, C.byref(stats), None) == st_e
+    n = C.c_size_t()
+    assert lib.jpeggpu_decoder_get_buffer_size(lazy.handle, C.byref(n)) == jb.INVALID_ARGUMENT
+    eager.cleanup()
+    lazy.cleanup()

@@ -181,3 +181,34 @@ def test_many_streams_concurrently():
                 assert np.array_equal(t.cpu().numpy()[:, : s.info.sizes_x[c]], ref["pixels"][c])
     for s in sessions:
         s.close()
+
+
+@pytest.mark.parametrize("defer", [True, False], ids=["deferred_walk", "eager_walk"])
+@pytest.mark.parametrize("tail", [b"", b"\xff\xd9", b"junk after eoi"], ids=["plain", "double_eoi", "trailing"])
+def test_deferred_and_eager_walk_agree(defer, tail):
+    """jpeggpu_b200_set_deferred_walk: the walk runs inside transfer (overlapping the upload)
+    or inside parse_header; scratch filled with garbage so that nothing depends on the slack
+    between the planned bounds and the exact counts.  `double_eoi`: the file ends with EOI but
+    the scan ends two bytes earlier than the bound assumed."""
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    base = inputs.synth(1920, 1080, 2, 90)
+    if base is None:
+        pytest.skip("stb generator not built")
+    data = base + tail
+    ref = ob.decode(data)
+    assert ref["status"] == 0
+    sess = DecodeSession()
+    sess.dec.set_deferred_walk(defer)
+    for rep in range(2):
+        info = sess.parse(pinned_bytes(data))
+        sess.scratch.fill_(0xC3)
+        sess.transfer()
+        planes = sess.alloc_planes()
+        sess.decode(planes)
+        coefs = sess.decode_coefficients()
+        torch.cuda.synchronize()
+        for c, t in enumerate(planes):
+            assert np.array_equal(t.cpu().numpy()[:, : info.sizes_x[c]], ref["pixels"][c]), (rep, c)
+            assert np.array_equal(coefs[c].cpu().numpy(), ref["planes"][c]), (rep, c)
+    sess.close()
