@@ -25,6 +25,8 @@ def main():
         path = name
     data = open(path, "rb").read()
     sess = DecodeSession("cuda:0")
+    if os.environ.get("JB2_EAGER_WALK") == "1":  # A/B of jpeggpu_b200_set_deferred_walk
+        sess.dec.set_deferred_walk(False)
     host = pinned_bytes(data)
     sess.parse(host)
     planes = sess.alloc_planes()
