@@ -34,6 +34,36 @@ enum jpeggpu_status jpeggpu_b200_decode_coefficients(
     size_t tmp_size,
     cudaStream_t stream);
 
+/* ---- optional output-side fusion: interleaved RGB ---------------------------
+ * The reference's contract ends at unconverted planes; its callers convert on the CPU with
+ * conv_to_rgbi (util/util.h:33-107: chroma replication, float BT.601 full-range matrix, roundf,
+ * clamp; example/example_tool.c calls it before writing the PNG).  These two calls produce
+ * byte-identical output on the device.
+ *
+ * jpeggpu_b200_decode_rgbi: like jpeggpu_decoder_decode, but the IDCT kernel converts in
+ * registers and writes height rows of width RGB triples to d_rgb (device, `pitch` bytes per row,
+ * pitch >= 3*width); the planes are never materialised.  Accepts what conv_to_rgbi accepts and
+ * the fused kernel can see in one pass: one grey component, or Y + 1x1 Cb + 1x1 Cr coded in one
+ * interleaved scan; anything else -> JPEGGPU_NOT_SUPPORTED (decode to planes, then convert). */
+enum jpeggpu_status jpeggpu_b200_decode_rgbi(
+    jpeggpu_decoder_t decoder,
+    uint8_t* d_rgb,
+    int pitch,
+    void* d_tmp,
+    size_t tmp_size,
+    cudaStream_t stream);
+
+/* conv_to_rgbi on device planes (as produced by jpeggpu_decoder_decode; info as filled by
+ * jpeggpu_decoder_parse_header): sizes_x[0] x sizes_y[0] pixels to d_rgb.  1 or 3 components,
+ * chroma factors 1x1 (conv_to_rgbi mis-indexes other chroma factors; refused here), else
+ * JPEGGPU_NOT_SUPPORTED.  Enqueues one kernel on `stream`. */
+enum jpeggpu_status jpeggpu_b200_convert_rgbi(
+    const struct jpeggpu_img* planes,
+    const struct jpeggpu_img_info* info,
+    uint8_t* d_rgb,
+    int pitch,
+    cudaStream_t stream);
+
 struct jpeggpu_b200_scan_stats {
     int num_components;
     int num_segments;          /* restart segments */

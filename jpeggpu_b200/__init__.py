@@ -33,6 +33,7 @@ API_SYMBOLS = [
     "jpeggpu_b200_get_scan_stats", "jpeggpu_b200_get_transfer_size",
     "jpeggpu_b200_set_profiling", "jpeggpu_b200_get_kernel_times", "jpeggpu_b200_kernel_name",
     "jpeggpu_b200_decode_batch", "jpeggpu_b200_parse_batch", "jpeggpu_b200_set_deferred_walk",
+    "jpeggpu_b200_decode_rgbi", "jpeggpu_b200_convert_rgbi",
 ]
 
 MAX_KERNELS = 16
@@ -110,6 +111,9 @@ def load_library(path=None):
     L.jpeggpu_b200_get_coefficient_size.argtypes = [dec, C.POINTER(C.c_int * 4), C.POINTER(C.c_int * 4)]
     L.jpeggpu_b200_decode_coefficients.argtypes = [dec, C.POINTER(C.c_void_p * 4), C.c_void_p,
                                                    C.c_size_t, C.c_void_p]
+    L.jpeggpu_b200_decode_rgbi.argtypes = [dec, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+    L.jpeggpu_b200_convert_rgbi.argtypes = [C.POINTER(Img), C.POINTER(ImgInfo), C.c_void_p, C.c_int,
+                                            C.c_void_p]
     L.jpeggpu_b200_get_scan_stats.argtypes = [dec, C.c_int, C.POINTER(ScanStats), C.POINTER(C.c_int)]
     L.jpeggpu_b200_get_transfer_size.argtypes = [dec, C.POINTER(C.c_size_t)]
     L.jpeggpu_b200_set_profiling.argtypes = [dec, C.c_int]
@@ -125,6 +129,17 @@ def load_library(path=None):
     if path is None:
         _lib = L
     return L
+
+
+def convert_rgbi(planes, pitches, info, d_rgb, pitch, stream=0, lib=None):
+    """jpeggpu_b200_convert_rgbi: device planes (as decode() wrote them) -> interleaved RGB."""
+    lib = lib or load_library()
+    img = Img()
+    for c, (p, pt) in enumerate(zip(planes, pitches)):
+        img.image[c] = p
+        img.pitch[c] = pt
+    _check(lib.jpeggpu_b200_convert_rgbi(C.byref(img), C.byref(info), d_rgb, pitch, stream),
+           "jpeggpu_b200_convert_rgbi")
 
 
 def _check(status, where):
@@ -181,6 +196,11 @@ class Decoder:
         arr = (C.c_void_p * 4)(*(list(planes) + [None] * (4 - len(planes))))
         _check(self.lib.jpeggpu_b200_decode_coefficients(self.handle, C.byref(arr), d_tmp, tmp_size,
                                                          stream), "jpeggpu_b200_decode_coefficients")
+
+    def decode_rgbi(self, d_rgb, pitch, d_tmp, tmp_size, stream=0):
+        """Fused IDCT + chroma replication + YCbCr->RGB (jpeggpu_b200_decode_rgbi)."""
+        _check(self.lib.jpeggpu_b200_decode_rgbi(self.handle, d_rgb, pitch, d_tmp, tmp_size, stream),
+               "jpeggpu_b200_decode_rgbi")
 
     def num_scans(self):
         n = C.c_int()

@@ -172,6 +172,23 @@ struct OutPlanes {
     uint8_t q[kMaxComp][64]; // natural-order quantisation table per scan component
 };
 
+// Interleaved RGB destination of the fused IDCT + colour conversion (jpeggpu_b200_decode_rgbi).
+struct RgbOut {
+    uint8_t* ptr;  // 3 bytes per pixel, rows `pitch` bytes apart
+    int pitch;
+    int width, height;
+    int cy, cb, cr; // scan component that carries Y / Cb / Cr; cb < 0: single grey component
+    uint8_t q[kMaxComp][64]; // natural-order quantisation table per scan component
+};
+
+// Planes that already exist (jpeggpu_b200_convert_rgbi): frame component order.
+struct PlanarIn {
+    const uint8_t* ptr[3];
+    int pitch[3];
+    int num_comp;  // 1 or 3
+    int ssx, ssy;  // luma samples per chroma sample
+};
+
 struct CoefPlanes {
     int16_t* ptr[kMaxComp]; // indexed by scan component
     int stride[kMaxComp];   // in int16 elements

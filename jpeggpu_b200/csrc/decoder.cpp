@@ -159,7 +159,9 @@ struct jpeggpu_decoder {
     jpeggpu_status finish_walk();
     void fill_directories(int s);
     ScanBufs bufs(int s, void* d_tmp) const;
-    jpeggpu_status run(jpeggpu_img* img, int16_t* const* coef_planes, void* d_tmp, size_t tmp_size,
+    jpeggpu_status rgbi_layout(int* cy, int* cb, int* cr) const;
+    jpeggpu_status run(jpeggpu_img* img, int16_t* const* coef_planes, uint8_t* rgb, int rgb_pitch,
+                       void* d_tmp, size_t tmp_size,
                        cudaStream_t stream);
 };
 
@@ -332,8 +334,30 @@ ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
     } while (0)
 
 // The stage sequence of one image (reference decode_impl<true>, src/decoder.cpp:216-325).
-jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_planes, void* d_tmp,
-                                    size_t tmp_size, cudaStream_t stream)
+// Which scan components carry Y / Cb / Cr when the image can go through idct_rgbi_kernel: one
+// scan holding every frame component, grey or three components with 1x1 chroma (the layouts the
+// reference's conv_to_rgbi accepts, util/util.h:43-69, minus chroma factors other than 1x1, which
+// it mis-indexes).  *cb = -1 for grey.
+jpeggpu_status jpeggpu_decoder::rgbi_layout(int* cy, int* cb, int* cr) const
+{
+    if (plan.num_comp != 1 && plan.num_comp != 3) return JPEGGPU_NOT_SUPPORTED;
+    if (plan.num_scans != 1 || plan.scans[0].geom.num_comp != plan.num_comp) return JPEGGPU_NOT_SUPPORTED;
+    const ScanGeom& g = plan.scans[0].geom;
+    int at[3] = {-1, -1, -1};
+    for (int a = 0; a < g.num_comp; ++a) at[g.frame_comp[a]] = a;
+    *cy = at[0];
+    *cb = *cr = -1;
+    if (plan.num_comp == 1) return JPEGGPU_SUCCESS;
+    if (at[0] < 0 || at[1] < 0 || at[2] < 0) return JPEGGPU_NOT_SUPPORTED;
+    if (g.ssx[at[1]] != 1 || g.ssy[at[1]] != 1 || g.ssx[at[2]] != 1 || g.ssy[at[2]] != 1)
+        return JPEGGPU_NOT_SUPPORTED;
+    *cb = at[1];
+    *cr = at[2];
+    return JPEGGPU_SUCCESS;
+}
+
+jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_planes, uint8_t* rgb,
+                                    int rgb_pitch, void* d_tmp, size_t tmp_size, cudaStream_t stream)
 {
     if (!parsed) return JPEGGPU_INVALID_ARGUMENT;
     if (plan.walk_pending) return JPEGGPU_INVALID_ARGUMENT; // decode without transfer
@@ -363,6 +387,18 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
                 memcpy(out.q[a], plan.qtables[sp.qidx[a]], 64);
             }
             JB2_CUDA(launch_idct(g, b, out, stream, &timer));
+        }
+        if (rgb) {
+            RgbOut out;
+            memset(&out, 0, sizeof(out));
+            const jpeggpu_status st = rgbi_layout(&out.cy, &out.cb, &out.cr);
+            if (st != JPEGGPU_SUCCESS) return st;
+            out.ptr = rgb;
+            out.pitch = rgb_pitch;
+            out.width = plan.width;
+            out.height = plan.height;
+            for (int a = 0; a < g.num_comp; ++a) memcpy(out.q[a], plan.qtables[sp.qidx[a]], 64);
+            JB2_CUDA(launch_idct_rgbi(g, b, out, stream, &timer));
         }
         if (coef_planes) {
             CoefPlanes cp;
@@ -511,7 +547,7 @@ enum jpeggpu_status jpeggpu_decoder_decode(
     const ImagePlan& p = decoder->plan;
     for (int c = 0; c < p.num_comp; ++c)
         if (!img->image[c] || img->pitch[c] < p.comps[c].size_x) return JPEGGPU_INVALID_ARGUMENT;
-    return decoder->run(img, nullptr, d_tmp, tmp_size, stream);
+    return decoder->run(img, nullptr, nullptr, 0, d_tmp, tmp_size, stream);
 }
 
 // src/jpeggpu.cpp:149-159
@@ -559,7 +595,59 @@ enum jpeggpu_status jpeggpu_b200_decode_coefficients(
     for (int c = 0; c < decoder->plan.num_comp; ++c)
         if (!d_planes[c] || (reinterpret_cast<uintptr_t>(d_planes[c]) & 15u))
             return JPEGGPU_INVALID_ARGUMENT;
-    return decoder->run(nullptr, d_planes, d_tmp, tmp_size, stream);
+    return decoder->run(nullptr, d_planes, nullptr, 0, d_tmp, tmp_size, stream);
+}
+
+enum jpeggpu_status jpeggpu_b200_decode_rgbi(
+    jpeggpu_decoder_t decoder, uint8_t* d_rgb, int pitch, void* d_tmp, size_t tmp_size,
+    cudaStream_t stream)
+{
+    if (!decoder || !d_rgb || !decoder->parsed) return JPEGGPU_INVALID_ARGUMENT;
+    if ((long long)pitch < 3ll * decoder->plan.width) return JPEGGPU_INVALID_ARGUMENT;
+    int cy, cb, cr;
+    const jpeggpu_status st = decoder->rgbi_layout(&cy, &cb, &cr);
+    if (st != JPEGGPU_SUCCESS) return st;
+    return decoder->run(nullptr, nullptr, d_rgb, pitch, d_tmp, tmp_size, stream);
+}
+
+enum jpeggpu_status jpeggpu_b200_convert_rgbi(
+    const struct jpeggpu_img* planes, const struct jpeggpu_img_info* info, uint8_t* d_rgb,
+    int pitch, cudaStream_t stream)
+{
+    if (!planes || !info || !d_rgb) return JPEGGPU_INVALID_ARGUMENT;
+    const int nc = info->num_components;
+    if (nc != 1 && nc != 3) return JPEGGPU_NOT_SUPPORTED; // util/util.h:43-46
+    const jpeggpu_subsampling& ss = info->subsampling;
+    PlanarIn in;
+    memset(&in, 0, sizeof(in));
+    in.num_comp = nc;
+    in.ssx = in.ssy = 1;
+    if (nc == 3) {
+        // util/util.h:61-69 refuses subsampled luma and unequal chroma; chroma factors other
+        // than 1x1 (which it would mis-index) are refused here as well
+        if (ss.x[1] != 1 || ss.y[1] != 1 || ss.x[2] != 1 || ss.y[2] != 1) return JPEGGPU_NOT_SUPPORTED;
+        if (ss.x[0] < 1 || ss.x[0] > 4 || ss.y[0] < 1 || ss.y[0] > 4) return JPEGGPU_INVALID_ARGUMENT;
+        in.ssx = ss.x[0];
+        in.ssy = ss.y[0];
+    }
+    const int w = info->sizes_x[0], h = info->sizes_y[0];
+    if (w < 0 || h < 0 || (long long)pitch < 3ll * w) return JPEGGPU_INVALID_ARGUMENT;
+    for (int c = 0; c < nc; ++c) {
+        if (!planes->image[c] || planes->pitch[c] < info->sizes_x[c]) return JPEGGPU_INVALID_ARGUMENT;
+        in.ptr[c] = planes->image[c];
+        in.pitch[c] = planes->pitch[c];
+    }
+    RgbOut out;
+    memset(&out, 0, sizeof(out));
+    out.ptr = d_rgb;
+    out.pitch = pitch;
+    out.width = w;
+    out.height = h;
+    if (launch_ycc_to_rgbi(in, out, stream) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return JPEGGPU_INTERNAL_ERROR;
+    }
+    return JPEGGPU_SUCCESS;
 }
 
 enum jpeggpu_status jpeggpu_b200_get_scan_stats(
@@ -652,7 +740,7 @@ const char* jpeggpu_b200_kernel_name(int id)
 {
     static const char* names[kIdCount] = {
         "destuff_kernel", "huff_sync", "huff_write", "dc_scan",
-        "idct_kernel", "transpose_kernel"};
+        "idct_kernel", "transpose_kernel", "idct_rgbi_kernel"};
     return id >= 0 && id < kIdCount ? names[id] : "";
 }
 

@@ -43,7 +43,7 @@ struct ScanBufs {
 // Optional per-kernel timing (jpeggpu_b200_set_profiling): an event is recorded on the launching
 // stream before every kernel and one after the last; off by default and absent from timed runs.
 enum KernelId {
-    kIdDestuff = 0, kIdSync, kIdWrite, kIdDcScan, kIdIdct, kIdTranspose,
+    kIdDestuff = 0, kIdSync, kIdWrite, kIdDcScan, kIdIdct, kIdTranspose, kIdIdctRgbi,
     kIdCount
 };
 
@@ -70,6 +70,11 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
                         cudaStream_t stream, StageTimer* tm);
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
                              cudaStream_t stream, StageTimer* tm);
+// Optional output-side fusion: IDCT straight to interleaved RGB, and the same
+// conversion (reference util/util.h:33-107) on existing planes.
+cudaError_t launch_idct_rgbi(const ScanGeom& g, const ScanBufs& b, const RgbOut& out,
+                             cudaStream_t stream, StageTimer* tm);
+cudaError_t launch_ycc_to_rgbi(const PlanarIn& in, const RgbOut& out, cudaStream_t stream);
 
 // Runs `f` once per device (launch wrappers set their kernel attributes there).  Concurrent first
 // calls - the host threads of jpeggpu_b200_decode_batch all start at once - wait until the

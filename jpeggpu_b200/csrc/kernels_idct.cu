@@ -105,6 +105,38 @@ __device__ __forceinline__ bool locate(const ScanGeom& g, uint32_t t, DuPos& pos
     return true;
 }
 
+// Loads data unit `du` (zig-zag order), dequantises with the natural-order table `q` and runs both
+// IDCT passes in registers: v[y][x] is the sample before the level shift.
+__device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
+                                          const int16_t* __restrict__ dc, uint32_t du,
+                                          const int* q, int (&v)[8][8])
+{
+    const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)du * 64);
+    // the buffer holds every data unit in zig-zag order: un-zig-zag while loading (register
+    // indices are compile-time constants after unrolling)
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const uint4 w = src[r];
+        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int lo = (int)(short)(ww[k] & 0xffffu);
+            const int hi = (int)(short)(ww[k] >> 16);
+            const int n0 = natural_of(r * 8 + 2 * k), n1 = natural_of(r * 8 + 2 * k + 1);
+            // src/idct.cu:178-180: the product is stored as int16
+            v[n0 >> 3][n0 & 7] = (int)(short)(lo * q[n0]);
+            v[n1 >> 3][n1 & 7] = (int)(short)(hi * q[n1]);
+        }
+    }
+    v[0][0] = (int)(short)((int)dc[du] * q[0]); // absolute DC lives in the compact array
+#pragma unroll
+    for (int x = 0; x < 8; ++x)
+        idct8(v[0][x], v[1][x], v[2][x], v[3][x], v[4][x], v[5][x], v[6][x], v[7][x]);
+#pragma unroll
+    for (int y = 0; y < 8; ++y)
+        idct8(v[y][0], v[y][1], v[y][2], v[y][3], v[y][4], v[y][5], v[y][6], v[y][7]);
+}
+
 constexpr int kIdctThreads = 128;
 #ifndef JB2_IDCT_MIN_CTAS
 #define JB2_IDCT_MIN_CTAS 6
@@ -123,31 +155,8 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
     DuPos pos;
     if (!locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos)) return;
     const int a = pos.comp;
-    const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)pos.du * 64);
-    // the buffer holds every data unit in zig-zag order: un-zig-zag while loading (register
-    // indices are compile-time constants after unrolling)
     int v[8][8];
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-        const uint4 w = src[r];
-        const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int lo = (int)(short)(ww[k] & 0xffffu);
-            const int hi = (int)(short)(ww[k] >> 16);
-            const int n0 = natural_of(r * 8 + 2 * k), n1 = natural_of(r * 8 + 2 * k + 1);
-            // src/idct.cu:178-180: the product is stored as int16
-            v[n0 >> 3][n0 & 7] = (int)(short)(lo * s_q[a][n0]);
-            v[n1 >> 3][n1 & 7] = (int)(short)(hi * s_q[a][n1]);
-        }
-    }
-    v[0][0] = (int)(short)((int)dc[pos.du] * s_q[a][0]); // absolute DC lives in the compact array
-#pragma unroll
-    for (int x = 0; x < 8; ++x)
-        idct8(v[0][x], v[1][x], v[2][x], v[3][x], v[4][x], v[5][x], v[6][x], v[7][x]);
-#pragma unroll
-    for (int y = 0; y < 8; ++y)
-        idct8(v[y][0], v[y][1], v[y][2], v[y][3], v[y][4], v[y][5], v[y][6], v[y][7]);
+    load_idct(coef, dc, pos.du, s_q[a], v);
 
     const int x0 = pos.bx * 8, y0 = pos.by * 8;
     const int size_x = g.size_x[a], size_y = g.size_y[a];
@@ -201,6 +210,202 @@ transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef,
     *reinterpret_cast<uint4*>(dst) = make_uint4(px[0], px[1], px[2], px[3]);
 }
 
+// ---- optional output-side fusion: chroma replication + YCbCr -> interleaved RGB ----------------
+// (the step the reference's callers run on the CPU, util/util.h:33-107.)
+// The arithmetic is the reference's float expression, operation for operation, with explicit
+// round-to-nearest multiplies and adds so that nvcc cannot contract them into FMAs (a CPU build
+// of util.h without FMA contraction is the parity target): r = y + 1.402 (cr-128),
+// g = (y - .344136 (cb-128)) - .714136 (cr-128), b = y + 1.772 (cb-128), roundf, clamp 0..255.
+struct ChromaTerms {
+    float rr, gb, gr, bb;
+};
+__device__ __forceinline__ ChromaTerms chroma_terms(int cb, int cr)
+{
+    const float fb = __fsub_rn((float)cb, 128.f), fr = __fsub_rn((float)cr, 128.f);
+    ChromaTerms t;
+    t.rr = __fmul_rn(1.402f, fr);
+    t.gb = __fmul_rn(.344136f, fb);
+    t.gr = __fmul_rn(.714136f, fr);
+    t.bb = __fmul_rn(1.772f, fb);
+    return t;
+}
+// roundf() without the clamp: the packing instruction saturates to 0..255 afterwards
+__device__ __forceinline__ int round_away(float x) { return __float2int_rz(roundf(x)); }
+__device__ __forceinline__ void ycc_pixel(int cy, const ChromaTerms& t, int& r, int& g, int& b)
+{
+    const float fy = (float)cy;
+    r = round_away(__fadd_rn(fy, t.rr));
+    g = round_away(__fsub_rn(__fsub_rn(fy, t.gb), t.gr));
+    b = round_away(__fadd_rn(fy, t.bb));
+}
+
+// Stores pixels [0, n) of eight RGB triples at `row`; vec: row is 8-byte aligned and n == 8.
+__device__ __forceinline__ void store_rgb8(uint8_t* row, const int (&r)[8], const int (&g)[8],
+                                           const int (&b)[8], bool vec, int n)
+{
+    if (vec) {
+        uint2* d = reinterpret_cast<uint2*>(row);
+        d[0] = make_uint2(pack_sat_u8(r[0], g[0], b[0], r[1]), pack_sat_u8(g[1], b[1], r[2], g[2]));
+        d[1] = make_uint2(pack_sat_u8(b[2], r[3], g[3], b[3]), pack_sat_u8(r[4], g[4], b[4], r[5]));
+        d[2] = make_uint2(pack_sat_u8(g[5], b[5], r[6], g[6]), pack_sat_u8(b[6], r[7], g[7], b[7]));
+    } else {
+#pragma unroll
+        for (int x = 0; x < 8; ++x)
+            if (x < n) {
+                row[3 * x + 0] = (uint8_t)min(max(r[x], 0), 255);
+                row[3 * x + 1] = (uint8_t)min(max(g[x], 0), 255);
+                row[3 * x + 2] = (uint8_t)min(max(b[x], 0), 255);
+            }
+    }
+}
+
+// idct_rgbi_kernel: fused dequantise + IDCT + chroma replication + colour conversion for an image
+// that is ONE interleaved scan of Y (ssx x ssy data units per MCU) and 1x1 Cb, Cr - or a single
+// grey component.  A CTA owns `mcus` horizontally adjacent MCUs.  Thread order: the Y data units
+// first, by (row inside the MCU, MCU, column inside the MCU) so that a warp holds horizontally
+// adjacent blocks and its three 8-byte stores per row cover 768 contiguous bytes; then `mcus` Cb
+// threads and `mcus` Cr threads.  Every thread runs the IDCT of its data unit; the chroma threads
+// leave their clamped samples in shared memory (72-byte stride per data unit: conflict-free 8-byte
+// row reads), the Y threads convert and store.  The planes are never written.
+// Algorithmic bytes: 2*C coefficient bytes read + 3*W*H bytes written.
+constexpr int kRgbMcus = 32;      // MCUs per CTA of a colour image
+constexpr int kRgbGreyMcus = 128; // data units per CTA of a grey image
+constexpr int kRgbMaxThreads = kRgbMcus * kMaxDuPerMcu;
+
+template <int SSX> // Y data units per MCU in x when 1 or 2; 0: any (runtime g.ssx)
+__global__ void __launch_bounds__(kRgbMaxThreads)
+idct_rgbi_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
+                 const RgbOut out)
+{
+    __shared__ int s_q[kMaxComp][64];
+    __shared__ unsigned long long s_c[2][kRgbMcus][9];
+    for (int i = threadIdx.x; i < kMaxComp * 64; i += blockDim.x)
+        s_q[i >> 6][i & 63] = out.q[i >> 6][i & 63];
+    grid_dependency_wait();
+    grid_dependency_trigger();
+    __syncthreads();
+
+    const bool grey = out.cb < 0;
+    const int mcus = grey ? kRgbGreyMcus : kRgbMcus;
+    const int ssx = SSX ? SSX : g.ssx[out.cy], ssy = g.ssy[out.cy];
+    const int groups_x = (g.mcus_x + mcus - 1) / mcus;
+    const int my = blockIdx.x / groups_x;
+    const int mx0 = (blockIdx.x - my * groups_x) * mcus;
+    const int t = threadIdx.x;
+    const int y_threads = mcus * ssx * ssy;
+    const bool is_y = t < y_threads;
+    int a, m, ix = 0, iy = 0, k = 0;
+    if (is_y) {
+        const int per_row = mcus * ssx;
+        iy = t / per_row;
+        const int rem = t - iy * per_row;
+        m = rem / ssx;
+        ix = rem - m * ssx;
+        a = out.cy;
+    } else {
+        k = (t - y_threads) / mcus;
+        m = (t - y_threads) - k * mcus;
+        a = k ? out.cr : out.cb;
+    }
+    const int mx = mx0 + m;
+    const bool valid = mx < g.mcus_x;
+    int v[8][8];
+    if (valid) {
+        const uint32_t du = ((uint32_t)my * (uint32_t)g.mcus_x + (uint32_t)mx) * (uint32_t)g.dus_per_mcu +
+                            (uint32_t)(g.du_off[a] + iy * ssx + ix);
+        load_idct(coef, dc, du, s_q[a], v);
+        if (!is_y) {
+#pragma unroll
+            for (int y = 0; y < 8; ++y) {
+                int s[8];
+#pragma unroll
+                for (int x = 0; x < 8; ++x) s[x] = (int)(short)(v[y][x] + 128);
+                s_c[k][m][y] = (unsigned long long)pack_sat_u8(s[0], s[1], s[2], s[3]) |
+                               ((unsigned long long)pack_sat_u8(s[4], s[5], s[6], s[7]) << 32);
+            }
+        }
+    }
+    if (!grey) __syncthreads();
+    if (!is_y || !valid) return;
+
+    const int x0 = (mx * ssx + ix) * 8, y0 = (my * ssy + iy) * 8;
+    if (x0 >= out.width || y0 >= out.height) return; // MCU padding
+    uint8_t* dst = out.ptr + (size_t)y0 * out.pitch + (size_t)x0 * 3;
+    const int n = min(8, out.width - x0);
+    const bool vec = n == 8 && ((reinterpret_cast<uintptr_t>(out.ptr) | (uintptr_t)out.pitch) & 7u) == 0;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) {
+        if (y0 + y >= out.height) break;
+        int s[8], r[8], gg[8], b[8];
+#pragma unroll
+        for (int x = 0; x < 8; ++x) s[x] = min(max((int)(short)(v[y][x] + 128), 0), 255);
+        if (grey) {
+#pragma unroll
+            for (int x = 0; x < 8; ++x) r[x] = gg[x] = b[x] = s[x];
+        } else {
+            const int yc = (iy * 8 + y) / ssy;
+            const unsigned long long cbrow = s_c[0][m][yc], crrow = s_c[1][m][yc];
+            if (SSX == 1 || SSX == 2) {
+                constexpr int S = SSX ? SSX : 1;
+                // chroma column of pixel x: ix * (8 / SSX) + x / SSX
+                const int sh = ix * (64 / S);
+                const uint32_t cbw = (uint32_t)(cbrow >> sh), crw = (uint32_t)(crrow >> sh);
+                const uint32_t cbw2 = (uint32_t)(cbrow >> 32), crw2 = (uint32_t)(crrow >> 32);
+#pragma unroll
+                for (int j = 0; j < 8 / S; ++j) {
+                    const uint32_t wb = (S == 1 && j >= 4) ? cbw2 : cbw;
+                    const uint32_t wr = (S == 1 && j >= 4) ? crw2 : crw;
+                    const ChromaTerms ct = chroma_terms((wb >> (8 * (j & 3))) & 0xff, (wr >> (8 * (j & 3))) & 0xff);
+#pragma unroll
+                    for (int e = 0; e < S; ++e)
+                        ycc_pixel(s[j * S + e], ct, r[j * S + e], gg[j * S + e], b[j * S + e]);
+                }
+            } else {
+#pragma unroll
+                for (int x = 0; x < 8; ++x) {
+                    const int xc = (ix * 8 + x) / ssx;
+                    const ChromaTerms ct = chroma_terms((int)(cbrow >> (8 * xc)) & 0xff, (int)(crrow >> (8 * xc)) & 0xff);
+                    ycc_pixel(s[x], ct, r[x], gg[x], b[x]);
+                }
+            }
+        }
+        store_rgb8(dst + (size_t)y * out.pitch, r, gg, b, vec, n);
+    }
+}
+
+// ycc_to_rgbi_kernel: the same conversion on planes that already exist (any scan structure):
+// one thread per group of eight horizontally adjacent output pixels.
+// Algorithmic bytes: P plane bytes read + 3*W*H written.
+__global__ void __launch_bounds__(256)
+ycc_to_rgbi_kernel(const PlanarIn in, const RgbOut out)
+{
+    const int groups_x = (out.width + 7) >> 3;
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+    const int y = (int)(t / (uint32_t)groups_x);
+    if (y >= out.height) return;
+    const int x0 = (int)(t - (uint32_t)y * (uint32_t)groups_x) * 8;
+    const int n = min(8, out.width - x0);
+    const uint8_t* py = in.ptr[0] + (size_t)y * in.pitch[0] + x0;
+    int r[8], gg[8], b[8];
+    if (in.num_comp == 1) {
+#pragma unroll
+        for (int x = 0; x < 8; ++x) r[x] = gg[x] = b[x] = x < n ? py[x] : 0;
+    } else {
+        const uint8_t* pb = in.ptr[1] + (size_t)(y / in.ssy) * in.pitch[1];
+        const uint8_t* pr = in.ptr[2] + (size_t)(y / in.ssy) * in.pitch[2];
+#pragma unroll
+        for (int x = 0; x < 8; ++x) {
+            r[x] = gg[x] = b[x] = 0;
+            if (x < n) {
+                const int xc = (x0 + x) / in.ssx;
+                ycc_pixel(py[x], chroma_terms(pb[xc], pr[xc]), r[x], gg[x], b[x]);
+            }
+        }
+    }
+    const bool vec = n == 8 && ((reinterpret_cast<uintptr_t>(out.ptr) | (uintptr_t)out.pitch) & 7u) == 0;
+    store_rgb8(out.ptr + (size_t)y * out.pitch + (size_t)x0 * 3, r, gg, b, vec, n);
+}
+
 } // namespace
 
 cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& out,
@@ -225,6 +430,34 @@ cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPla
     tm->mark(stream, kIdTranspose);
     return launch_dependent(transpose_kernel, (total + 255) / 256, 256, 0, stream, g, b.coef, b.dc,
                             planes);
+}
+
+cudaError_t launch_idct_rgbi(const ScanGeom& g, const ScanBufs& b, const RgbOut& out,
+                             cudaStream_t stream, StageTimer* tm)
+{
+    if (g.total_mcus == 0) return cudaSuccess;
+    const bool grey = out.cb < 0;
+    const int mcus = grey ? kRgbGreyMcus : kRgbMcus;
+    const int ssx = g.ssx[out.cy], ssy = g.ssy[out.cy];
+    const unsigned threads = grey ? kRgbGreyMcus : kRgbMcus * (ssx * ssy + 2);
+    const unsigned grid = (unsigned)((g.mcus_x + mcus - 1) / mcus) * (unsigned)g.mcus_y;
+    static PerDeviceOnce configured;
+    configured.run([] {
+        prefer_max_shared(idct_rgbi_kernel<0>);
+        prefer_max_shared(idct_rgbi_kernel<1>);
+        prefer_max_shared(idct_rgbi_kernel<2>);
+    });
+    tm->mark(stream, kIdIdctRgbi);
+    auto* kernel = ssx == 1 ? idct_rgbi_kernel<1> : ssx == 2 ? idct_rgbi_kernel<2> : idct_rgbi_kernel<0>;
+    return launch_dependent(kernel, grid, threads, 0, stream, g, b.coef, b.dc, out);
+}
+
+cudaError_t launch_ycc_to_rgbi(const PlanarIn& in, const RgbOut& out, cudaStream_t stream)
+{
+    const unsigned long long groups = (unsigned long long)((out.width + 7) / 8) * (unsigned long long)out.height;
+    if (groups == 0) return cudaSuccess;
+    ycc_to_rgbi_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(in, out);
+    return cudaGetLastError();
 }
 
 int count_launches(const ScanGeom& g, bool with_transpose)

@@ -50,6 +50,17 @@ class DecodeSession:
         self.dec.decode([p.data_ptr() for p in planes], [p.stride(0) for p in planes],
                         self.scratch.data_ptr(), self.scratch.numel(), s)
 
+    def decode_rgbi(self, rgb=None, stream=None):
+        """Fused decode to an (H, W, 3) uint8 device tensor (allocated when not given; any row
+        stride >= 3*W is accepted)."""
+        s = stream.cuda_stream if stream is not None else torch.cuda.current_stream().cuda_stream
+        if rgb is None:
+            rgb = torch.empty((self.info.sizes_y[0], self.info.sizes_x[0], 3), dtype=torch.uint8,
+                              device=self.device)
+        self.dec.decode_rgbi(rgb.data_ptr(), rgb.stride(0), self.scratch.data_ptr(),
+                             self.scratch.numel(), s)
+        return rgb
+
     def decode_coefficients(self, stream=None):
         s = stream.cuda_stream if stream is not None else torch.cuda.current_stream().cuda_stream
         w, h = self.dec.coefficient_size()

@@ -10,6 +10,7 @@
  */
 #include "jpeg_oracle.h"
 
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -707,4 +708,49 @@ long orc_count_symbols(const uint8_t* data, size_t size)
     g_symbols = 0;
     if (orc_decode(data, size, &info, 0, 0, 0, 0, 0) != ORC_SUCCESS) return 0;
     return g_symbols;
+}
+
+/* util/util.h:33-107.  Written per output pixel instead of per chroma sample: every luma pixel
+ * (X, Y) takes the chroma sample (X / ssx, Y / ssy), which is what the reference's nested
+ * replication loops visit; the float expression keeps the reference's operation order. */
+static uint8_t rgb_sample(float v)
+{
+    float r = roundf(v); /* util/util.h:97-99: round half away from zero, then clamp */
+    if (r < 0.f) r = 0.f;
+    if (r > 255.f) r = 255.f;
+    return (uint8_t)r;
+}
+
+int orc_conv_to_rgbi(const int* sizes_x, const int* sizes_y, int num_components, const int* ssx,
+                     const int* ssy, const uint8_t* plane0, const uint8_t* plane1,
+                     const uint8_t* plane2, uint8_t* out)
+{
+    if (num_components != 1 && num_components != 3) return 1; /* :43-46 */
+    const int w = sizes_x[0], h = sizes_y[0];
+    if (num_components == 1) { /* :48-60 */
+        for (size_t i = 0; i < (size_t)w * (size_t)h; ++i)
+            out[3 * i] = out[3 * i + 1] = out[3 * i + 2] = plane0[i];
+        return 0;
+    }
+    /* :62-71 */
+    if (ssx[0] == 1 && ssy[0] == 1 && (ssx[1] != 1 || ssy[1] != 1) && (ssx[2] != 1 || ssy[2] != 1))
+        return 1;
+    if (ssx[1] != ssx[2] || ssy[1] != ssy[2]) return 1;
+    const int fx = ssx[0], fy = ssy[0]; /* :73-74: luma factors are taken as the replication */
+    const int cw = sizes_x[1];          /* :79: chroma row length */
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const size_t ci = (size_t)(y / fy) * (size_t)cw + (size_t)(x / fx);
+            const uint8_t cb = plane1[ci], cr = plane2[ci];
+            const uint8_t cy = plane0[(size_t)y * (size_t)w + (size_t)x];
+            /* :91-95 */
+            const float r = cy + 1.402f * (cr - 128.f);
+            const float g = cy - .344136f * (cb - 128.f) - .714136f * (cr - 128.f);
+            const float b = cy + 1.772f * (cb - 128.f);
+            uint8_t* o = out + 3 * ((size_t)y * (size_t)w + (size_t)x);
+            o[0] = rgb_sample(r);
+            o[1] = rgb_sample(g);
+            o[2] = rgb_sample(b);
+        }
+    return 0;
 }

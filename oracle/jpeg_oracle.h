@@ -93,6 +93,18 @@ int orc_decode(const uint8_t* data, size_t size, const struct orc_info* info,
 size_t orc_stream_coef_count(const struct orc_info* info, int scan);
 size_t orc_plane_coef_count(const struct orc_info* info, int comp, int* stride_out);
 
+/* Planar YCbCr / grey -> interleaved RGB as the reference's callers do it on the CPU: restates
+ * conv_to_rgbi, util/util.h:33-107 (nearest-neighbour chroma replication; float matrix
+ * r = y + 1.402 (cr-128), g = y - .344136 (cb-128) - .714136 (cr-128), b = y + 1.772 (cb-128);
+ * roundf; clamp).  Planes are dense (row length sizes_x[c]) like the reference's; out holds
+ * 3 * sizes_x[0] * sizes_y[0] bytes.  ssx/ssy: frame sampling factors.  Returns 0, or 1 where the
+ * reference returns EXIT_FAILURE (component count not 1/3, subsampled luma, unequal chroma).
+ * Pinned against the reference's own function (oracle/_ref/libref_util.so) in
+ * tests/test_oracle.py; compiled with -ffp-contract=off so no FMA contraction can occur. */
+int orc_conv_to_rgbi(const int* sizes_x, const int* sizes_y, int num_components, const int* ssx,
+                     const int* ssy, const uint8_t* plane0, const uint8_t* plane1,
+                     const uint8_t* plane2, uint8_t* out);
+
 /* Statistics helper used by tests: count Huffman symbols of the whole file (0 on error). */
 long orc_count_symbols(const uint8_t* data, size_t size);
 

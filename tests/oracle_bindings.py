@@ -77,6 +77,8 @@ def lib():
         L.orc_idct_block.restype = None
         L.orc_count_symbols.restype = C.c_long
         L.orc_count_symbols.argtypes = [C.c_void_p, C.c_size_t]
+        L.orc_conv_to_rgbi.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -134,3 +136,37 @@ def idct_block(coef, q, ref_signed_q=False):
     out = np.zeros((8, 8), dtype=np.uint8)
     lib().orc_idct_block(coef.ctypes.data, q.ctypes.data, out.ctypes.data, 8, int(ref_signed_q))
     return out
+
+
+REF_UTIL_LIB = os.path.join(ORACLE_DIR, "_ref", "libref_util.so")
+
+
+def _conv(fn, planes, ssx, ssy):
+    """planes: 1 or 3 dense uint8 2-D arrays.  Returns (rc, HxWx3 uint8)."""
+    planes = [np.ascontiguousarray(p, dtype=np.uint8) for p in planes]
+    n = len(planes)
+    sx = (C.c_int * 4)(*[p.shape[1] for p in planes] + [0] * (4 - n))
+    sy = (C.c_int * 4)(*[p.shape[0] for p in planes] + [0] * (4 - n))
+    fx = (C.c_int * 4)(*(list(ssx) + [0] * (4 - len(ssx))))
+    fy = (C.c_int * 4)(*(list(ssy) + [0] * (4 - len(ssy))))
+    out = np.zeros((planes[0].shape[0], planes[0].shape[1], 3), dtype=np.uint8)
+    ptr = [p.ctypes.data for p in planes] + [None] * (3 - n)
+    rc = fn(sx, sy, n, fx, fy, ptr[0], ptr[1], ptr[2], out.ctypes.data)
+    return rc, out
+
+
+def conv_to_rgbi(planes, ssx, ssy):
+    """orc_conv_to_rgbi (restatement of the reference's util/util.h conv_to_rgbi)."""
+    return _conv(lib().orc_conv_to_rgbi, planes, ssx, ssy)
+
+
+def ref_util_available():
+    return os.path.exists(REF_UTIL_LIB)
+
+
+def ref_conv_to_rgbi(planes, ssx, ssy):
+    """The reference's own conv_to_rgbi, compiled from its header by oracle/Makefile."""
+    L = C.CDLL(REF_UTIL_LIB)
+    L.ref_conv_to_rgbi.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    return _conv(L.ref_conv_to_rgbi, planes, ssx, ssy)
