@@ -187,6 +187,7 @@ struct PlanarIn {
     int pitch[3];
     int num_comp;  // 1 or 3
     int ssx, ssy;  // luma samples per chroma sample
+    bool aligned;  // every plane pointer and pitch is a multiple of 8 (set by the launcher)
 };
 
 struct CoefPlanes {

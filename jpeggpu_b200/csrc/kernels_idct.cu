@@ -77,6 +77,17 @@ __device__ __forceinline__ uint32_t pack_sat_u8(int p0, int p1, int p2, int p3)
     return d;
 }
 
+// Kernel parameters: destinations without the byte quantisers (those travel as QPairs).
+struct PlaneDst {
+    uint8_t* ptr[kMaxComp];
+    int pitch[kMaxComp];
+};
+struct RgbDst {
+    uint8_t* ptr;
+    int pitch, width, height;
+    int cy, cb, cr;
+};
+
 // Position of a plane-order thread: scan component, block coordinates and coded DU index.
 struct DuPos {
     int comp, bx, by;
@@ -105,30 +116,66 @@ __device__ __forceinline__ bool locate(const ScanGeom& g, uint32_t t, DuPos& pos
     return true;
 }
 
-// Loads data unit `du` (zig-zag order), dequantises with the natural-order table `q` and runs both
-// IDCT passes in registers: v[y][x] is the sample before the level shift.
+// Quantisers as the kernels want them: one 32-bit word per PAIR of zig-zag-consecutive
+// coefficients, bytes {q[2j], 0, 0, q[2j+1]}, so that one dp2a instruction per coefficient
+// extracts the signed 16-bit coefficient from its pair word AND multiplies it with its unsigned
+// 8-bit quantiser (dp2a.lo uses bytes 0,1 of the second operand, dp2a.hi bytes 2,3; the zero
+// bytes silence the other half).  8 x 16-byte shared-memory loads per data unit instead of 64
+// scalar ones.
+struct QPairs {
+    uint32_t w[kMaxComp][32];
+};
+QPairs pack_quantisers(const uint8_t (&q)[kMaxComp][64])
+{
+    QPairs r;
+    for (int a = 0; a < kMaxComp; ++a)
+        for (int j = 0; j < 32; ++j)
+            r.w[a][j] = (uint32_t)q[a][natural_of(2 * j)] | ((uint32_t)q[a][natural_of(2 * j + 1)] << 24);
+    return r;
+}
+__device__ __forceinline__ int dp2a_lo_su(uint32_t a, uint32_t b)
+{
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(0));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(uint32_t a, uint32_t b)
+{
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(0));
+    return d;
+}
+__device__ __forceinline__ void stage_quantisers(uint32_t (*s_q)[32], const QPairs& q)
+{
+    for (int i = threadIdx.x; i < kMaxComp * 32; i += blockDim.x) s_q[i >> 5][i & 31] = q.w[i >> 5][i & 31];
+}
+
+// Loads data unit `du` (zig-zag order), dequantises with the packed table `q` (16-byte aligned
+// shared memory) and runs both IDCT passes in registers: v[y][x] is the sample before the level
+// shift.
 __device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
                                           const int16_t* __restrict__ dc, uint32_t du,
-                                          const int* q, int (&v)[8][8])
+                                          const uint32_t* q, int (&v)[8][8])
 {
     const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)du * 64);
+    const uint4* qsrc = reinterpret_cast<const uint4*>(q);
     // the buffer holds every data unit in zig-zag order: un-zig-zag while loading (register
     // indices are compile-time constants after unrolling)
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         const uint4 w = src[r];
+        const uint4 qq = qsrc[r];
         const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+        const uint32_t qw[4] = {qq.x, qq.y, qq.z, qq.w};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            const int lo = (int)(short)(ww[k] & 0xffffu);
-            const int hi = (int)(short)(ww[k] >> 16);
             const int n0 = natural_of(r * 8 + 2 * k), n1 = natural_of(r * 8 + 2 * k + 1);
             // src/idct.cu:178-180: the product is stored as int16
-            v[n0 >> 3][n0 & 7] = (int)(short)(lo * q[n0]);
-            v[n1 >> 3][n1 & 7] = (int)(short)(hi * q[n1]);
+            v[n0 >> 3][n0 & 7] = (int)(short)dp2a_lo_su(ww[k], qw[k]);
+            v[n1 >> 3][n1 & 7] = (int)(short)dp2a_hi_su(ww[k], qw[k]);
         }
     }
-    v[0][0] = (int)(short)((int)dc[du] * q[0]); // absolute DC lives in the compact array
+    v[0][0] = (int)(short)((int)dc[du] * (int)(q[0] & 0xffu)); // absolute DC lives in the compact array
 #pragma unroll
     for (int x = 0; x < 8; ++x)
         idct8(v[0][x], v[1][x], v[2][x], v[3][x], v[4][x], v[5][x], v[6][x], v[7][x]);
@@ -144,11 +191,10 @@ constexpr int kIdctThreads = 128;
 
 __global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
 idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
-            const OutPlanes out)
+            const PlaneDst out, const QPairs q)
 {
-    __shared__ int s_q[kMaxComp][64];
-    for (int i = threadIdx.x; i < kMaxComp * 64; i += kIdctThreads)
-        s_q[i >> 6][i & 63] = out.q[i >> 6][i & 63];
+    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
+    stage_quantisers(s_q, q);
     grid_dependency_wait();
     grid_dependency_trigger();
     __syncthreads();
@@ -219,9 +265,19 @@ transpose_kernel(const ScanGeom g, const int16_t* __restrict__ coef,
 struct ChromaTerms {
     float rr, gb, gr, bb;
 };
+// None of the conversions below touches the (eighth-rate) I2F/F2I pipe.  Integers 0..255 become
+// floats by planting them in the mantissa of 2^23; round-half-away + clamp of the result is
+// floor(x + 0.5) taken by a round-down multiply into the denormal range, where the bit pattern IS
+// the integer (negative inputs give a negative pattern), and the saturating byte pack clamps.
+// floor(fl(x + 0.5)) equals clamp(roundf(x)) for every value the matrix can produce from 8-bit
+// inputs; tests/test_gpu_rgbi.py::test_convert_rgbi_every_triple checks all 2^24 triples.
+__device__ __forceinline__ float u8_to_float(int v, float bias)
+{
+    return __fsub_rn(__int_as_float(0x4b000000 | v), bias); // (2^23 + v) - bias, exact
+}
 __device__ __forceinline__ ChromaTerms chroma_terms(int cb, int cr)
 {
-    const float fb = __fsub_rn((float)cb, 128.f), fr = __fsub_rn((float)cr, 128.f);
+    const float fb = u8_to_float(cb, 8388736.f), fr = u8_to_float(cr, 8388736.f); // c - 128
     ChromaTerms t;
     t.rr = __fmul_rn(1.402f, fr);
     t.gb = __fmul_rn(.344136f, fb);
@@ -229,11 +285,14 @@ __device__ __forceinline__ ChromaTerms chroma_terms(int cb, int cr)
     t.bb = __fmul_rn(1.772f, fb);
     return t;
 }
-// roundf() without the clamp: the packing instruction saturates to 0..255 afterwards
-__device__ __forceinline__ int round_away(float x) { return __float2int_rz(roundf(x)); }
+__device__ __forceinline__ int round_away(float x)
+{
+    return __float_as_int(__fmul_rd(__fadd_rn(x, 0.5f), __int_as_float(1))); // * 2^-149, toward -inf
+}
+// cy must already be clamped to 0..255; r, g, b come back unclamped (negative: any negative int)
 __device__ __forceinline__ void ycc_pixel(int cy, const ChromaTerms& t, int& r, int& g, int& b)
 {
-    const float fy = (float)cy;
+    const float fy = u8_to_float(cy, 8388608.f);
     r = round_away(__fadd_rn(fy, t.rr));
     g = round_away(__fsub_rn(__fsub_rn(fy, t.gb), t.gr));
     b = round_away(__fadd_rn(fy, t.bb));
@@ -268,26 +327,35 @@ __device__ __forceinline__ void store_rgb8(uint8_t* row, const int (&r)[8], cons
 // leave their clamped samples in shared memory (72-byte stride per data unit: conflict-free 8-byte
 // row reads), the Y threads convert and store.  The planes are never written.
 // Algorithmic bytes: 2*C coefficient bytes read + 3*W*H bytes written.
-constexpr int kRgbMcus = 32;      // MCUs per CTA of a colour image
+#ifndef JB2_RGB_MCUS
+#define JB2_RGB_MCUS 32
+#endif
+constexpr int kRgbMcus = JB2_RGB_MCUS; // MCUs per CTA of a colour image
 constexpr int kRgbGreyMcus = 128; // data units per CTA of a grey image
 constexpr int kRgbMaxThreads = kRgbMcus * kMaxDuPerMcu;
 
-template <int SSX> // Y data units per MCU in x when 1 or 2; 0: any (runtime g.ssx)
-__global__ void __launch_bounds__(kRgbMaxThreads)
+#ifndef JB2_RGB_MIN_CTAS
+#define JB2_RGB_MIN_CTAS 3
+#endif
+// SSX, SSY: Y data units per MCU in x / y for the common layouts 1x1 (4:4:4, grey), 2x1 (4:2:2)
+// and 2x2 (4:2:0) - the CTA size and the register budget follow from them; 0, 0: any layout
+// (runtime g.ssx / g.ssy, CTA of up to kRgbMaxThreads).
+template <int SSX, int SSY>
+__global__ void __launch_bounds__(SSX ? kRgbMcus * (SSX * SSY + 2) : kRgbMaxThreads,
+                                  SSX ? JB2_RGB_MIN_CTAS : 1)
 idct_rgbi_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
-                 const RgbOut out)
+                 const RgbDst out, const QPairs q)
 {
-    __shared__ int s_q[kMaxComp][64];
+    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
     __shared__ unsigned long long s_c[2][kRgbMcus][9];
-    for (int i = threadIdx.x; i < kMaxComp * 64; i += blockDim.x)
-        s_q[i >> 6][i & 63] = out.q[i >> 6][i & 63];
+    stage_quantisers(s_q, q);
     grid_dependency_wait();
     grid_dependency_trigger();
     __syncthreads();
 
     const bool grey = out.cb < 0;
     const int mcus = grey ? kRgbGreyMcus : kRgbMcus;
-    const int ssx = SSX ? SSX : g.ssx[out.cy], ssy = g.ssy[out.cy];
+    const int ssx = SSX ? SSX : g.ssx[out.cy], ssy = SSY ? SSY : g.ssy[out.cy];
     const int groups_x = (g.mcus_x + mcus - 1) / mcus;
     const int my = blockIdx.x / groups_x;
     const int mx0 = (blockIdx.x - my * groups_x) * mcus;
@@ -338,7 +406,7 @@ idct_rgbi_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16
         if (y0 + y >= out.height) break;
         int s[8], r[8], gg[8], b[8];
 #pragma unroll
-        for (int x = 0; x < 8; ++x) s[x] = min(max((int)(short)(v[y][x] + 128), 0), 255);
+        for (int x = 0; x < 8; ++x) s[x] = __vimin_s32_relu((int)(short)(v[y][x] + 128), 255);
         if (grey) {
 #pragma unroll
             for (int x = 0; x < 8; ++x) r[x] = gg[x] = b[x] = s[x];
@@ -374,10 +442,14 @@ idct_rgbi_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16
 }
 
 // ycc_to_rgbi_kernel: the same conversion on planes that already exist (any scan structure):
-// one thread per group of eight horizontally adjacent output pixels.
+// one thread per group of eight horizontally adjacent output pixels.  LG = log2 of the luma
+// samples per chroma sample in x when that is 1, 2 or 4 (vector loads of the eight luma bytes and
+// of the 8 >> LG chroma bytes when the planes are aligned, chroma terms shared between the pixels
+// of one chroma sample); LG < 0: any factor, byte loads.
 // Algorithmic bytes: P plane bytes read + 3*W*H written.
+template <int LG>
 __global__ void __launch_bounds__(256)
-ycc_to_rgbi_kernel(const PlanarIn in, const RgbOut out)
+ycc_to_rgbi_kernel(const PlanarIn in, const RgbDst out)
 {
     const int groups_x = (out.width + 7) >> 3;
     const uint32_t t = blockIdx.x * 256u + threadIdx.x;
@@ -386,19 +458,61 @@ ycc_to_rgbi_kernel(const PlanarIn in, const RgbOut out)
     const int x0 = (int)(t - (uint32_t)y * (uint32_t)groups_x) * 8;
     const int n = min(8, out.width - x0);
     const uint8_t* py = in.ptr[0] + (size_t)y * in.pitch[0] + x0;
-    int r[8], gg[8], b[8];
-    if (in.num_comp == 1) {
+    const bool grey = in.num_comp == 1;
+    int s[8], r[8], gg[8], b[8];
+    if (n == 8 && in.aligned) {
+        const uint2 w = *reinterpret_cast<const uint2*>(py);
 #pragma unroll
-        for (int x = 0; x < 8; ++x) r[x] = gg[x] = b[x] = x < n ? py[x] : 0;
+        for (int x = 0; x < 8; ++x) s[x] = ((x < 4 ? w.x : w.y) >> (8 * (x & 3))) & 0xff;
+    } else {
+#pragma unroll
+        for (int x = 0; x < 8; ++x) s[x] = x < n ? py[x] : 0;
+    }
+    if (grey) {
+#pragma unroll
+        for (int x = 0; x < 8; ++x) r[x] = gg[x] = b[x] = s[x];
     } else {
         const uint8_t* pb = in.ptr[1] + (size_t)(y / in.ssy) * in.pitch[1];
         const uint8_t* pr = in.ptr[2] + (size_t)(y / in.ssy) * in.pitch[2];
+        if (LG >= 0) {
+            constexpr int L = LG >= 0 ? LG : 0;
+            constexpr int kC = 8 >> L; // chroma samples under eight luma pixels
+            const int c0 = x0 >> L;
+            unsigned long long cbrow = 0, crrow = 0;
+            if (n == 8 && in.aligned) {
+                if (kC == 8) {
+                    cbrow = *reinterpret_cast<const unsigned long long*>(pb + c0);
+                    crrow = *reinterpret_cast<const unsigned long long*>(pr + c0);
+                } else if (kC == 4) {
+                    cbrow = *reinterpret_cast<const uint32_t*>(pb + c0);
+                    crrow = *reinterpret_cast<const uint32_t*>(pr + c0);
+                } else {
+                    cbrow = *reinterpret_cast<const uint16_t*>(pb + c0);
+                    crrow = *reinterpret_cast<const uint16_t*>(pr + c0);
+                }
+            } else {
 #pragma unroll
-        for (int x = 0; x < 8; ++x) {
-            r[x] = gg[x] = b[x] = 0;
-            if (x < n) {
-                const int xc = (x0 + x) / in.ssx;
-                ycc_pixel(py[x], chroma_terms(pb[xc], pr[xc]), r[x], gg[x], b[x]);
+                for (int j = 0; j < kC; ++j)
+                    if ((j << L) < n) {
+                        cbrow |= (unsigned long long)pb[c0 + j] << (8 * j);
+                        crrow |= (unsigned long long)pr[c0 + j] << (8 * j);
+                    }
+            }
+#pragma unroll
+            for (int j = 0; j < kC; ++j) {
+                const ChromaTerms ct = chroma_terms((int)(cbrow >> (8 * j)) & 0xff, (int)(crrow >> (8 * j)) & 0xff);
+#pragma unroll
+                for (int e = 0; e < (1 << L); ++e)
+                    ycc_pixel(s[(j << L) + e], ct, r[(j << L) + e], gg[(j << L) + e], b[(j << L) + e]);
+            }
+        } else {
+#pragma unroll
+            for (int x = 0; x < 8; ++x) {
+                r[x] = gg[x] = b[x] = 0;
+                if (x < n) {
+                    const int xc = (x0 + x) / in.ssx;
+                    ycc_pixel(s[x], chroma_terms(pb[xc], pr[xc]), r[x], gg[x], b[x]);
+                }
             }
         }
     }
@@ -416,8 +530,13 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
     static PerDeviceOnce configured;
     configured.run([] { prefer_max_shared(idct_kernel); });
     tm->mark(stream, kIdIdct);
+    PlaneDst dst;
+    for (int a = 0; a < kMaxComp; ++a) {
+        dst.ptr[a] = out.ptr[a];
+        dst.pitch[a] = out.pitch[a];
+    }
     return launch_dependent(idct_kernel, (total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0,
-                            stream, g, b.coef, b.dc, out);
+                            stream, g, b.coef, b.dc, dst, pack_quantisers(out.q));
 }
 
 cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPlanes& planes,
@@ -432,6 +551,19 @@ cudaError_t launch_transpose(const ScanGeom& g, const ScanBufs& b, const CoefPla
                             planes);
 }
 
+static RgbDst rgb_dst(const RgbOut& out)
+{
+    RgbDst d;
+    d.ptr = out.ptr;
+    d.pitch = out.pitch;
+    d.width = out.width;
+    d.height = out.height;
+    d.cy = out.cy;
+    d.cb = out.cb;
+    d.cr = out.cr;
+    return d;
+}
+
 cudaError_t launch_idct_rgbi(const ScanGeom& g, const ScanBufs& b, const RgbOut& out,
                              cudaStream_t stream, StageTimer* tm)
 {
@@ -443,20 +575,36 @@ cudaError_t launch_idct_rgbi(const ScanGeom& g, const ScanBufs& b, const RgbOut&
     const unsigned grid = (unsigned)((g.mcus_x + mcus - 1) / mcus) * (unsigned)g.mcus_y;
     static PerDeviceOnce configured;
     configured.run([] {
-        prefer_max_shared(idct_rgbi_kernel<0>);
-        prefer_max_shared(idct_rgbi_kernel<1>);
-        prefer_max_shared(idct_rgbi_kernel<2>);
+        prefer_max_shared(idct_rgbi_kernel<0, 0>);
+        prefer_max_shared(idct_rgbi_kernel<1, 1>);
+        prefer_max_shared(idct_rgbi_kernel<2, 1>);
+        prefer_max_shared(idct_rgbi_kernel<2, 2>);
     });
     tm->mark(stream, kIdIdctRgbi);
-    auto* kernel = ssx == 1 ? idct_rgbi_kernel<1> : ssx == 2 ? idct_rgbi_kernel<2> : idct_rgbi_kernel<0>;
-    return launch_dependent(kernel, grid, threads, 0, stream, g, b.coef, b.dc, out);
+    auto* kernel = grey ? idct_rgbi_kernel<0, 0>
+                   : ssx == 1 && ssy == 1 ? idct_rgbi_kernel<1, 1>
+                   : ssx == 2 && ssy == 1 ? idct_rgbi_kernel<2, 1>
+                   : ssx == 2 && ssy == 2 ? idct_rgbi_kernel<2, 2> : idct_rgbi_kernel<0, 0>;
+    return launch_dependent(kernel, grid, threads, 0, stream, g, b.coef, b.dc, rgb_dst(out),
+                            pack_quantisers(out.q));
 }
 
 cudaError_t launch_ycc_to_rgbi(const PlanarIn& in, const RgbOut& out, cudaStream_t stream)
 {
     const unsigned long long groups = (unsigned long long)((out.width + 7) / 8) * (unsigned long long)out.height;
     if (groups == 0) return cudaSuccess;
-    ycc_to_rgbi_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(in, out);
+    const unsigned grid = (unsigned)((groups + 255) / 256);
+    PlanarIn p = in;
+    const RgbDst dst = rgb_dst(out);
+    uintptr_t bits = 0;
+    for (int c = 0; c < in.num_comp; ++c) bits |= reinterpret_cast<uintptr_t>(in.ptr[c]) | (uintptr_t)in.pitch[c];
+    p.aligned = (bits & 7u) == 0;
+    switch (in.ssx) {
+    case 1: ycc_to_rgbi_kernel<0><<<grid, 256, 0, stream>>>(p, dst); break;
+    case 2: ycc_to_rgbi_kernel<1><<<grid, 256, 0, stream>>>(p, dst); break;
+    case 4: ycc_to_rgbi_kernel<2><<<grid, 256, 0, stream>>>(p, dst); break;
+    default: ycc_to_rgbi_kernel<-1><<<grid, 256, 0, stream>>>(p, dst); break;
+    }
     return cudaGetLastError();
 }
 
