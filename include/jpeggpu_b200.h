@@ -92,7 +92,10 @@ enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, si
  * upper bounds (<= 0.1 % above the exact plan), and jpeggpu_decoder_transfer enqueues the upload of
  * the scan bytes first and walks them on the host while the DMA is in flight.  Statuses the walk
  * can produce are then returned by transfer instead of parse_header.  The reference walks inside
- * parse_header (src/reader.cpp:443-489); `on` = 0 restores that order. */
+ * parse_header (src/reader.cpp:443-489); `on` = 0 restores that order.
+ * Scans of at least 1 MiB are walked by the calling thread plus up to three helper threads owned
+ * by the decoder (started on first use, asleep otherwise; they read the file only while
+ * jpeggpu_decoder_transfer runs); `on` = 2 keeps the deferred walk on the calling thread alone. */
 enum jpeggpu_status jpeggpu_b200_set_deferred_walk(jpeggpu_decoder_t decoder, int on);
 
 /* Per-kernel device times. With profiling on, jpeggpu_decoder_decode records a CUDA event on the

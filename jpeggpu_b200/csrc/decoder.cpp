@@ -75,9 +75,12 @@ struct jpeggpu_decoder {
     } lut_cache[kMaxScans];
     std::vector<uint8_t> lut_key;
     StageTimer timer;
+    WalkPool* walk_pool = nullptr; // helper threads of the deferred walk (large scans only)
+    bool walk_threads = true;
 
     ~jpeggpu_decoder()
     {
+        walk_pool_destroy(walk_pool);
         for (StagingSlot& sl : slots) {
             if (sl.have_event) cudaEventDestroy(sl.copied);
             release_slot(sl);
@@ -285,7 +288,7 @@ jpeggpu_status jpeggpu_decoder::finish_walk()
 {
     if (!plan.walk_pending) return JPEGGPU_SUCCESS;
     const uint32_t planned_bytes = plan.scans[0].geom.scan_bytes;
-    const jpeggpu_status st = finish_deferred_walk(plan, log);
+    const jpeggpu_status st = finish_deferred_walk(plan, log, walk_threads ? walk_pool : nullptr);
     if (st != JPEGGPU_SUCCESS) {
         parsed = false;
         return st;
@@ -516,6 +519,11 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
     if (decoder->plan.walk_pending) {
         // the big copy goes first; the host walks the same bytes while the DMA engine reads them
         const ScanPlan& sp = decoder->plan.scans[0];
+        if (decoder->walk_threads && decoder->plan.file_size - sp.begin >= kWalkParallelMin) {
+            // wake the helpers before the enqueue below so that their start-up hides behind it
+            if (!decoder->walk_pool) decoder->walk_pool = walk_pool_create();
+            walk_pool_kick(decoder->walk_pool, decoder->plan);
+        }
         JB2_CUDA(cudaMemcpyAsync(base + decoder->layout[0].off_bytes, decoder->plan.file + sp.begin,
                                  sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream));
         const jpeggpu_status st = decoder->finish_walk();
@@ -697,6 +705,7 @@ enum jpeggpu_status jpeggpu_b200_set_deferred_walk(jpeggpu_decoder_t decoder, in
 {
     if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
     decoder->defer_walk = on != 0;
+    decoder->walk_threads = on != 2;
     return JPEGGPU_SUCCESS;
 }
 

@@ -4,7 +4,12 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
 #include <new>
+#include <thread>
 #if defined(__x86_64__)
 #include <immintrin.h>
 #endif
@@ -335,16 +340,26 @@ FindFn pick_find_marker()
 FindFn pick_find_marker() { return find_marker_scalar; }
 #endif
 
-jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp)
+FindFn find_marker_fn()
 {
-    static const FindFn find_marker = pick_find_marker();
+    static const FindFn f = pick_find_marker();
+    return f;
+}
+
+// start_off (a multiple of kDestuffTile): walk from that offset of the scan as if the bytes
+// before it held no data at all; the tiles before it are left as placeholders.  The caller adds
+// what the skipped bytes contribute (parallel walk below).
+jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp, uint64_t start_off = 0)
+{
+    const FindFn find_marker = find_marker_fn();
     const uint8_t* const scan_begin = cur.p;
-    const uint8_t* p = cur.p;
+    const uint8_t* p = cur.p + start_off;
     const uint8_t* const end = cur.end;
     uint64_t kept_total = 0;   // data bytes of the scan before p
     uint64_t seg_kept0 = 0;    // kept_total at the start of the open segment
     uint64_t sub_off = 0, src_begin = 0;
-    uint64_t tile_next = 0;    // stuffed offset of the next tile boundary to record
+    uint64_t tile_next = start_off; // stuffed offset of the next tile boundary to record
+    sp.tiles.resize((size_t)(start_off / kDestuffTile));
     auto close_segment = [&]() {
         SegDesc d;
         d.sub_off = (uint32_t)sub_off;
@@ -403,6 +418,159 @@ jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp)
     sp.geom.num_segments = (int)sp.segs.size();
     sp.tiles.resize(((size_t)sp.geom.scan_bytes + kDestuffTile - 1) / kDestuffTile);
     return JPEGGPU_SUCCESS;
+}
+
+
+// ---- parallel walk (see parser.hpp) ------------------------------------------------------------
+constexpr size_t kWalkBlock = 64 * 1024; // counting unit handed to a thread
+constexpr int kWalkHelpers = 3;
+
+struct WalkJob {
+    const uint8_t* scan_begin = nullptr;
+    uint32_t num_blocks = 0;          // counting blocks [0, num_blocks) of kWalkBlock bytes
+    std::vector<uint32_t> tile_ffs;   // 0xff bytes per destuff tile of the counting region
+    std::atomic<uint32_t> next{0}, done{0};
+    std::atomic<bool> impure{false};
+};
+
+// Pull counting blocks until none is left.  A block is pure when every 0xff in it is followed by
+// 0x00 (the byte after the block included): then data bytes = bytes - number of 0xff.
+void walk_job_work(WalkJob& job)
+{
+    const FindFn find_marker = find_marker_fn();
+    constexpr uint32_t tiles_per_block = (uint32_t)(kWalkBlock / kDestuffTile);
+    for (;;) {
+        const uint32_t b = job.next.fetch_add(1, std::memory_order_relaxed);
+        if (b >= job.num_blocks) return;
+        const uint8_t* t0 = job.scan_begin + (size_t)b * kWalkBlock;
+        for (uint32_t i = 0; i < tiles_per_block; ++i, t0 += kDestuffTile) {
+            uint64_t ffs = 0;
+            if (find_marker(t0, t0 + kDestuffTile, &ffs) != t0 + kDestuffTile)
+                job.impure.store(true, std::memory_order_relaxed);
+            job.tile_ffs[(size_t)b * tiles_per_block + i] = (uint32_t)ffs;
+        }
+        job.done.fetch_add(1, std::memory_order_release);
+    }
+}
+
+} // namespace
+
+struct WalkPool {
+    std::vector<std::thread> threads;
+    std::mutex m;
+    std::condition_variable cv;
+    bool stop = false;
+    std::shared_ptr<WalkJob> job; // the job of the image being transferred (guarded by m)
+    uint64_t generation = 0;
+    const ImagePlan* kicked_for = nullptr;
+    uint64_t stitched = 0; // walks completed on the parallel path (tests, diagnostics)
+
+    void worker()
+    {
+        uint64_t seen = 0;
+        for (;;) {
+            std::shared_ptr<WalkJob> mine;
+            {
+                std::unique_lock<std::mutex> lk(m);
+                cv.wait(lk, [&] { return stop || generation != seen; });
+                if (stop) return;
+                seen = generation;
+                mine = job;
+            }
+            // a helper that wakes late finds its (old) job exhausted and never touches file bytes
+            if (mine) walk_job_work(*mine);
+        }
+    }
+};
+
+WalkPool* walk_pool_create() { return new (std::nothrow) WalkPool; }
+
+uint64_t walk_pool_stitched(const WalkPool* pool) { return pool ? pool->stitched : 0; }
+
+void walk_pool_destroy(WalkPool* pool)
+{
+    if (!pool) return;
+    {
+        std::lock_guard<std::mutex> lk(pool->m);
+        pool->stop = true;
+    }
+    pool->cv.notify_all();
+    for (std::thread& t : pool->threads) t.join();
+    delete pool;
+}
+
+void walk_pool_kick(WalkPool* pool, const ImagePlan& plan)
+{
+    if (!pool || !plan.walk_pending) return;
+    pool->kicked_for = nullptr;
+    const ScanPlan& sp = plan.scans[0];
+    const size_t avail = plan.file_size - sp.begin; // the scan runs to the EOI at the end of the file
+    if (avail < kWalkParallelMin) return;
+    try {
+        if (pool->threads.empty())
+            for (int i = 0; i < kWalkHelpers; ++i) pool->threads.emplace_back([pool] { pool->worker(); });
+        auto job = std::make_shared<WalkJob>();
+        job->scan_begin = plan.file + sp.begin;
+        job->num_blocks = (uint32_t)((avail - kWalkBlock) / kWalkBlock); // tail: 64..128 KB
+        job->tile_ffs.resize((size_t)job->num_blocks * (kWalkBlock / kDestuffTile));
+        {
+            std::lock_guard<std::mutex> lk(pool->m);
+            pool->job = job;
+            ++pool->generation;
+        }
+        pool->cv.notify_all();
+        pool->kicked_for = &plan;
+    } catch (...) { // no threads / no memory: the sequential walk needs neither
+        pool->kicked_for = nullptr;
+    }
+}
+
+namespace {
+
+// Returns false when the parallel path does not apply or its result had to be discarded (the
+// caller then walks sequentially from a clean state); true with *status set otherwise.
+bool walk_parallel(WalkPool* pool, const ImagePlan& plan, Cursor& cur, ScanPlan& sp,
+                   jpeggpu_status* status)
+{
+    if (!pool || pool->kicked_for != &plan || !pool->job) return false;
+    pool->kicked_for = nullptr;
+    const std::shared_ptr<WalkJob> job = pool->job;
+    if (job->scan_begin != cur.p) return false;
+    const uint64_t counted = (uint64_t)job->num_blocks * kWalkBlock;
+    // tail first (only this thread can do it), then help with the counting blocks
+    sp.segs.clear();
+    sp.tiles.clear();
+    const jpeggpu_status st = walk_scan(cur, sp, counted);
+    walk_job_work(*job);
+    while (job->done.load(std::memory_order_acquire) != job->num_blocks) {
+#if defined(__x86_64__)
+        _mm_pause();
+#endif
+    }
+    if (st != JPEGGPU_SUCCESS || job->impure.load(std::memory_order_relaxed) || sp.segs.size() != 1)
+        return false; // let the sequential walk decide (it also produces the right status)
+    // stitch: tile totals of the counting region, then shift the tail by what that region holds
+    uint64_t kept = 0;
+    const size_t counted_tiles = (size_t)(counted / kDestuffTile);
+    for (size_t i = 0; i < counted_tiles && i < sp.tiles.size(); ++i) {
+        sp.tiles[i].kept_before = (uint32_t)kept;
+        sp.tiles[i].segs_before = 0;
+        kept += kDestuffTile - job->tile_ffs[i];
+    }
+    for (size_t i = counted_tiles; i < sp.tiles.size(); ++i) {
+        if (sp.tiles[i].segs_before != 0) return false;
+        sp.tiles[i].kept_before += (uint32_t)kept;
+    }
+    SegDesc& seg = sp.segs[0];
+    const uint64_t nbytes = (uint64_t)seg.nbytes + kept;
+    const uint64_t subs = (nbytes + kSubBytes - 1) / kSubBytes;
+    if (nbytes >= (1ull << 31) || subs >= (1ull << 31)) return false;
+    seg.nbytes = (uint32_t)nbytes;
+    seg.src_begin = 0;
+    sp.geom.num_subs = (uint32_t)subs;
+    ++pool->stitched;
+    *status = JPEGGPU_SUCCESS;
+    return true;
 }
 
 // Scan header + geometry. Statuses follow src/reader.cpp:305-441.
@@ -579,13 +747,19 @@ jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, con
     return marker_loop(cur, plan, log, allow_defer);
 }
 
-jpeggpu_status finish_impl(ImagePlan& plan, const Logger& log)
+jpeggpu_status finish_impl(ImagePlan& plan, const Logger& log, WalkPool* pool)
 {
     ScanPlan& sp = plan.scans[0];
     const ScanGeom bound = sp.geom;
     Cursor cur{plan.file + sp.begin, plan.file, plan.file + plan.file_size};
     plan.walk_pending = false;
-    jpeggpu_status s = walk_scan(cur, sp);
+    jpeggpu_status s = JPEGGPU_SUCCESS;
+    if (!walk_parallel(pool, plan, cur, sp, &s)) {
+        cur = Cursor{plan.file + sp.begin, plan.file, plan.file + plan.file_size};
+        sp.segs.clear();
+        sp.tiles.clear();
+        s = walk_scan(cur, sp);
+    }
     if (s != JPEGGPU_SUCCESS) return s;
     // the scratch plan was sized from the bounds
     if (sp.geom.scan_bytes > bound.scan_bytes || sp.geom.num_subs > bound.num_subs ||
@@ -606,11 +780,11 @@ jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, con
     }
 }
 
-jpeggpu_status finish_deferred_walk(ImagePlan& plan, const Logger& log)
+jpeggpu_status finish_deferred_walk(ImagePlan& plan, const Logger& log, WalkPool* pool)
 {
     if (!plan.walk_pending) return JPEGGPU_SUCCESS;
     try {
-        return finish_impl(plan, log);
+        return finish_impl(plan, log, pool);
     } catch (const std::bad_alloc&) {
         plan.walk_pending = false;
         return JPEGGPU_OUT_OF_HOST_MEMORY;

@@ -78,9 +78,27 @@ struct Logger {
 jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
                           bool allow_defer = false);
 
+// Helper threads for the deferred walk of large scans.  The walk is memory bound on one core
+// (~35 GB/s: the previous upload has evicted the file from the caches), so scans of at least
+// kWalkParallelMin bytes are cut into 64 KB blocks: everything but the tail is a pure counting
+// job (0xff bytes per destuff tile, valid only while every 0xff is followed by 0x00) that the
+// helpers and the calling thread pull from a shared counter; the calling thread walks the tail,
+// where the scan ends, with the general code.  Anything unexpected in a counting block (restart
+// or fill markers) discards the parallel result and re-walks sequentially.  The pool is owned by
+// one decoder; threads start on first use and only ever read file bytes between
+// walk_pool_kick() and the return of finish_deferred_walk(), i.e. inside jpeggpu_decoder_transfer.
+struct WalkPool;
+constexpr size_t kWalkParallelMin = 1u << 20;
+WalkPool* walk_pool_create();
+void walk_pool_destroy(WalkPool* pool);
+uint64_t walk_pool_stitched(const WalkPool* pool); // walks that completed on the parallel path
+// Hands the counting blocks of plan.scans[0] to the helpers (no-op for small scans).
+void walk_pool_kick(WalkPool* pool, const ImagePlan& plan);
+
 // Walks the deferred scan, replaces the bounds in scans[0] by the exact values and resumes the
 // marker loop behind the scan (same statuses as the eager parse).  No-op unless walk_pending.
-jpeggpu_status finish_deferred_walk(ImagePlan& plan, const Logger& log);
+// pool: optional, after walk_pool_kick() for the same plan.
+jpeggpu_status finish_deferred_walk(ImagePlan& plan, const Logger& log, WalkPool* pool = nullptr);
 
 } // namespace jb2
 #endif

@@ -25,13 +25,24 @@ def lib():
             os.makedirs(os.path.dirname(OUT), exist_ok=True)
             subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", *DEFS, "-I" + CSRC,
                             "-I" + os.path.join(ROOT, "include"), "-I" + CUDA_INC, SRC,
-                            os.path.join(CSRC, "parser.cpp"), "-o", OUT], check=True)
+                            os.path.join(CSRC, "parser.cpp"), "-lpthread", "-o", OUT], check=True)
         L = C.CDLL(OUT)
         L.emul_parse.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
         L.emul_decode_scan.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t,
                                        C.c_void_p, C.c_size_t, C.c_void_p]
+        L.emul_walk_compare.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_int),
+                                        C.POINTER(C.c_int)]
         _lib = L
     return _lib
+
+
+def walk_compare(data: bytes, threads: bool):
+    """(difference code, pool use, status): eager walk vs deferred walk (+ helper threads).
+    pool use: 0 not kicked, 1 kicked but the result was discarded (sequential re-walk), 2 kept."""
+    buf = np.frombuffer(data, dtype=np.uint8)
+    used, st = C.c_int(), C.c_int()
+    rc = lib().emul_walk_compare(buf.ctypes.data, len(data), int(threads), C.byref(used), C.byref(st))
+    return rc, used.value, st.value
 
 
 def parse(data: bytes):

@@ -278,4 +278,43 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     return 0;
 }
 
+// Walk equivalence: eager parse vs deferred parse + finish, sequential (threads = 0) or with the
+// helper pool (threads = 1).  Returns 0 when both give the same status and - on success - the
+// same geometry, segment directory and tile directory; otherwise a code naming the difference.
+// *used_pool = 1 when the scan was large enough for the pool to be kicked.
+int emul_walk_compare(const uint8_t* data, size_t size, int threads, int* used_pool, int* status)
+{
+    static ImagePlan eager, lazy;
+    static WalkPool* pool = walk_pool_create();
+    Logger log;
+    const jpeggpu_status se = parse_jpeg(data, size, eager, log, false);
+    jpeggpu_status sl = parse_jpeg(data, size, lazy, log, true);
+    *used_pool = 0;
+    if (sl == JPEGGPU_SUCCESS && lazy.walk_pending) {
+        if (threads && size - lazy.scans[0].begin >= kWalkParallelMin) {
+            walk_pool_kick(pool, lazy);
+            *used_pool = 1;
+        }
+        const uint64_t before = walk_pool_stitched(pool);
+        sl = finish_deferred_walk(lazy, log, threads ? pool : nullptr);
+        if (*used_pool && walk_pool_stitched(pool) != before) *used_pool = 2; // parallel result kept
+    }
+    *status = (int)sl;
+    if (se != sl) return 1;
+    if (se != JPEGGPU_SUCCESS) return 0;
+    if (eager.num_scans != lazy.num_scans) return 2;
+    for (int s = 0; s < eager.num_scans; ++s) {
+        const ScanPlan &a = eager.scans[s], &b = lazy.scans[s];
+        if (a.begin != b.begin || a.end != b.end) return 3;
+        if (memcmp(&a.geom, &b.geom, sizeof(ScanGeom)) != 0) return 4;
+        if (a.segs.size() != b.segs.size() ||
+            memcmp(a.segs.data(), b.segs.data(), a.segs.size() * sizeof(SegDesc)) != 0)
+            return 5;
+        if (a.tiles.size() != b.tiles.size() ||
+            memcmp(a.tiles.data(), b.tiles.data(), a.tiles.size() * sizeof(TileDesc)) != 0)
+            return 6;
+    }
+    return 0;
+}
+
 } // extern "C"

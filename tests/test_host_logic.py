@@ -135,3 +135,51 @@ def test_emulated_pipeline_tuning_variants(defs):
                                            os.path.dirname(here)]))
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+# ---- deferred / parallel marker walk (csrc/parser.cpp) ------------------------------------------
+
+def _big_scan_file(seed, w=2048, h=1536, quality=97):
+    """> 1 MiB of entropy-coded data in one scan without DRI (the parallel walk's precondition)."""
+    data = inputs.pillow_jpeg(w=w, h=h, seed=seed, mode="YCbCr", subsampling=0, quality=quality)
+    assert len(data) > (1 << 20) + (1 << 17), len(data)
+    return data
+
+
+@pytest.mark.parametrize("threads", [False, True])
+def test_deferred_walk_equals_eager_walk(threads):
+    for seed in (61, 62):
+        data = _big_scan_file(seed)
+        for _ in range(3):  # the pool is reused across images
+            rc, used, st = eb.walk_compare(data, threads)
+            assert (rc, st) == (0, 0)
+            assert used == (2 if threads else 0)  # 2: the stitched parallel result was kept
+    small = inputs.pillow_jpeg(w=640, h=480, seed=63, mode="YCbCr", subsampling=2)
+    rc, used, st = eb.walk_compare(small, threads)
+    assert (rc, st, used) == (0, 0, 0)
+
+
+def test_parallel_walk_falls_back_on_markers_and_damage():
+    """Anything but data and stuffed pairs inside a counting block (restart markers without DRI,
+    fill bytes, an early EOI, truncation) must give exactly what the sequential walk gives."""
+    import test_gpu_robustness as rb
+    good = _big_scan_file(64)
+    lo, hi = rb.scan_range(good)
+    variants = [rb.mutate(good, kind, seed) for kind in rb.KINDS for seed in range(2)]
+    b = bytearray(good)
+    b[lo + 300000: lo + 300002] = b"\xff\xd3"  # one stray RSTn deep inside a counting block
+    variants.append(bytes(b))
+    b = bytearray(good)
+    cut = lo + (4096 * 37) - 1                 # a stuffed pair straddling a tile boundary
+    b[cut: cut + 2] = b"\xff\x00"
+    variants.append(bytes(b))
+    b = bytearray(good)
+    cut = lo + 65536 * 5 - 1                   # ... and a block boundary
+    b[cut: cut + 2] = b"\xff\x00"
+    variants.append(bytes(b))
+    kept = 0
+    for v in variants:
+        rc, used, st = eb.walk_compare(v, True)
+        assert rc == 0, (rc, st)
+        kept += used == 2
+    assert kept >= 2  # the straddling stuffed pairs are ordinary data: parallel result kept

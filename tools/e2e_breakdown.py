@@ -27,6 +27,8 @@ def main():
     sess = DecodeSession("cuda:0")
     if os.environ.get("JB2_EAGER_WALK") == "1":  # A/B of jpeggpu_b200_set_deferred_walk
         sess.dec.set_deferred_walk(False)
+    elif os.environ.get("JB2_WALK_THREADS") == "0":  # deferred walk on the calling thread alone
+        sess.dec.set_deferred_walk(2)
     host = pinned_bytes(data)
     sess.parse(host)
     planes = sess.alloc_planes()
