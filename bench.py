@@ -441,7 +441,7 @@ def run_ours(args):
         "cpu_baseline": cpu,
         "clocks": clocks,
     }
-    print(json.dumps(out))
+    emit(out)
 
 
 def run_reference(args):
@@ -470,7 +470,7 @@ def run_reference(args):
                      "e2e": {"value": cpu["value"], "unit": "MP/s", "h2d_bytes_per_step": 0,
                              "d2h_bytes_per_step": 0},
                      "note": "reference CUDA library unavailable: timed the CPU oracle port"})
-        print(json.dumps(base))
+        emit(base)
         return
     import numpy as np
     import torch
@@ -536,10 +536,29 @@ def run_reference(args):
                          "d2h_bytes_per_step": 4096,
                          "protocol": "parse_header+get_buffer_size+transfer+decode+4KiB D2H+sync, wall clock"},
                  "cpu_baseline": cpu, "nvjpeg": nvj, "clocks": clocks})
-    print(json.dumps(base))
+    emit(base)
+
+
+_RESULT_FD = None
+
+
+def emit(obj):
+    """The ONE JSON line of the contract, written to the process's original stdout."""
+    line = json.dumps(obj) + "\n"
+    if _RESULT_FD is None:
+        sys.stdout.write(line)
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, line.encode())
 
 
 def main():
+    # Libraries talk on stdout (NCCL prints its version line there when NCCL_DEBUG is set in the
+    # environment): keep the original stdout for the result line and point fd 1 at stderr.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
