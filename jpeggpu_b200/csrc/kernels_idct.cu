@@ -186,7 +186,7 @@ __device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
 
 constexpr int kIdctThreads = 128;
 #ifndef JB2_IDCT_MIN_CTAS
-#define JB2_IDCT_MIN_CTAS 6
+#define JB2_IDCT_MIN_CTAS 5
 #endif
 
 __global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
