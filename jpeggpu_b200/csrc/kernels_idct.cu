@@ -153,17 +153,45 @@ __device__ __forceinline__ void stage_quantisers(uint32_t (*s_q)[32], const QPai
 // Loads data unit `du` (zig-zag order), dequantises with the packed table `q` (16-byte aligned
 // shared memory) and runs both IDCT passes in registers: v[y][x] is the sample before the level
 // shift.
+#ifndef JB2_IDCT_STAGED
+#define JB2_IDCT_STAGED 1
+#endif
+// Warp-cooperative fetch of the warp's 32 data units.  Thread-per-data-unit loads touch 32
+// different 128-byte lines per instruction; here eight lanes fetch the eight 16-byte chunks of
+// ONE data unit, so an instruction covers four whole data units (4 lines), and the chunks go to
+// the owning thread through a 4 KB shared-memory tile per warp.  Chunk c of the data unit of
+// lane d sits at d*128 + ((c ^ (d & 7)) * 16): conflict-free for the stores (a quarter-warp
+// writes the eight chunks of one unit) and for the loads (eight lanes read chunk r of eight
+// consecutive units).  Every lane of the warp must call this (invalid lanes fetch nothing).
+__device__ __forceinline__ void stage_units(const int16_t* __restrict__ coef, uint32_t du, bool valid,
+                                            uint4* tile)
+{
+    const int lane = threadIdx.x & 31;
+    const int c = lane & 7, sub = lane >> 3;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int d = i * 4 + sub;
+        const uint32_t du_d = __shfl_sync(0xffffffffu, du, d);
+        const bool ok = __shfl_sync(0xffffffffu, (int)valid, d) != 0;
+        if (ok)
+            tile[d * 8 + (c ^ (d & 7))] =
+                __ldg(reinterpret_cast<const uint4*>(coef + (size_t)du_d * 64) + c);
+    }
+    __syncwarp();
+}
+
 __device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
                                           const int16_t* __restrict__ dc, uint32_t du,
-                                          const uint32_t* q, int (&v)[8][8])
+                                          const uint32_t* q, int (&v)[8][8], const uint4* tile)
 {
+    const int lane = threadIdx.x & 31;
     const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)du * 64);
     const uint4* qsrc = reinterpret_cast<const uint4*>(q);
     // the buffer holds every data unit in zig-zag order: un-zig-zag while loading (register
     // indices are compile-time constants after unrolling)
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
-        const uint4 w = src[r];
+        const uint4 w = JB2_IDCT_STAGED ? tile[lane * 8 + (r ^ (lane & 7))] : src[r];
         const uint4 qq = qsrc[r];
         const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
         const uint32_t qw[4] = {qq.x, qq.y, qq.z, qq.w};
@@ -199,10 +227,20 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
     grid_dependency_trigger();
     __syncthreads();
     DuPos pos;
-    if (!locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos)) return;
+    pos.comp = 0;
+    pos.du = 0;
+    const bool located = locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos);
+#if JB2_IDCT_STAGED
+    __shared__ uint4 s_tile[kIdctThreads / 32][256];
+    uint4* tile = s_tile[threadIdx.x >> 5];
+    stage_units(coef, pos.du, located, tile);
+#else
+    const uint4* tile = nullptr;
+#endif
+    if (!located) return;
     const int a = pos.comp;
     int v[8][8];
-    load_idct(coef, dc, pos.du, s_q[a], v);
+    load_idct(coef, dc, pos.du, s_q[a], v, tile);
 
     const int x0 = pos.bx * 8, y0 = pos.by * 8;
     const int size_x = g.size_x[a], size_y = g.size_y[a];
@@ -378,10 +416,18 @@ idct_rgbi_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16
     const int mx = mx0 + m;
     const bool valid = mx < g.mcus_x;
     int v[8][8];
+    const uint32_t du = valid ? ((uint32_t)my * (uint32_t)g.mcus_x + (uint32_t)mx) * (uint32_t)g.dus_per_mcu +
+                                    (uint32_t)(g.du_off[a] + iy * ssx + ix)
+                              : 0u;
+#if JB2_IDCT_STAGED
+    __shared__ uint4 s_tile[kRgbMaxThreads / 32][256];
+    uint4* tile = s_tile[threadIdx.x >> 5];
+    stage_units(coef, du, valid, tile);
+#else
+    const uint4* tile = nullptr;
+#endif
     if (valid) {
-        const uint32_t du = ((uint32_t)my * (uint32_t)g.mcus_x + (uint32_t)mx) * (uint32_t)g.dus_per_mcu +
-                            (uint32_t)(g.du_off[a] + iy * ssx + ix);
-        load_idct(coef, dc, du, s_q[a], v);
+        load_idct(coef, dc, du, s_q[a], v, tile);
         if (!is_y) {
 #pragma unroll
             for (int y = 0; y < 8; ++y) {
