@@ -213,34 +213,46 @@ __device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
 }
 
 constexpr int kIdctThreads = 128;
+#ifndef JB2_IDCT_UNITS
+#define JB2_IDCT_UNITS 2
+#endif
+constexpr int kIdctUnits = JB2_IDCT_STAGED ? JB2_IDCT_UNITS : 1; // data units per thread
+
 #ifndef JB2_IDCT_MIN_CTAS
 #define JB2_IDCT_MIN_CTAS 5
 #endif
 
-__global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
-idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
-            const PlaneDst out, const QPairs q)
+// cp.async flavour of stage_units: the 16-byte chunks go from global to shared memory without
+// passing through registers, so the fetch of the next data unit overlaps the IDCT of this one.
+__device__ __forceinline__ void stage_units_async(const int16_t* __restrict__ coef, uint32_t du,
+                                                  bool valid, uint4* tile)
 {
-    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
-    stage_quantisers(s_q, q);
-    grid_dependency_wait();
-    grid_dependency_trigger();
-    __syncthreads();
-    DuPos pos;
-    pos.comp = 0;
-    pos.du = 0;
-    const bool located = locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos);
-#if JB2_IDCT_STAGED
-    __shared__ uint4 s_tile[kIdctThreads / 32][256];
-    uint4* tile = s_tile[threadIdx.x >> 5];
-    stage_units(coef, pos.du, located, tile);
-#else
-    const uint4* tile = nullptr;
-#endif
-    if (!located) return;
+    const int lane = threadIdx.x & 31;
+    const int c = lane & 7, sub = lane >> 3;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int d = i * 4 + sub;
+        const uint32_t du_d = __shfl_sync(0xffffffffu, du, d);
+        const bool ok = __shfl_sync(0xffffffffu, (int)valid, d) != 0;
+        if (ok) {
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile + d * 8 + (c ^ (d & 7)));
+            const void* src = reinterpret_cast<const uint4*>(coef + (size_t)du_d * 64) + c;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
+    }
+}
+__device__ __forceinline__ void async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// Dequantise + IDCT + level shift + clamp of one data unit and its eight row stores.
+__device__ __forceinline__ void store_unit(const ScanGeom& g, const int16_t* __restrict__ coef,
+                                           const int16_t* __restrict__ dc,
+                                           const PlaneDst& out, const DuPos& pos, const uint32_t* q,
+                                           const uint4* tile)
+{
     const int a = pos.comp;
     int v[8][8];
-    load_idct(coef, dc, pos.du, s_q[a], v, tile);
+    load_idct(coef, dc, pos.du, q, v, tile);
 
     const int x0 = pos.bx * 8, y0 = pos.by * 8;
     const int size_x = g.size_x[a], size_y = g.size_y[a];
@@ -266,6 +278,50 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
                 if (x0 + x < size_x) row[x] = (uint8_t)min(max(s[x], 0), 255);
         }
     }
+}
+
+__global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
+idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
+            const PlaneDst out, const QPairs q)
+{
+    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
+    stage_quantisers(s_q, q);
+    grid_dependency_wait();
+    grid_dependency_trigger();
+    __syncthreads();
+#if JB2_IDCT_STAGED
+    // Software pipeline over kIdctUnits data units per thread: while the IDCT of one unit runs,
+    // the cp.async fetch of the next one is in flight (double-buffered tile per warp).
+    __shared__ uint4 s_tile[kIdctThreads / 32][2][256];
+    uint4* const tiles = s_tile[threadIdx.x >> 5][0];
+    const uint32_t first = blockIdx.x * (uint32_t)(kIdctThreads * kIdctUnits) + threadIdx.x;
+    DuPos pos, nxt;
+    pos.comp = nxt.comp = 0;
+    pos.du = nxt.du = 0;
+    bool located = locate(g, first, pos);
+    stage_units_async(coef, pos.du, located, tiles);
+    async_commit();
+#pragma unroll 1
+    for (int it = 0; it < kIdctUnits; ++it) {
+        const uint4* tile = tiles + (it & 1) * 256;
+        bool located_next = false;
+        if (it + 1 < kIdctUnits) {
+            located_next = locate(g, first + (uint32_t)(it + 1) * kIdctThreads, nxt);
+            stage_units_async(coef, nxt.du, located_next, tiles + ((it + 1) & 1) * 256);
+        }
+        async_commit();
+        async_wait_all_but_one();
+        __syncwarp();
+        if (located) store_unit(g, coef, dc, out, pos, s_q[pos.comp], tile);
+        __syncwarp(); // the tile is refilled two iterations from now
+        pos = nxt;
+        located = located_next;
+    }
+#else
+    DuPos pos;
+    if (!locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos)) return;
+    store_unit(g, coef, dc, out, pos, s_q[pos.comp], nullptr);
+#endif
 }
 
 // Stand-alone transpose: coded order (zig-zag inside a DU) -> planar raster int16 (row length =
@@ -581,7 +637,8 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
         dst.ptr[a] = out.ptr[a];
         dst.pitch[a] = out.pitch[a];
     }
-    return launch_dependent(idct_kernel, (total + kIdctThreads - 1) / kIdctThreads, kIdctThreads, 0,
+    const uint32_t per_cta = (uint32_t)(kIdctThreads * kIdctUnits);
+    return launch_dependent(idct_kernel, (total + per_cta - 1) / per_cta, kIdctThreads, 0,
                             stream, g, b.coef, b.dc, dst, pack_quantisers(out.q));
 }
 
