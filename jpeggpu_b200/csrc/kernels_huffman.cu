@@ -539,11 +539,31 @@ huff_write(const ScanGeom g, const ScanBufs b)
     // whole data units in shared memory and storing 16-byte vectors was 15% slower: ~3000 more
     // warp instructions per warp and, through its shared-memory tiles, one wave more of CTAs.)
     const uint32_t gs0 = first_du * 64u + qs; // global slot of this thread's first coefficient
-    for (uint32_t at = list_addr; at != list_end; at += 4u) {
+#ifndef JB2_WRITE_MERGE
+#define JB2_WRITE_MERGE 1
+#endif
+    // Two list entries that fill one aligned 32-bit word of the coefficient buffer (an even
+    // zig-zag slot and its successor - the low frequencies are usually all non-zero) leave as one
+    // store: scattered stores cost one L1 sector slot each, whatever their width.  Only words
+    // whose two halves both belong to THIS thread's list are merged, so no other thread's
+    // coefficient can be overwritten by a zero half.
+    for (uint32_t at = list_addr; at != list_end;) {
         const uint32_t e = lds32(at);
         const uint32_t slot = gs0 + (e >> 16);
-        if ((slot & 63u) == 0) b.dc[slot >> 6] = (int16_t)(e & 0xffffu);
-        else b.coef[slot] = (int16_t)(e & 0xffffu);
+        at += 4u;
+        if ((slot & 63u) == 0) {
+            b.dc[slot >> 6] = (int16_t)(e & 0xffffu);
+            continue;
+        }
+        if (JB2_WRITE_MERGE && (slot & 1u) == 0 && at != list_end) {
+            const uint32_t e2 = lds32(at);
+            if (gs0 + (e2 >> 16) == slot + 1u) {
+                *reinterpret_cast<uint32_t*>(b.coef + slot) = (e & 0xffffu) | (e2 << 16);
+                at += 4u;
+                continue;
+            }
+        }
+        b.coef[slot] = (int16_t)(e & 0xffffu);
     }
     if (lane == 0) {
         atomicMax(&b.ctrl->write_stage_ns, (uint32_t)(t1 - t0));
