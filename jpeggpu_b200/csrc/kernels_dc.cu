@@ -120,9 +120,11 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, unsigned long long* __restri
     __shared__ uint32_t warp_flag[kDcTile / 32];
     __shared__ Dc4 s_red[kDcTile / 32];
     __shared__ uint32_t s_tile;
+    // the ticket does not depend on huff_write (the counter was cleared three kernels ago and
+    // completion is transitive, kernels.hpp): take it while the predecessor is still draining
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     grid_dependency_wait();
     grid_dependency_trigger();
-    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const uint32_t tile = s_tile;
     const uint32_t tile_mcu0 = tile * kDcTile;
