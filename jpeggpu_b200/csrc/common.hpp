@@ -91,13 +91,18 @@ JB2_HD uint32_t make_entry(unsigned symbol, int code_len, bool is_dc)
 JB2_HD uint32_t entry_skip(uint32_t e) { return e >> 27; }
 JB2_HD uint32_t entry_adv(uint32_t e) { return e & 127u; }
 JB2_HD uint32_t entry_size(uint32_t e) { return (e >> 8) & 15u; }
-// Pair fields of a primary AC entry (0 if absent): when the LUT index also holds a complete
-// second AC symbol behind the first, bits 26..22 = its length in bits (code + magnitude) and bits
-// 21..15 = its slot advance.  The state-only passes (huff_sync) consume both symbols with one
-// probe; the write pass ignores the fields.
+// Pair entries (primary AC tables): when the LUT index also holds a complete second AC symbol
+// behind the first, bits 26..22 = the second symbol's length in bits (code + magnitude), bits
+// 21..15 = its slot advance, and the skip / advance fields hold the TOTALS of both symbols (the
+// size field stays that of the first).  The state-only pass (huff_sync) consumes both symbols
+// with one probe and without looking at the pair fields; the write pass first reduces an entry
+// to its first symbol (huff_core.hpp first_symbol, or once per table at staging time).
 JB2_HD uint32_t entry_skip2(uint32_t e) { return (e >> 22) & 31u; }
 JB2_HD uint32_t entry_adv2(uint32_t e) { return (e >> 15) & 127u; }
-JB2_HD uint32_t with_pair(uint32_t e, uint32_t skip2, uint32_t adv2) { return e | (skip2 << 22) | (adv2 << 15); }
+JB2_HD uint32_t with_pair(uint32_t e, uint32_t skip2, uint32_t adv2)
+{
+    return (e | (skip2 << 22) | (adv2 << 15)) + (skip2 << 27) + adv2;
+}
 
 // ---- device-visible descriptors ---------------------------------------------------------------
 

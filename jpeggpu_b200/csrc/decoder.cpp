@@ -82,9 +82,13 @@ struct jpeggpu_decoder {
     {
         walk_pool_destroy(walk_pool);
         for (StagingSlot& sl : slots) {
+            // a copy out of the block may still be queued (jpeggpu_b200_decode_batch destroys its
+            // lane decoders right after enqueueing): the pinned memory must outlive it
+            if (sl.in_flight && sl.have_event) (void)cudaEventSynchronize(sl.copied);
             if (sl.have_event) cudaEventDestroy(sl.copied);
             release_slot(sl);
         }
+        (void)cudaGetLastError();
         if (timer.created)
             for (int i = 0; i < StageTimer::kMaxMarks; ++i) cudaEventDestroy(timer.ev[i]);
     }
@@ -135,21 +139,31 @@ struct jpeggpu_decoder {
     {
         StagingSlot& sl = slots[cur_slot];
         if (!sl.pinned) return JPEGGPU_SUCCESS; // pageable source: the copy call already staged it
+        if (record_staging_event(sl, stream)) {
+            sl.in_flight = true;
+            return JPEGGPU_SUCCESS;
+        }
+        // The copy is queued but cannot be guarded by an event: wait for it here, so that the
+        // block is never rewritten under a pending DMA.
+        (void)cudaGetLastError();
+        return cudaStreamSynchronize(stream) == cudaSuccess ? JPEGGPU_SUCCESS : JPEGGPU_INTERNAL_ERROR;
+    }
+
+    bool record_staging_event(StagingSlot& sl, cudaStream_t stream)
+    {
         int dev = -1;
-        if (cudaGetDevice(&dev) != cudaSuccess) return JPEGGPU_INTERNAL_ERROR;
+        if (cudaGetDevice(&dev) != cudaSuccess) return false;
         if (sl.have_event && sl.event_device != dev) {
             cudaEventDestroy(sl.copied);
             sl.have_event = false;
         }
         if (!sl.have_event) {
             if (cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming | cudaEventBlockingSync) != cudaSuccess)
-                return JPEGGPU_INTERNAL_ERROR;
+                return false;
             sl.have_event = true;
             sl.event_device = dev;
         }
-        if (cudaEventRecord(sl.copied, stream) != cudaSuccess) return JPEGGPU_INTERNAL_ERROR;
-        sl.in_flight = true;
-        return JPEGGPU_SUCCESS;
+        return cudaEventRecord(sl.copied, stream) == cudaSuccess;
     }
 
     // Deferred entropy walk (parser.hpp): parse_header stops at the scan header of a single-scan
@@ -524,8 +538,13 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
             if (!decoder->walk_pool) decoder->walk_pool = walk_pool_create();
             walk_pool_kick(decoder->walk_pool, decoder->plan);
         }
-        JB2_CUDA(cudaMemcpyAsync(base + decoder->layout[0].off_bytes, decoder->plan.file + sp.begin,
-                                 sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream));
+        if (cudaMemcpyAsync(base + decoder->layout[0].off_bytes, decoder->plan.file + sp.begin,
+                            sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream) != cudaSuccess) {
+            (void)cudaGetLastError();
+            walk_pool_cancel(decoder->walk_pool); // no helper may read the caller's buffer after we return
+            decoder->parsed = false;
+            return JPEGGPU_INTERNAL_ERROR;
+        }
         const jpeggpu_status st = decoder->finish_walk();
         if (st != JPEGGPU_SUCCESS) return st;
         JB2_CUDA(cudaMemcpyAsync(base, decoder->staging, decoder->upload_bytes,

@@ -28,6 +28,9 @@
 //                     segment relative; slot % 64 == 0 is a DC difference)
 //   word_handle(i) -> handle of big-endian word i of the scan window the policy was built for;
 //   word(h)        -> that word; consecutive words are kWordStep handles apart
+//   probe(tbl, peek) -> primary-LUT entry for the 32 stream bits `peek` (index = its top kLutBits)
+//   slide_peek(w0, w1, w2, wn, pp, pn) -> move the window from bit position pp to pn (at most one
+//                     word further) and return the 32 stream bits at pn
 #ifndef JB2_HUFF_CORE_HPP_
 #define JB2_HUFF_CORE_HPP_
 
@@ -123,10 +126,42 @@ JB2_HD void advance_unit(uint32_t& qq, uint32_t qn, uint32_t& ch, uint32_t& tbl,
 #endif
 }
 
+// A primary AC entry may describe TWO symbols (common.hpp): its skip / advance fields then hold the
+// totals of both.  The entry of the first symbol alone:
+// (pair fields cleared, so the reduction is idempotent)
+JB2_HD uint32_t first_symbol(uint32_t e)
+{
+    return (e - (entry_skip2(e) << 27) - entry_adv2(e)) & ~((31u << 22) | (127u << 15));
+}
+
+// One step of the symbol loop, shared by both passes: consume entry `e` (pp += skip, slot counter
+// += advance, data-unit bookkeeping), slide the window and probe the table for the next symbol.
+template <class Mem>
+JB2_HD void symbol_step(const Mem& M, uint32_t& e, uint32_t& pp, uint32_t& qq, uint32_t& ch,
+                        uint32_t& tbl, SlotRec& r, uint32_t& w0, uint32_t& w1, uint32_t& w2,
+                        uint32_t& wn, uint32_t& peek)
+{
+    const uint32_t pn = pp + entry_skip(e);
+    const uint32_t qn = qq + entry_adv(e);
+    peek = M.slide_peek(w0, w1, w2, wn, pp, pn);
+    pp = pn;
+    advance_unit(qq, qn, ch, tbl, r);
+    e = M.probe(tbl, peek); // entry of the next symbol
+    r = M.rec(ch);
+}
+
 // Decode the symbols that start in [p, end).  State: p bit position inside the policy's word
 // window, q linear slot counter (q & 63 = zig-zag index), c MCU slot of the current data unit.
 // WRITE: hand every non-zero coefficient (DC differences included) to the policy's put(slot, v),
 // slot = q of the coefficient (data unit q >> 6, zig-zag index q & 63), while q < q_limit.
+//
+// The state-only pass (huff_sync; !WRITE) takes both symbols of a pair entry in one step.  That is
+// the same as two single steps iff the first symbol stays inside its data unit and the second one
+// starts before `end`.  Both hold by construction inside the FAST ZONE - zig-zag index < 48 (a
+// non-terminal AC symbol advances by at most 16) and more than kLutBits - 1 bits to go (the first
+// symbol of a pair is at most kLutBits - 1 bits long) - so the fast loop carries no pair test on
+// its dependency chain: position += skip is one shift-add on the entry.  Outside the zone, and in
+// the write pass, every entry is reduced to its first symbol.
 template <bool WRITE, class Mem>
 JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, uint32_t& c,
                         uint32_t q_limit)
@@ -140,48 +175,36 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
     uint32_t w0 = M.word(wn - 3u * Mem::kWordStep), w1 = M.word(wn - 2u * Mem::kWordStep);
     uint32_t w2 = M.word(wn - Mem::kWordStep);
     uint32_t peek = funnel_left_wrap(w0, w1, pp);
-    uint32_t e = M.lut(tbl, peek >> (32 - kLutBits));
+    uint32_t e = M.probe(tbl, peek);
+    const uint32_t end_fast = end >= (uint32_t)kLutBits ? end - (uint32_t)(kLutBits - 1) : 0u;
 
     // The loop is rotated: each iteration consumes the entry `e` of the symbol at pp and then
     // probes the LUT for the symbol that follows, so that the only branch of the hot loop is its
-    // back edge (taken while the next entry is an ordinary one) and the probe is issued before
-    // the bookkeeping of the current symbol.
+    // back edge and the probe is issued before the bookkeeping of the current symbol.
     for (;;) {
         if (e < kEntryMarkerLimit) { // rare: code longer than kLutBits
             M.note_long_code();
             const uint32_t tbls = M.slot_tbls(r.w >> 24);
             e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16, e);
+        } else if (WRITE ? !Mem::kSingleEntries : (pp >= end_fast || (qq & 48u) == 48u)) {
+            e = first_symbol(e);
         }
-        bool more;
+        bool more, fast;
         do {
-            uint32_t skip = entry_skip(e);
-            uint32_t qn = qq + entry_adv(e);
-            if (!WRITE) {
-                // state-only pass: take the second symbol of a pair entry along if the first one
-                // stays inside its data unit and the second one starts before `end`
-                const bool pair = ((qn ^ qq) & 64u) == 0 && pp + skip < end;
-                qn += pair ? entry_adv2(e) : 0u;
-                skip += pair ? entry_skip2(e) : 0u;
-            }
             if (WRITE) {
                 // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
                 // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers)
                 const uint32_t size = entry_size(e);
-                const uint32_t pos = qn - 1u;
+                const uint32_t pos = qq + entry_adv(e) - 1u;
                 if (size != 0 && ((pos ^ qq) & 64u) == 0) {
-                    const uint32_t bits = (peek << (skip - size)) >> (32 - size);
+                    const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
                     M.put(pos, extend_value(bits, size));
                 }
             }
-            const uint32_t pn = pp + skip;
-            M.slide(w0, w1, w2, wn, pp, pn);
-            pp = pn;
-            advance_unit(qq, qn, ch, tbl, r);
-            peek = funnel_left_wrap(w0, w1, pp);
-            e = M.lut(tbl, peek >> (32 - kLutBits)); // entry of the next symbol
-            r = M.rec(ch);
+            symbol_step(M, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek);
             more = pp < end && (!WRITE || qq < q_limit);
-        } while (more && e >= kEntryMarkerLimit);
+            fast = WRITE ? (more && Mem::kSingleEntries) : (pp < end_fast && (qq & 48u) != 48u);
+        } while (fast && e >= kEntryMarkerLimit);
         if (!more) break;
     }
     p = pp;
@@ -211,6 +234,7 @@ struct HostMem {
     const HuffSlow* slow_;
     const uint32_t* words_; // word 0 = first word of the restart segment
     static constexpr uint32_t kWordStep = 1;
+    static constexpr bool kSingleEntries = false; // lut() returns pair entries as built
     JB2_HD uint32_t lut(uint32_t tbl, uint32_t i) const { return lut_[(uint32_t)(tbl + i)]; }
     JB2_HD uint32_t slot_handle(uint32_t c) const { return c; }
     JB2_HD SlotRec rec(uint32_t h) const { return recs_[h]; }
@@ -218,9 +242,11 @@ struct HostMem {
     JB2_HD const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     JB2_HD uint32_t word_handle(uint32_t i) const { return i; }
     JB2_HD uint32_t word(uint32_t h) const { return words_[h]; }
-    JB2_HD void slide(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t pp, uint32_t pn) const
+    JB2_HD uint32_t probe(uint32_t tbl, uint32_t peek) const { return lut(tbl, peek >> (32 - kLutBits)); }
+    JB2_HD uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t pp, uint32_t pn) const
     {
         slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
+        return funnel_left_wrap(w0, w1, pn);
     }
     int16_t* coef_ = nullptr; // WRITE: first data unit of the restart segment
     int16_t* dc_ = nullptr;

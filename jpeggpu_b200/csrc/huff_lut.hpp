@@ -91,13 +91,18 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, Huf
     // complete symbol of the same table, record its length and advance.  The first symbol must
     // not be an end-of-block (the next symbol would be a DC symbol of another table).
     if (!is_dc) {
+        // singles first: a pair entry's own fields hold totals, so the second symbol is looked up
+        // in a copy of the table that has not been paired yet
+        std::vector<uint32_t> single(lut1, lut1 + first_long_prefix);
         for (uint32_t i = 0; i < first_long_prefix; ++i) {
-            const uint32_t e1 = lut1[i];
+            const uint32_t e1 = single[i];
             if (e1 < kEntryMarkerLimit) continue;
             const uint32_t s1 = entry_skip(e1);
             if (s1 >= (uint32_t)kLutBits || entry_adv(e1) == 64u) continue;
             const uint32_t rem = (uint32_t)kLutBits - s1;
-            const uint32_t e2 = lut1[(i << s1) & ((uint32_t)kLut1Size - 1u)]; // base fields only
+            const uint32_t i2 = (i << s1) & ((uint32_t)kLut1Size - 1u);
+            if (i2 >= first_long_prefix) continue;
+            const uint32_t e2 = single[i2];
             if (e2 < kEntryMarkerLimit || entry_skip(e2) > rem) continue;
             lut1[i] = with_pair(e1, entry_skip(e2), entry_adv(e2));
         }

@@ -79,6 +79,24 @@ JB2_HD bool boundary_ok(unsigned long long prev, unsigned long long cur)
     return (entry_g(cur) & kStateHead) != 0 || (entry_g(cur) & kStateMask) == entry_x(prev);
 }
 
+// Stores the record of subsequence m.  Two-word records go out as ONE 16-byte store on the device:
+// verify_and_repair lets several threads repair overlapping ranges, and a record assembled from
+// two writers (entry word of one, mid states of another) would pass the boundary check.
+template <typename WordPtr>
+JB2_HD void store_record(WordPtr rec_words, size_t m, unsigned long long e, const Mids& mids)
+{
+#if defined(__CUDA_ARCH__)
+    if (kRecWords == 2) {
+        asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(rec_words + kRecWords * m), "l"(e),
+                     "l"(mids_word(mids, 0))
+                     : "memory");
+        return;
+    }
+#endif
+    for (int w = 0; 2 * w < kWriteParts - 1; ++w) rec_words[kRecWords * m + 1 + w] = mids_word(mids, w);
+    rec_words[kRecWords * m] = e;
+}
+
 // repair: re-decode forward from subsequence j (entry = exit of j-1) until the
 // stored records agree again.  M addresses words relative to the segment start; rec_words holds
 // kRecWords 64-bit words per record.  Returns the number of records rewritten.
@@ -93,9 +111,7 @@ JB2_HD uint32_t relink_from(const Mem& M, const SegDesc& seg, WordPtr rec_words,
         if (m != j && (entry_g(rec_words[kRecWords * (size_t)m]) & kStateMask) == state) break;
         Mids mids;
         const unsigned long long e = decode_sub(M, seg_bits, m - seg.sub_off, state, &mids);
-        for (int w = 0; 2 * w < kWriteParts - 1; ++w)
-            rec_words[kRecWords * (size_t)m + 1 + w] = mids_word(mids, w);
-        rec_words[kRecWords * (size_t)m] = e;
+        store_record(rec_words, (size_t)m, e, mids);
         state = entry_x(e);
         ++rewritten;
     }

@@ -103,13 +103,25 @@ __device__ __forceinline__ void make_device_recs(const ScanGeom& g, SharedTables
 // destuffed scan (zero outside [0, total_words)).
 // Staging in two steps so that the first can run before the producer of the destuffed scan has
 // finished (programmatic dependent launch): the decode tables come from the upload block...
+// SINGLE (huff_write): pair entries are reduced to their first symbol on the way in.  Words
+// below kEntryMarkerLimit (table headers, markers) have empty pair fields and pass unchanged.
+template <bool SINGLE>
 __device__ __forceinline__ void stage_tables(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
                                              const int WIN_WORDS)
 {
     const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
     const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
     uint4* ldst = s_dyn + WIN_WORDS / 4;
-    for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
+    for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) {
+        uint4 v = __ldg(lsrc + i);
+        if (SINGLE) {
+            v.x = v.x < kEntryMarkerLimit ? v.x : first_symbol(v.x);
+            v.y = v.y < kEntryMarkerLimit ? v.y : first_symbol(v.y);
+            v.z = v.z < kEntryMarkerLimit ? v.z : first_symbol(v.z);
+            v.w = v.w < kEntryMarkerLimit ? v.w : first_symbol(v.w);
+        }
+        ldst[i] = v;
+    }
     if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(ldst));
 }
 // ...the window of the scan from the destuff kernel's output.  Ends with a barrier.
@@ -134,6 +146,7 @@ struct DevMem {
     uint32_t recs_addr;
     uint32_t win_addr;
     static constexpr uint32_t kWordStep = 4;
+    static constexpr bool kSingleEntries = false;
     __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
     __device__ __forceinline__ uint32_t slot_handle(uint32_t c) const
     {
@@ -144,16 +157,33 @@ struct DevMem {
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t word_handle(uint32_t i) const { return win_addr + i * 4u; }
     __device__ __forceinline__ uint32_t word(uint32_t h) const { return lds32(h); }
-    // one LOP3 with predicate output + predicated moves and the predicated look-ahead load
-    __device__ __forceinline__ void slide(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
-                                          uint32_t pp, uint32_t pn) const
+    // The probe address in two dependent instructions: mask the index bits, multiply-high-add.
+    __device__ __forceinline__ uint32_t probe(uint32_t tbl, uint32_t peek) const
     {
-        asm volatile("{\n\t.reg .pred s;\n\t.reg .b32 t;\n\t"
-                     "xor.b32 t, %4, %5;\n\tand.b32 t, t, 32;\n\tsetp.ne.u32 s, t, 0;\n\t"
-                     "@s mov.b32 %0, %1;\n\t@s mov.b32 %1, %2;\n\t@s ld.shared.u32 %2, [%3];\n\t"
-                     "@s add.u32 %3, %3, 4;\n\t}"
-                     : "+r"(w0), "+r"(w1), "+r"(w2), "+r"(wn)
+        uint32_t addr;
+        asm("mad.hi.u32 %0, %1, %2, %3;"
+            : "=r"(addr)
+            : "r"(peek & (0xffffffffu << (32 - kLutBits))), "r"(1u << (kLutBits + 2)), "r"(tbl));
+        return lds32(addr);
+    }
+    // Both candidate windows are shifted as soon as the new position is known; the "crossed a
+    // word boundary" predicate only selects between the two results, so the dependency chain of
+    // the symbol loop is position -> funnel shift -> select.  The window registers themselves
+    // move by predicated instructions off that chain, with the look-ahead load for the NEXT slide.
+    __device__ __forceinline__ uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
+                                                   uint32_t pp, uint32_t pn) const
+    {
+        uint32_t peek;
+        asm volatile("{\n\t.reg .pred s;\n\t.reg .b32 t, a, b;\n\t"
+                     "shf.l.wrap.b32 a, %2, %1, %5;\n\t"
+                     "shf.l.wrap.b32 b, %3, %2, %5;\n\t"
+                     "xor.b32 t, %5, %6;\n\tand.b32 t, t, 32;\n\tsetp.ne.u32 s, t, 0;\n\t"
+                     "selp.b32 %0, b, a, s;\n\t"
+                     "@s mov.b32 %1, %2;\n\t@s mov.b32 %2, %3;\n\t@s ld.shared.u32 %3, [%4];\n\t"
+                     "@s add.u32 %4, %4, 4;\n\t}"
+                     : "=r"(peek), "+r"(w0), "+r"(w1), "+r"(w2), "+r"(wn)
                      : "r"(pn), "r"(pp));
+        return peek;
     }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
@@ -164,6 +194,7 @@ struct DevMem {
 // odd number of words apart); huff_write turns the lists into data units afterwards, all lanes
 // working on one list at a time.
 struct WriteMem : DevMem {
+    static constexpr bool kSingleEntries = true; // huff_write stages the tables with first_symbol()
     mutable uint32_t list_ptr; // shared address of the next entry
     uint32_t slot0;            // first slot of this thread's half subsequence (segment relative)
     __device__ __forceinline__ void put(uint32_t slot, int v) const
@@ -182,6 +213,7 @@ struct GlobalMem {
     uint32_t recs_addr;
     const uint32_t* words;
     static constexpr uint32_t kWordStep = 1;
+    static constexpr bool kSingleEntries = false;
     __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
     __device__ __forceinline__ uint32_t slot_handle(uint32_t c) const
     {
@@ -192,10 +224,15 @@ struct GlobalMem {
     __device__ __forceinline__ const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     __device__ __forceinline__ uint32_t word_handle(uint32_t i) const { return i; }
     __device__ __forceinline__ uint32_t word(uint32_t h) const { return __ldg(words + h); }
-    __device__ __forceinline__ void slide(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
-                                          uint32_t pp, uint32_t pn) const
+    __device__ __forceinline__ uint32_t probe(uint32_t tbl, uint32_t peek) const
+    {
+        return lut(tbl, peek >> (32 - kLutBits));
+    }
+    __device__ __forceinline__ uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
+                                                   uint32_t pp, uint32_t pn) const
     {
         slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
+        return funnel_left_wrap(w0, w1, pn);
     }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
@@ -240,16 +277,37 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
 #pragma unroll
     for (int k = 0; k < kWriteParts - 1; ++k) mids.v[k] = 0;
     unsigned long long rec = active ? decode_sub(M, seg_bits, i, entry, &mids) : 0ull;
+    // One-entry memo: the evaluation this lane held before the current one.  A lane inside a
+    // stretch that is slow to synchronise alternates between the state of the decoder that is
+    // right and the state of one that is not yet (each arrives from the left one pass after the
+    // other); switching back is then free, and the iteration needs as many decoding passes as an
+    // oracle that picks the right neighbour state would (tools/sim/sync_sim.cpp: 18 -> 10 passes
+    // for the slowest warp of the 12 MP workload, 34 -> 15 on IMG_6510.JPG).
+    uint32_t memo_entry = 0xffffffffu; // no packed state has bit 16 set
+    unsigned long long memo_rec = 0ull;
+    Mids memo_mids = mids;
+    auto adopt = [&](uint16_t want) {
+        const uint32_t old_entry = entry;
+        const unsigned long long old_rec = rec;
+        const Mids old_mids = mids;
+        entry = want;
+        if (memo_entry == (uint32_t)want) {
+            rec = memo_rec;
+            mids = memo_mids;
+        } else {
+            rec = decode_sub(M, seg_bits, i, entry, &mids);
+        }
+        memo_entry = old_entry;
+        memo_rec = old_rec;
+        memo_mids = old_mids;
+    };
     auto iterate = [&](int frozen) {
         for (;;) {
             const uint16_t px = (uint16_t)__shfl_up_sync(0xffffffffu, (uint32_t)entry_x(rec), 1);
             const uint16_t want = (lane <= frozen || head || !active) ? entry : px;
             const bool changed = want != entry;
             if (!__any_sync(0xffffffffu, changed)) break;
-            if (changed) {
-                entry = want;
-                rec = decode_sub(M, seg_bits, i, entry, &mids);
-            }
+            if (changed) adopt(want);
         }
     };
     iterate(0);
@@ -272,8 +330,7 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
         const uint16_t assumed = (uint16_t)__shfl_sync(0xffffffffu, (uint32_t)entry, kOverlapSubs);
         if (left != 0 && (uint16_t)(left & 0xffffu) != assumed) { // warp-uniform
             if (lane == kOverlapSubs) {
-                entry = (uint16_t)(left & 0xffffu);
-                rec = decode_sub(M, seg_bits, i, entry, &mids);
+                adopt((uint16_t)(left & 0xffffu));
                 atomicAdd(&b.ctrl->relinked, 1u);
             }
             iterate(kOverlapSubs);
@@ -334,7 +391,7 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     const unsigned long long t0 = now_ns();
     const long long win_sub0 = (long long)blockIdx.x * kSyncUseful - kOverlapSubs;
     // before the destuff kernel is done: tables into shared memory, zero-fill of the output
-    stage_tables(g, b, st, kSyncWinWords);
+    stage_tables<false>(g, b, st, kSyncWinWords);
     zero_fill(b.coef, b.coef_bytes);
     zero_fill(b.dc, b.dc_bytes);
     grid_dependency_wait();
@@ -463,7 +520,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
     const int win_words = (int)(subs_per_cta * kSubWords + kWinMargin);
     // before huff_sync is done (the control block was cleared two kernels ago): ticket, tables
     if (threadIdx.x == 0) s_cta = atomicAdd(&b.ctrl->write_ticket, 1u);
-    stage_tables(g, b, st, win_words);
+    stage_tables<true>(g, b, st, win_words);
     grid_dependency_wait();
     grid_dependency_trigger();
     __syncthreads();

@@ -462,7 +462,7 @@ struct WalkPool {
     bool stop = false;
     std::shared_ptr<WalkJob> job; // the job of the image being transferred (guarded by m)
     uint64_t generation = 0;
-    const ImagePlan* kicked_for = nullptr;
+    uint64_t kicked_for = 0; // ImagePlan::generation of the image the job was cut from (0: none)
     uint64_t stitched = 0; // walks completed on the parallel path (tests, diagnostics)
 
     void worker()
@@ -502,7 +502,7 @@ void walk_pool_destroy(WalkPool* pool)
 void walk_pool_kick(WalkPool* pool, const ImagePlan& plan)
 {
     if (!pool || !plan.walk_pending) return;
-    pool->kicked_for = nullptr;
+    pool->kicked_for = 0;
     const ScanPlan& sp = plan.scans[0];
     const size_t avail = plan.file_size - sp.begin; // the scan runs to the EOI at the end of the file
     if (avail < kWalkParallelMin) return;
@@ -519,10 +519,27 @@ void walk_pool_kick(WalkPool* pool, const ImagePlan& plan)
             ++pool->generation;
         }
         pool->cv.notify_all();
-        pool->kicked_for = &plan;
+        pool->kicked_for = plan.generation;
     } catch (...) { // no threads / no memory: the sequential walk needs neither
-        pool->kicked_for = nullptr;
+        pool->kicked_for = 0;
     }
+}
+
+namespace {
+// take every block that has not been handed out; wait for the ones in progress
+void drain_job(WalkJob& job)
+{
+    const uint32_t taken = job.next.exchange(job.num_blocks, std::memory_order_relaxed);
+    const uint32_t started = taken < job.num_blocks ? taken : job.num_blocks;
+    while (job.done.load(std::memory_order_acquire) < started) std::this_thread::yield();
+}
+} // namespace
+
+void walk_pool_cancel(WalkPool* pool)
+{
+    if (!pool || !pool->kicked_for || !pool->job) return;
+    pool->kicked_for = 0;
+    drain_job(*pool->job);
 }
 
 namespace {
@@ -532,10 +549,13 @@ namespace {
 bool walk_parallel(WalkPool* pool, const ImagePlan& plan, Cursor& cur, ScanPlan& sp,
                    jpeggpu_status* status)
 {
-    if (!pool || pool->kicked_for != &plan || !pool->job) return false;
-    pool->kicked_for = nullptr;
+    if (!pool || pool->kicked_for == 0 || pool->kicked_for != plan.generation || !pool->job) return false;
+    pool->kicked_for = 0;
     const std::shared_ptr<WalkJob> job = pool->job;
-    if (job->scan_begin != cur.p) return false;
+    if (job->scan_begin != cur.p) {
+        drain_job(*job);
+        return false;
+    }
     const uint64_t counted = (uint64_t)job->num_blocks * kWalkBlock;
     // tail first (only this thread can do it), then help with the counting blocks
     sp.segs.clear();
@@ -734,6 +754,7 @@ jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, con
     Cursor cur{data, data, data + size};
     plan.st = ParseState{};
     plan.walk_pending = false;
+    ++plan.generation;
     plan.width = plan.height = plan.num_comp = 0;
     plan.restart_interval = 0;
     plan.num_scans = 0;

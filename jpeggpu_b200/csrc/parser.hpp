@@ -62,6 +62,7 @@ struct ImagePlan {
     // true: scans[0] holds an upper-bound geometry (scan_bytes, num_subs, num_segments) and empty
     // directories; finish_deferred_walk() must run before the directories are used.
     bool walk_pending = false;
+    uint64_t generation = 0; // bumped by every parse: identifies the image a helper job belongs to
 };
 
 struct Logger {
@@ -94,6 +95,9 @@ void walk_pool_destroy(WalkPool* pool);
 uint64_t walk_pool_stitched(const WalkPool* pool); // walks that completed on the parallel path
 // Hands the counting blocks of plan.scans[0] to the helpers (no-op for small scans).
 void walk_pool_kick(WalkPool* pool, const ImagePlan& plan);
+// Withdraws a kicked job that will not be collected (transfer failed after the kick): returns once
+// no helper is reading the file any more.
+void walk_pool_cancel(WalkPool* pool);
 
 // Walks the deferred scan, replaces the bounds in scans[0] by the exact values and resumes the
 // marker loop behind the scan (same statuses as the eager parse).  No-op unless walk_pending.

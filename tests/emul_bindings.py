@@ -30,6 +30,7 @@ def lib():
         L.emul_parse.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
         L.emul_decode_scan.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t,
                                        C.c_void_p, C.c_size_t, C.c_void_p]
+        L.emul_pair_equivalence.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_long)]
         L.emul_walk_compare.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_int),
                                         C.POINTER(C.c_int)]
         _lib = L
@@ -43,6 +44,14 @@ def walk_compare(data: bytes, threads: bool):
     used, st = C.c_int(), C.c_int()
     rc = lib().emul_walk_compare(buf.ctypes.data, len(data), int(threads), C.byref(used), C.byref(st))
     return rc, used.value, st.value
+
+
+def pair_equivalence(data: bytes, tries=3):
+    """(records that differ between pair stepping and single stepping, pair entries in the LUTs)."""
+    buf = np.frombuffer(data, dtype=np.uint8)
+    pairs = C.c_long()
+    bad = lib().emul_pair_equivalence(buf.ctypes.data, len(data), tries, C.byref(pairs))
+    return bad, pairs.value
 
 
 def parse(data: bytes):

@@ -131,6 +131,9 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         uint16_t entry[32];
         unsigned long long rec[32];
         Mids mid[32];
+        uint32_t memo_entry[32]; // the one-entry memo of sync_chunk (kernels_huffman.cu)
+        unsigned long long memo_rec[32];
+        Mids memo_mid[32];
         for (int l = 0; l < 32; ++l) {
             const long long sub = (long long)chunk_first - kOverlapSubs + l;
             active[l] = sub >= 0 && sub < (long long)N;
@@ -138,6 +141,9 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
             entry[l] = 0;
             rec[l] = 0;
             mid[l] = Mids{};
+            memo_entry[l] = 0xffffffffu;
+            memo_rec[l] = 0;
+            memo_mid[l] = Mids{};
             if (!active[l]) continue;
             k[l] = find_segment(sp.segs.data(), g.num_segments, (uint32_t)sub);
             const SegDesc& seg = sp.segs[k[l]];
@@ -147,6 +153,23 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
             rec[l] = decode_sub(mem_of(seg), seg_bits[l], i[l], 0, &mid[l]);
         }
         int chunk_passes = 1;
+        auto adopt = [&](int l, uint16_t want) { // returns true when a decode was needed
+            const uint32_t old_entry = entry[l];
+            const unsigned long long old_rec = rec[l];
+            const Mids old_mid = mid[l];
+            entry[l] = want;
+            const bool hit = memo_entry[l] == (uint32_t)want;
+            if (hit) {
+                rec[l] = memo_rec[l];
+                mid[l] = memo_mid[l];
+            } else {
+                rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l], &mid[l]);
+            }
+            memo_entry[l] = old_entry;
+            memo_rec[l] = old_rec;
+            memo_mid[l] = old_mid;
+            return !hit;
+        };
         auto iterate = [&](int frozen) {
             int rounds = 0;
             for (;;) {
@@ -158,16 +181,16 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
                     any |= want[l] != entry[l];
                 }
                 if (!any) break;
-                ++rounds;
+                bool decoded = false;
                 for (int l = 0; l < 32; ++l)
                     if (want[l] != entry[l]) {
                         if (rounds >= 4 && getenv("EMUL_DIAG")) {
                             const uint16_t d = want[l] ^ entry[l];
                             ++diag[(d & 0x1f) ? 0 : (d & 0x7e00) ? 1 : 2]; // o differs / z differs / c only
                         }
-                        entry[l] = want[l];
-                        rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l], &mid[l]);
+                        decoded |= adopt(l, want[l]);
                     }
+                if (decoded) ++rounds; // passes in which some lane had to decode
             }
             if (rounds >= 100 && getenv("EMUL_DIAG")) {
                 fprintf(stderr, "chunk %u rounds %d frozen %d n:", chunk, rounds, frozen);
@@ -185,9 +208,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         if (chunk > 0 && !head[kOverlapSubs]) {
             const uint32_t left = mailbox[chunk - 1];
             if ((uint16_t)(left & 0xffffu) != entry[kOverlapSubs]) {
-                const int l = kOverlapSubs;
-                entry[l] = (uint16_t)(left & 0xffffu);
-                rec[l] = decode_sub(mem_of(sp.segs[k[l]]), seg_bits[l], i[l], entry[l], &mid[l]);
+                adopt(kOverlapSubs, (uint16_t)(left & 0xffffu));
                 ++relinked;
                 iterate(kOverlapSubs);
                 mailbox[chunk] = 0x80000000u | entry_x(rec[last_lane]);
@@ -276,6 +297,82 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     for (size_t du = 0; du < need / 64; ++du)
         for (int z = 0; z < 64; ++z) coef[du * 64 + kNat[z]] = zz[du * 64 + z];
     return 0;
+}
+
+// Pair-step equivalence: the state-only pass consumes two symbols per probe inside its fast zone
+// (huff_core.hpp decode_span<false>); the result must equal single stepping for ANY entry state,
+// also the speculative ones the fix-point feeds it.  Decodes every subsequence of scan 0 from the
+// cold state and from `tries` pseudo-random entry states with both and returns the number of
+// differing records (0 expected), or a negative parse error.
+struct SingleMem : HostMem { // every primary entry reduced to its first symbol
+    JB2_HD uint32_t lut(uint32_t tbl, uint32_t i) const
+    {
+        const uint32_t e = lut_[(uint32_t)(tbl + i)];
+        return e < kEntryMarkerLimit ? e : first_symbol(e);
+    }
+    JB2_HD uint32_t probe(uint32_t tbl, uint32_t peek) const { return lut(tbl, peek >> (32 - kLutBits)); }
+    JB2_HD uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t pp, uint32_t pn) const
+    {
+        slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
+        return funnel_left_wrap(w0, w1, pn);
+    }
+};
+
+int emul_pair_equivalence(const uint8_t* data, size_t size, int tries, long* pairs_possible)
+{
+    static ImagePlan plan;
+    Logger log;
+    if (parse_jpeg(data, size, plan, log) != JPEGGPU_SUCCESS) return -1;
+    ScanPlan& sp = plan.scans[0];
+    ScanGeom& g = sp.geom;
+    std::vector<uint32_t> pool;
+    HuffSlow slow[kMaxTables];
+    for (int t = 0; t < g.num_tables; ++t) g.table_off[t] = build_lut(sp.tables[t], pool, slow[t]);
+    long pairs = 0;
+    for (uint32_t e : pool) pairs += e >= kEntryMarkerLimit && entry_skip2(e) != 0;
+    if (pairs_possible) *pairs_possible = pairs;
+    SlotRec recs[kMaxDuPerMcu];
+    uint32_t tbls[kMaxDuPerMcu];
+    make_slot_recs(g, recs, tbls);
+    const uint32_t N = g.num_subs;
+    std::vector<uint8_t> dst((size_t)N * kSubBytes + 64, 0);
+    {
+        const uint8_t* src = data + sp.begin;
+        uint32_t kept = 0, seg = 0, prev = 0;
+        for (uint32_t i = 0; i < g.scan_bytes; ++i) {
+            const uint32_t b = src[i];
+            const bool after_ff = prev == 0xff;
+            if ((after_ff ? b == 0 : b != 0xff) && (int)seg < g.num_segments) {
+                const SegDesc& sd = sp.segs[seg];
+                dst[(kept - sd.kept_before + sd.sub_off * (uint32_t)kSubBytes) ^ 3u] = after_ff ? 0xff : (uint8_t)b;
+                ++kept;
+            }
+            if (after_ff && b >= 0xd0 && b <= 0xd7) ++seg;
+            prev = b;
+        }
+    }
+    const uint32_t* words = reinterpret_cast<const uint32_t*>(dst.data());
+    int bad = 0;
+    uint32_t rng = 12345u;
+    for (int k = 0; k < g.num_segments; ++k) {
+        const SegDesc& seg = sp.segs[k];
+        HostMem pm{pool.data(), recs, tbls, slow, words + (size_t)seg.sub_off * kSubWords};
+        SingleMem sm;
+        static_cast<HostMem&>(sm) = pm;
+        const uint32_t n = subs_in_segment(seg);
+        for (uint32_t i = 0; i < n; ++i)
+            for (int t = 0; t <= tries; ++t) {
+                rng = rng * 1664525u + 1013904223u;
+                const uint16_t gs = t == 0 ? 0 : pack_state((rng >> 8) % 32u, (rng >> 13) % (uint32_t)g.dus_per_mcu, (rng >> 20) % 64u);
+                Mids ma, mb;
+                const unsigned long long a = decode_sub(pm, seg.nbytes * 8u, i, gs, &ma);
+                const unsigned long long b = decode_sub(sm, seg.nbytes * 8u, i, gs, &mb);
+                bool same = a == b;
+                for (int w = 0; w < kWriteParts - 1; ++w) same &= ma.v[w] == mb.v[w];
+                bad += same ? 0 : 1;
+            }
+    }
+    return bad;
 }
 
 // Walk equivalence: eager parse vs deferred parse + finish, sequential (threads = 0) or with the

@@ -80,6 +80,23 @@ def test_parser_statuses_match_oracle():
         assert st == ost, (len(s), st, ost)
 
 
+@pytest.mark.parametrize("case", [
+    dict(w=643, h=477, seed=3, mode="YCbCr", subsampling=2),
+    dict(w=500, h=375, seed=7, mode="YCbCr", subsampling=2, restart_blocks=7),
+    dict(w=500, h=375, seed=8, mode="YCbCr", subsampling=0, optimize=True, quality=98),
+    dict(w=500, h=375, seed=9, mode="YCbCr", subsampling=2, optimize=True, quality=20),
+    dict(w=320, h=240, seed=5, mode="CMYK"),
+], ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items()))
+def test_pair_steps_equal_single_steps(case):
+    """huff_sync consumes two symbols per table probe inside its fast zone (zig-zag index < 48,
+    more than 10 bits to go); records must equal single stepping for every subsequence from the
+    cold state and from arbitrary (speculative) entry states."""
+    data = inputs.pillow_jpeg(**case)
+    bad, pairs = eb.pair_equivalence(data, tries=4)
+    assert pairs > 0, "the tables hold no pair entries: nothing was tested"
+    assert bad == 0
+
+
 def test_img6510_emulated():
     data = inputs.img6510()
     if data is None:
