@@ -18,6 +18,12 @@
 #define JB2_HD inline
 #endif
 
+#if defined(__GNUC__) || defined(__CUDACC__)
+#define JB2_UNLIKELY(x) __builtin_expect(!!(x), 0)
+#else
+#define JB2_UNLIKELY(x) (x)
+#endif
+
 namespace jb2 {
 
 constexpr int kMaxComp = 4;       // JPEGGPU_MAX_COMP (include/jpeggpu/jpeggpu.h:33)

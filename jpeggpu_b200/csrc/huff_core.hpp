@@ -178,34 +178,35 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
     uint32_t e = M.probe(tbl, peek);
     const uint32_t end_fast = end >= (uint32_t)kLutBits ? end - (uint32_t)(kLutBits - 1) : 0u;
 
-    // The loop is rotated: each iteration consumes the entry `e` of the symbol at pp and then
-    // probes the LUT for the symbol that follows, so that the only branch of the hot loop is its
-    // back edge and the probe is issued before the bookkeeping of the current symbol.
+    // One flat loop: every iteration consumes the entry `e` of the symbol at pp and probes the
+    // table for the symbol that follows.  The rare cases (a code longer than kLutBits, an entry
+    // that has to be reduced to its first symbol) are branches INSIDE the body that rejoin before
+    // the step, so the lanes of a warp stay in lock step: a lane that meets a rare case costs the
+    // warp that case once, whereas an inner fast loop that such lanes leave makes them wait
+    // until every other lane has left it too, and the warp then runs the loop again for them.
     for (;;) {
-        if (e < kEntryMarkerLimit) { // rare: code longer than kLutBits
-            M.note_long_code();
-            const uint32_t tbls = M.slot_tbls(r.w >> 24);
-            e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16, e);
-        } else if (WRITE ? !Mem::kSingleEntries : (pp >= end_fast || (qq & 48u) == 48u)) {
-            e = first_symbol(e);
-        }
-        bool more, fast;
-        do {
-            if (WRITE) {
-                // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
-                // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers)
-                const uint32_t size = entry_size(e);
-                const uint32_t pos = qq + entry_adv(e) - 1u;
-                if (size != 0 && ((pos ^ qq) & 64u) == 0) {
-                    const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
-                    M.put(pos, extend_value(bits, size));
-                }
+        const bool reduce = WRITE ? !Mem::kSingleEntries : (pp >= end_fast || (qq & 48u) == 48u);
+        if (JB2_UNLIKELY((e < kEntryMarkerLimit) | reduce)) {
+            if (e < kEntryMarkerLimit) { // rare: code longer than kLutBits
+                M.note_long_code();
+                const uint32_t tbls = M.slot_tbls(r.w >> 24);
+                e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16, e);
+            } else {
+                e = first_symbol(e);
             }
-            symbol_step(M, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek);
-            more = pp < end && (!WRITE || qq < q_limit);
-            fast = WRITE ? (more && Mem::kSingleEntries) : (pp < end_fast && (qq & 48u) != 48u);
-        } while (fast && e >= kEntryMarkerLimit);
-        if (!more) break;
+        }
+        if (WRITE) {
+            // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
+            // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers)
+            const uint32_t size = entry_size(e);
+            const uint32_t pos = qq + entry_adv(e) - 1u;
+            if (size != 0 && ((pos ^ qq) & 64u) == 0) {
+                const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
+                M.put(pos, extend_value(bits, size));
+            }
+        }
+        symbol_step(M, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek);
+        if (!(pp < end && (!WRITE || qq < q_limit))) break;
     }
     p = pp;
     q = qq;

@@ -284,6 +284,7 @@ int main(int argc, char** argv)
         long cost = 0;
         int passes = 0;
         long pass_cost = 0;
+        long span_max[8] = {0};
         auto full_decode = [&](Lane& l, uint16_t g, bool first_time) {
             const Eval& e = sim.eval(l.j, g);
             long steps = e.steps[CK - 1];
@@ -302,6 +303,8 @@ int main(int argc, char** argv)
             l.cur = e;
             ++st.decodes;
             pass_cost = std::max(pass_cost, steps);
+            for (int k = 0; k < CK; ++k)
+                span_max[k] = std::max<long>(span_max[k], e.steps[k] - (k ? e.steps[k - 1] : 0));
         };
         auto adopt = [&](Lane& l, uint16_t g) { // returns true if a decode was needed
             for (size_t m = 0; m < l.memo.size(); ++m)
@@ -345,7 +348,13 @@ int main(int argc, char** argv)
             for (int l = 0; l < 32; ++l)
                 if (L[l].active) full_decode(L[l], 0, true);
         }
-        cost += pass_cost + 3;
+        auto close_pass = [&]() {
+            long simt = 0;
+            for (int k = 0; k < CK; ++k) simt += span_max[k], span_max[k] = 0;
+            if (getenv("SIMT")) pass_cost = simt;
+            cost += pass_cost + 3;
+        };
+        close_pass();
         ++passes;
         auto iterate = [&](int frozen) {
             for (;;) {
@@ -371,7 +380,7 @@ int main(int argc, char** argv)
                 bool decoded = false;
                 for (int l = 0; l < 32; ++l)
                     if (changed[l]) decoded |= adopt(L[l], want[l]);
-                cost += pass_cost + 3;
+                close_pass();
                 if (decoded) ++passes;
             }
         };
@@ -381,7 +390,7 @@ int main(int argc, char** argv)
             ++st.relink;
             pass_cost = 0;
             adopt(L[o.overlap], truth[L[o.overlap].j]);
-            cost += pass_cost + 3;
+            close_pass();
             ++passes;
             iterate(o.overlap);
         }
