@@ -53,22 +53,38 @@ constexpr int kDestuffBytesPerThread = 16;
 constexpr int kDestuffTile = kDestuffThreads * kDestuffBytesPerThread; // stuffed bytes per CTA
 
 // ---- Huffman lookup tables -------------------------------------------------------------------
-// One table = header (8 words) + primary LUT (2^kLutBits words, indexed by the next kLutBits
-// bits) + secondary LUT (lut2_size words, indexed by peek16 - base16) for codes longer than
-// kLutBits + slow-path arrays for pathological tables whose long-code region exceeds kLut2Max.
+// One table = header (kLutHeader words: [0] base16, [1] secondary size, [2] word offset of the
+// secondary LUT from the primary one, [3] 1 if a singles half follows the primary LUT)
+//   + primary LUT (2^kLutBits words, indexed by the next kLutBits bits; AC tables: pair entries)
+//   + AC tables only: the same LUT with every entry reduced to its first symbol ("singles half")
+//   + secondary LUT (indexed by peek16 - base16) for codes longer than kLutBits
+//   + slow-path arrays (HuffSlow) for pathological tables whose long-code region exceeds kLut2Max.
 // Entry (32 bit): bits 31-27 total bits to skip (code length + magnitude bits, >= 1),
 //                 bits 11-8 magnitude size, bits 6-0 slot advance (run + 1; 64 = end of block).
 // The skip field sits at the top so that "position += skip" is a single shift-add and the
-// advance at the bottom so that it is a single mask; an entry whose skip field is zero is a
-// marker (kEntryLong / kEntrySlow).
+// advance at the bottom so that it is a single mask.
+// A code longer than kLutBits has no branch of its own in the symbol loop; it takes two steps:
+// the primary entry is a CONTINUATION (kEntryCont set): skip = kContBits - every long code starts
+// with that many one bits, because the long-code region is the top <= kLut2Max values of the
+// 16-bit code space - advance 0, size 0, and bits 26-12 = where the next probe goes instead of
+// the regular table (in 16-byte units from the start of the LUT pool): the base of the table's
+// secondary LUT, indexed like a primary one by the kLutBits bits that follow.  (The base lies
+// before the entries that can actually be reached: index i stands for the 16-bit prefix
+// 0xF800 + i, and prefixes below base16 never arrive there.)  Secondary entries are ordinary
+// ones whose skip no longer counts the kContBits bits already consumed.
+// kEntrySlow (all other fields zero; pathological tables whose long-code region exceeds kLut2Max)
+// makes the step a no-op: the symbol loop notices that the position did not move and leaves.
 #ifndef JB2_LUT_BITS
 #define JB2_LUT_BITS 11
 #endif
 constexpr int kLutBits = JB2_LUT_BITS;
 constexpr int kLut1Size = 1 << kLutBits;
-constexpr int kLut2Max = 2048;
-constexpr uint32_t kEntryLong = 1u; // primary miss: go to the secondary LUT
-constexpr uint32_t kEntrySlow = 2u; // secondary miss: canonical length search
+constexpr int kLut2Max = kLut1Size; // a secondary LUT is probed like a primary one
+constexpr int kLutHeader = 8;
+constexpr uint32_t kContBits = 16 - kLutBits;           // 5: one bits consumed by a continuation entry
+constexpr uint32_t kContBase16 = 0x10000u - kLut2Max;   // 0xF800: first prefix a secondary LUT can hold
+constexpr uint32_t kEntryCont = 1u << 7;                // flag: continuation entry
+constexpr uint32_t kEntrySlow = 2u << 12;               // canonical length search (no-op step)
 constexpr uint32_t kEntryMarkerLimit = 1u << 27; // e < limit  <=>  marker
 
 struct HuffSlow {       // canonical decode data (T.81 F.2.2.3), used by the slow path only
@@ -94,6 +110,11 @@ JB2_HD uint32_t make_entry(unsigned symbol, int code_len, bool is_dc)
     const unsigned skip = (unsigned)code_len + size; // <= 16 + 15
     return (skip << 27) | (size << 8) | adv;
 }
+JB2_HD uint32_t make_cont(uint32_t pool_off_vec16) // pool_off_vec16: secondary base / 16 bytes
+{
+    return (kContBits << 27) | (pool_off_vec16 << 12) | kEntryCont;
+}
+JB2_HD uint32_t entry_cont_vec16(uint32_t e) { return (e >> 12) & 0x7fffu; }
 JB2_HD uint32_t entry_skip(uint32_t e) { return e >> 27; }
 JB2_HD uint32_t entry_adv(uint32_t e) { return e & 127u; }
 JB2_HD uint32_t entry_size(uint32_t e) { return (e >> 8) & 15u; }
@@ -173,8 +194,9 @@ struct ScanGeom { // by-value kernel parameter describing one scan
     int blocks_x[kMaxComp], blocks_y[kMaxComp]; // coded plane size in DUs (MCU padded)
     int size_x[kMaxComp], size_y[kMaxComp];     // output plane size in samples
     uint32_t du_prefix[kMaxComp + 1];           // prefix sum of blocks_x*blocks_y
-    uint32_t table_off[kMaxTables];             // word offset of each table in the LUT pool
+    uint32_t table_off[kMaxTables];             // word offset of each table's primary LUT in the pool
     uint32_t lut_pool_words;                    // total 32-bit words in the pool
+    uint32_t lut_compact_words;                 // words huff_write stages: header + one LUT half + secondary per table
 };
 
 struct OutPlanes {

@@ -72,6 +72,7 @@ struct jpeggpu_decoder {
         std::vector<uint32_t> pool;
         HuffSlow slow[kMaxTables];
         uint32_t table_off[kMaxTables];
+        uint32_t compact_words = 0;
     } lut_cache[kMaxScans];
     std::vector<uint8_t> lut_key;
     StageTimer timer;
@@ -204,10 +205,15 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
             for (int t = 0; t < sp.geom.num_tables; ++t)
                 lc.table_off[t] = build_lut(sp.tables[t], lc.pool, lc.slow[t]);
             while (lc.pool.size() & 3) lc.pool.push_back(0); // staged with 16-byte loads
+            lc.compact_words = 0; // what huff_write stages: header + one primary LUT + secondary
+            for (int t = 0; t < sp.geom.num_tables; ++t)
+                lc.compact_words += (uint32_t)(kLutHeader + kLut1Size) +
+                                    ((lc.pool[lc.table_off[t] - kLutHeader + 1] + 3u) & ~3u);
             lc.key = lut_key;
         }
         for (int t = 0; t < sp.geom.num_tables; ++t) sp.geom.table_off[t] = lc.table_off[t];
         sp.geom.lut_pool_words = (uint32_t)lc.pool.size();
+        sp.geom.lut_compact_words = lc.compact_words;
         if (sp.geom.lut_pool_words > 40 * 1024) return JPEGGPU_NOT_SUPPORTED; // > 160 KiB of LUTs
     }
     for (int s = 0; s < plan.num_scans; ++s) {

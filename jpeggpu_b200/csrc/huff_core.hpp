@@ -20,7 +20,8 @@
 //
 // Memory access goes through a policy type `Mem` (shared memory on the device, plain arrays on
 // the host):
-//   lut(tbl, i)    -> entry i of the table with handle tbl
+//   lut(tbl, i)    -> entry i of the table with handle tbl;  single_of(tbl) -> its singles half
+//   cont_table(e)  -> handle of the table a continuation entry points to (long codes)
 //   slot_handle(c) -> handle of MCU slot c;  rec(h) -> SlotRec of that slot
 //   slot_tbls(c)   -> dc table slot | ac table slot << 8   (slow path only)
 //   slow(slot)     -> HuffSlow
@@ -31,6 +32,7 @@
 //   probe(tbl, peek) -> primary-LUT entry for the 32 stream bits `peek` (index = its top kLutBits)
 //   slide_peek(w0, w1, w2, wn, pp, pn) -> move the window from bit position pp to pn (at most one
 //                     word further) and return the 32 stream bits at pn
+//   step<WRITE>(...) -> the bookkeeping of one symbol (generic_step, or the policy's own form)
 #ifndef JB2_HUFF_CORE_HPP_
 #define JB2_HUFF_CORE_HPP_
 
@@ -59,21 +61,6 @@ JB2_HD uint32_t slow_entry(const HuffSlow& t, uint32_t peek16)
     return make_entry(sym, l, t.is_dc != 0);
 }
 
-// second-level lookup for codes longer than kLutBits
-template <class Mem>
-JB2_HD uint32_t lookup_long(const Mem& M, uint32_t tbl, uint32_t tbl_slot, uint32_t peek16,
-                            uint32_t e)
-{
-    if (e == kEntryLong) {
-        const uint32_t base16 = M.lut(tbl, (uint32_t)-8);
-        const uint32_t n2 = M.lut(tbl, (uint32_t)-7);
-        const uint32_t i2 = peek16 - base16;
-        e = i2 < n2 ? M.lut(tbl, (uint32_t)kLut1Size + i2) : kEntrySlow;
-    }
-    if (e == kEntrySlow) e = slow_entry(M.slow(tbl_slot), peek16);
-    return e;
-}
-
 JB2_HD int extend_value(uint32_t bits, uint32_t size)
 {
     // T.81 F.2.2.1 (src/decode_huffman.cu:196-200); size >= 1
@@ -94,7 +81,7 @@ JB2_HD uint32_t funnel_left_wrap(uint32_t hi, uint32_t lo, uint32_t shift)
 // The window holds the two words being decoded (w0, w1) and the one after them (w2), which is
 // loaded at slide time for the NEXT slide - at least 32 bits of symbols later - so the load
 // latency never sits on the symbol-to-symbol dependency chain.  Policies provide
-// slide(w0, w1, w2, wn, pp, pn); this is the portable form.
+// slide_peek(w0, w1, w2, wn, pp, pn); this is the portable form.
 template <class Mem>
 JB2_HD void slide_window_generic(const Mem& M, uint32_t& w0, uint32_t& w1, uint32_t& w2,
                                  uint32_t& wn, uint32_t pp, uint32_t pn)
@@ -107,61 +94,57 @@ JB2_HD void slide_window_generic(const Mem& M, uint32_t& w0, uint32_t& w1, uint3
     }
 }
 
-// End of a data unit (EOB / slot 63; advance <= 64, so at most one boundary is crossed): the
-// slot counter snaps to the boundary, the MCU slot and the table move on.
-JB2_HD void advance_unit(uint32_t& qq, uint32_t qn, uint32_t& ch, uint32_t& tbl, const SlotRec& r)
-{
-#if defined(__CUDA_ARCH__)
-    asm("{\n\t.reg .pred d;\n\t.reg .b32 t;\n\t"
-        "xor.b32 t, %3, %0;\n\tand.b32 t, t, 64;\n\tsetp.ne.u32 d, t, 0;\n\t"
-        "mov.b32 %0, %3;\n\t@d and.b32 %0, %3, 0xffffffc0;\n\t"
-        "@d mov.b32 %1, %6;\n\tselp.b32 %2, %5, %4, d;\n\t}"
-        : "+r"(qq), "+r"(ch), "=r"(tbl)
-        : "r"(qn), "r"(r.x), "r"(r.y), "r"(r.z));
-#else
-    const bool done = ((qn ^ qq) & 64u) != 0;
-    qq = done ? (qn & ~63u) : qn;
-    ch = done ? r.z : ch;
-    tbl = done ? r.y : r.x;
-#endif
-}
-
-// A primary AC entry may describe TWO symbols (common.hpp): its skip / advance fields then hold the
-// totals of both.  The entry of the first symbol alone:
-// (pair fields cleared, so the reduction is idempotent)
-JB2_HD uint32_t first_symbol(uint32_t e)
-{
-    return (e - (entry_skip2(e) << 27) - entry_adv2(e)) & ~((31u << 22) | (127u << 15));
-}
-
-// One step of the symbol loop, shared by both passes: consume entry `e` (pp += skip, slot counter
-// += advance, data-unit bookkeeping), slide the window and probe the table for the next symbol.
-template <class Mem>
-JB2_HD void symbol_step(const Mem& M, uint32_t& e, uint32_t& pp, uint32_t& qq, uint32_t& ch,
-                        uint32_t& tbl, SlotRec& r, uint32_t& w0, uint32_t& w1, uint32_t& w2,
-                        uint32_t& wn, uint32_t& peek)
-{
-    const uint32_t pn = pp + entry_skip(e);
-    const uint32_t qn = qq + entry_adv(e);
-    peek = M.slide_peek(w0, w1, w2, wn, pp, pn);
-    pp = pn;
-    advance_unit(qq, qn, ch, tbl, r);
-    e = M.probe(tbl, peek); // entry of the next symbol
-    r = M.rec(ch);
-}
-
 // Decode the symbols that start in [p, end).  State: p bit position inside the policy's word
 // window, q linear slot counter (q & 63 = zig-zag index), c MCU slot of the current data unit.
 // WRITE: hand every non-zero coefficient (DC differences included) to the policy's put(slot, v),
 // slot = q of the coefficient (data unit q >> 6, zig-zag index q & 63), while q < q_limit.
 //
-// The state-only pass (huff_sync; !WRITE) takes both symbols of a pair entry in one step.  That is
-// the same as two single steps iff the first symbol stays inside its data unit and the second one
-// starts before `end`.  Both hold by construction inside the FAST ZONE - zig-zag index < 48 (a
-// non-terminal AC symbol advances by at most 16) and more than kLutBits - 1 bits to go (the first
-// symbol of a pair is at most kLutBits - 1 bits long) - so the fast loop carries no pair test on
-// its dependency chain: position += skip is one shift-add on the entry.  Outside the zone, and in
-// the write pass, every entry is reduced to its first symbol.
+// One step: position += skip(e), slot counter += advance(e), end-of-data-unit bookkeeping (EOB /
+// slot 63: the counter snaps to the boundary, the MCU slot and the table move on), probe the table
+// for the symbol that follows.  The loop's ONLY branch is its back edge, and its condition - the
+// position moved and is still below `end` - is known at the start of the step, long before the
+// branch issues (a predicate that comes fresh out of the table probe costs ~20 cycles of
+// predicate-to-branch latency per symbol on sm_100).  What would need a branch on the entry is
+// data instead:
+//  * a code longer than kLutBits takes two ordinary steps: its primary entry is a continuation
+//    (common.hpp) that consumes the code's leading one bits and names the table of the next
+//    probe - one more select on the table address.  (An exit from the loop instead makes the
+//    lane wait for the slowest lane of its warp, which then waits for it: measured +50 % on the
+//    write pass, +100 % on the sync pass of a photo with 0.6 % long codes.)  The span cannot end
+//    between the two steps: the loop continues after a continuation whatever the position.
+//    Only pathological tables (long-code region > kLut2Max) still leave the loop: their entry
+//    kEntrySlow is a no-op step, noticed because the position did not move;
+//  * the state-only pass (huff_sync; !WRITE) takes both symbols of a pair entry in one step,
+//    which equals two single steps iff the first symbol stays inside its data unit and the
+//    second starts before `end`.  Both hold by construction while the zig-zag index is < 48 (a
+//    non-terminal AC symbol advances by at most 16) and more than kLutBits - 1 bits remain (the
+//    first symbol of a pair is shorter than kLutBits).  Elsewhere the NEXT probe simply goes to
+//    the singles half of the AC table: a select on the table address, nothing on the chain of
+//    the bit position.  The write pass only ever sees singles (its slot records point there).
+// The bookkeeping of one step in portable form (policies may provide an equivalent `step`):
+// consumes entry `e` at position pp; returns bit 0 = the loop goes on, bit 1 = the position moved.
+template <bool WRITE, class Mem>
+JB2_HD uint32_t generic_step(const Mem& M, uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch,
+                             uint32_t& tbl, const SlotRec& r, uint32_t& w0, uint32_t& w1,
+                             uint32_t& w2, uint32_t& wn, uint32_t& peek, uint32_t end,
+                             uint32_t end_fast, uint32_t q_limit)
+{
+    const uint32_t pn = pp + entry_skip(e);
+    const uint32_t qn = qq + entry_adv(e);
+    peek = M.slide_peek(w0, w1, w2, wn, pp, pn);
+    const bool moved = pn != pp;
+    pp = pn;
+    // advance <= 64 (single) or <= 80 from an index < 48 (pair): one boundary at most
+    const bool unit_done = ((qn ^ qq) & 64u) != 0;
+    const bool pairs_ok = WRITE || (pn < end_fast && ((~qn) & 48u) != 0u); // index < 48
+    const bool cont = (e & kEntryCont) != 0;
+    tbl = cont ? M.cont_table(e) : unit_done ? r.y : pairs_ok ? r.x : M.single_of(r.x);
+    qq = unit_done ? (qn & ~63u) : qn;
+    ch = unit_done ? r.z : ch;
+    const bool go_on = moved && (cont || (pn < end && (!WRITE || qq < q_limit)));
+    return (go_on ? 1u : 0u) | (moved ? 2u : 0u);
+}
+
 template <bool WRITE, class Mem>
 JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, uint32_t& c,
                         uint32_t q_limit)
@@ -170,43 +153,37 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
     uint32_t pp = p, qq = q;
     uint32_t ch = M.slot_handle(c);
     SlotRec r = M.rec(ch);
-    uint32_t tbl = (qq & 63u) == 0 ? (r.w & 0xffffffu) : r.x;
+    const uint32_t end_fast = end >= (uint32_t)kLutBits ? end - (uint32_t)(kLutBits - 1) : 0u;
+    uint32_t tbl = (qq & 63u) == 0 ? (r.w & 0xffffffu)
+                   : (!WRITE && (pp >= end_fast || (qq & 48u) == 48u)) ? M.single_of(r.x) : r.x;
     uint32_t wn = M.word_handle((pp >> 5) + 3u);
     uint32_t w0 = M.word(wn - 3u * Mem::kWordStep), w1 = M.word(wn - 2u * Mem::kWordStep);
     uint32_t w2 = M.word(wn - Mem::kWordStep);
     uint32_t peek = funnel_left_wrap(w0, w1, pp);
     uint32_t e = M.probe(tbl, peek);
-    const uint32_t end_fast = end >= (uint32_t)kLutBits ? end - (uint32_t)(kLutBits - 1) : 0u;
-
-    // One flat loop: every iteration consumes the entry `e` of the symbol at pp and probes the
-    // table for the symbol that follows.  The rare cases (a code longer than kLutBits, an entry
-    // that has to be reduced to its first symbol) are branches INSIDE the body that rejoin before
-    // the step, so the lanes of a warp stay in lock step: a lane that meets a rare case costs the
-    // warp that case once, whereas an inner fast loop that such lanes leave makes them wait
-    // until every other lane has left it too, and the warp then runs the loop again for them.
     for (;;) {
-        const bool reduce = WRITE ? !Mem::kSingleEntries : (pp >= end_fast || (qq & 48u) == 48u);
-        if (JB2_UNLIKELY((e < kEntryMarkerLimit) | reduce)) {
-            if (e < kEntryMarkerLimit) { // rare: code longer than kLutBits
-                M.note_long_code();
-                const uint32_t tbls = M.slot_tbls(r.w >> 24);
-                e = lookup_long(M, tbl, (qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8), peek >> 16, e);
-            } else {
-                e = first_symbol(e);
+        uint32_t flags;
+        do {
+            if (WRITE) {
+                // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
+                // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers);
+                // continuations and kEntrySlow have size 0
+                const uint32_t size = entry_size(e);
+                const uint32_t pos = qq + entry_adv(e) - 1u;
+                if (size != 0 && ((pos ^ qq) & 64u) == 0) {
+                    const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
+                    M.put(pos, extend_value(bits, size));
+                }
             }
-        }
-        if (WRITE) {
-            // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
-            // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers)
-            const uint32_t size = entry_size(e);
-            const uint32_t pos = qq + entry_adv(e) - 1u;
-            if (size != 0 && ((pos ^ qq) & 64u) == 0) {
-                const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
-                M.put(pos, extend_value(bits, size));
-            }
-        }
-        symbol_step(M, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek);
-        if (!(pp < end && (!WRITE || qq < q_limit))) break;
+            flags = M.template step<WRITE>(e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
+            e = M.probe(tbl, peek); // entry of the next symbol
+            r = M.rec(ch);
+        } while (flags & 1u);
+        if (flags & 2u) break;
+        // the position did not move: kEntrySlow, a long code of a pathological table
+        M.note_long_code();
+        const uint32_t tbls = M.slot_tbls(r.w >> 24);
+        e = slow_entry(M.slow((qq & 63u) == 0 ? (tbls & 0xffu) : (tbls >> 8)), peek >> 16);
     }
     p = pp;
     q = qq;
@@ -214,12 +191,13 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
 }
 
 // Fills the per-slot records with host-style handles (word offsets and slot indices).
-JB2_HD void make_slot_recs(const ScanGeom& g, SlotRec* recs, uint32_t* tbls)
+// singles: the AC handle points at the singles half of the table (write pass).
+JB2_HD void make_slot_recs(const ScanGeom& g, SlotRec* recs, uint32_t* tbls, bool singles = false)
 {
     for (int s = 0; s < kMaxDuPerMcu; ++s) {
         const int cur = s < g.dus_per_mcu ? s : 0;
         const int nxt = cur + 1 == g.dus_per_mcu ? 0 : cur + 1;
-        recs[s].x = g.table_off[g.slot_ac[cur]];
+        recs[s].x = g.table_off[g.slot_ac[cur]] + (singles ? (uint32_t)kLut1Size : 0u);
         recs[s].y = g.table_off[g.slot_dc[nxt]];
         recs[s].z = (uint32_t)nxt;
         recs[s].w = g.table_off[g.slot_dc[cur]] | ((uint32_t)cur << 24);
@@ -234,9 +212,11 @@ struct HostMem {
     const uint32_t* tbls_; // per MCU slot: dc table slot | ac table slot << 8
     const HuffSlow* slow_;
     const uint32_t* words_; // word 0 = first word of the restart segment
+    const uint32_t* table_off_ = nullptr; // ScanGeom::table_off (long codes only)
     static constexpr uint32_t kWordStep = 1;
-    static constexpr bool kSingleEntries = false; // lut() returns pair entries as built
     JB2_HD uint32_t lut(uint32_t tbl, uint32_t i) const { return lut_[(uint32_t)(tbl + i)]; }
+    JB2_HD uint32_t single_of(uint32_t tbl) const { return tbl + (uint32_t)kLut1Size; }
+    JB2_HD uint32_t cont_table(uint32_t e) const { return entry_cont_vec16(e) * 4u; }
     JB2_HD uint32_t slot_handle(uint32_t c) const { return c; }
     JB2_HD SlotRec rec(uint32_t h) const { return recs_[h]; }
     JB2_HD uint32_t slot_tbls(uint32_t c) const { return tbls_[c]; }
@@ -248,6 +228,13 @@ struct HostMem {
     {
         slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
         return funnel_left_wrap(w0, w1, pn);
+    }
+    template <bool WRITE>
+    JB2_HD uint32_t step(uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch, uint32_t& tbl,
+                         const SlotRec& r, uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
+                         uint32_t& peek, uint32_t end, uint32_t end_fast, uint32_t q_limit) const
+    {
+        return generic_step<WRITE>(*this, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
     }
     int16_t* coef_ = nullptr; // WRITE: first data unit of the restart segment
     int16_t* dc_ = nullptr;

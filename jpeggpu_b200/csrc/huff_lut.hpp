@@ -12,8 +12,6 @@
 
 namespace jb2 {
 
-constexpr int kLutHeader = 8; // words before the primary LUT: [0] base16, [1] lut2 size
-
 // Appends one table to `pool`; returns the u16 offset of its primary LUT. Fills `slow`.
 inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, HuffSlow& slow)
 {
@@ -53,24 +51,36 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, Huf
             if (aligned < base16) base16 = aligned;
         }
     uint32_t lut2_size = 0x10000u - base16;
-    const bool truncated = lut2_size > (uint32_t)kLut2Max;
-    if (truncated) lut2_size = kLut2Max;
+    const bool truncated = lut2_size > (uint32_t)kLut2Max; // pathological: canonical search instead
+    if (truncated) lut2_size = 0;
+    const uint32_t lut2_alloc = (lut2_size + 3u) & ~3u; // every piece stays 16-byte aligned
+    const uint32_t lut2_off = is_dc ? (uint32_t)kLut1Size : 2u * (uint32_t)kLut1Size;
 
     const size_t header_at = pool.size();
-    pool.resize(header_at + kLutHeader + kLut1Size + lut2_size);
+    pool.resize(header_at + kLutHeader + lut2_off + lut2_alloc);
     uint32_t* hdr = pool.data() + header_at;
     uint32_t* lut1 = hdr + kLutHeader;
-    uint32_t* lut2 = lut1 + kLut1Size;
+    uint32_t* lut2 = lut1 + lut2_off;
     for (int i = 0; i < kLutHeader; ++i) hdr[i] = 0;
     hdr[0] = base16; // 0x10000 with lut2_size 0: never matches
     hdr[1] = lut2_size;
+    hdr[2] = lut2_off;
+    hdr[3] = is_dc ? 0u : 1u;
     // unused code space: behave like the reference's forced 16-bit termination
     // (src/decode_huffman.cu:177-193) with symbol 0
     const uint32_t invalid = make_entry(0, 16, is_dc);
     for (int i = 0; i < kLut1Size; ++i) lut1[i] = invalid;
-    for (uint32_t i = 0; i < lut2_size; ++i) lut2[i] = truncated ? kEntrySlow : invalid;
+    // secondary entries are reached through a continuation entry that has already consumed
+    // kContBits bits of the code
+    const uint32_t consumed = (uint32_t)kContBits << 27;
+    for (uint32_t i = 0; i < lut2_alloc; ++i) lut2[i] = invalid - consumed;
     const uint32_t first_long_prefix = base16 >> (16 - kLutBits);
-    for (uint32_t i = first_long_prefix; i < (uint32_t)kLut1Size; ++i) lut1[i] = kEntryLong;
+    // where a continuation sends the next probe: index i of that probe stands for the 16-bit
+    // prefix kContBase16 + i, the entry of prefix base16 is lut2[0]
+    const uint32_t lut2_word = (uint32_t)(header_at + kLutHeader) + lut2_off; // pool word offset of lut2[0]
+    const uint32_t cont = truncated ? kEntrySlow
+                                    : make_cont((lut2_word - (base16 - kContBase16)) / 4u);
+    for (uint32_t i = first_long_prefix; i < (uint32_t)kLut1Size; ++i) lut1[i] = cont;
 
     for (int i = 0; i < nsym; ++i) {
         const int l = len_of[i];
@@ -84,7 +94,7 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, Huf
             const uint32_t first = ((uint32_t)code_of[i] << (16 - l)) - base16;
             const uint32_t n = 1u << (16 - l);
             for (uint32_t j = 0; j < n; ++j)
-                if (first + j < lut2_size) lut2[first + j] = e;
+                if (first + j < lut2_size) lut2[first + j] = e - consumed;
         }
     }
     // Pair fields (AC tables): if the index bits behind a complete first symbol hold another
@@ -106,6 +116,10 @@ inline uint32_t build_lut(const HuffSpec& spec, std::vector<uint32_t>& pool, Huf
             if (e2 < kEntryMarkerLimit || entry_skip(e2) > rem) continue;
             lut1[i] = with_pair(e1, entry_skip(e2), entry_adv(e2));
         }
+        // singles half: what the write pass decodes with, and the state-only pass where a pair
+        // could straddle the end of its span or of a data unit
+        uint32_t* singles = lut1 + kLut1Size;
+        for (uint32_t i = 0; i < (uint32_t)kLut1Size; ++i) singles[i] = i < first_long_prefix ? single[i] : lut1[i];
     }
     // short codes that fall inside the long region's prefixes cannot exist (canonical order puts
     // every short code numerically below every long code), so the two levels never conflict.

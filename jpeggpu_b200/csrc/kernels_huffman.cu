@@ -55,6 +55,7 @@ static_assert(kSyncWinWords % 4 == 0 && kSubWords % 4 == 0, "window must be uint
 struct __align__(16) SharedTables {
     SlotRec recs[kMaxDuPerMcu]; // device handles: shared-memory byte addresses
     uint32_t tbls[kMaxDuPerMcu];
+    uint32_t tbase[kMaxTables]; // shared address of every table's primary LUT (header in front)
 };
 
 extern __shared__ __align__(16) uint4 s_dyn[]; // [window words | LUT pool]
@@ -85,44 +86,79 @@ __device__ __forceinline__ SlotRec lds_rec(uint32_t addr)
 }
 
 // Converts the host-style slot records into shared-memory addresses (thread 0, before the
-// barrier in stage()).  lut_addr = shared address of the LUT pool.
-__device__ __forceinline__ void make_device_recs(const ScanGeom& g, SharedTables& st, uint32_t lut_addr)
+// barrier in stage_window()).  st.tbase[] must be set.  SINGLE: AC handles point at singles.
+__device__ __forceinline__ void make_device_recs(const ScanGeom& g, SharedTables& st, bool staged_singles)
 {
-    make_slot_recs(g, st.recs, st.tbls);
     const uint32_t recs_addr = smem_addr(st.recs);
     for (int s = 0; s < kMaxDuPerMcu; ++s) {
+        const int cur = s < g.dus_per_mcu ? s : 0;
+        const int nxt = cur + 1 == g.dus_per_mcu ? 0 : cur + 1;
         SlotRec& r = st.recs[s];
-        r.x = lut_addr + r.x * 4u;
-        r.y = lut_addr + r.y * 4u;
-        r.z = recs_addr + r.z * (uint32_t)sizeof(SlotRec);
-        r.w = (lut_addr + (r.w & 0xffffffu) * 4u) | (r.w & 0xff000000u);
+        // the compact staging of huff_write holds ONLY the singles half, at the table base
+        r.x = st.tbase[g.slot_ac[cur]];
+        r.y = st.tbase[g.slot_dc[nxt]];
+        r.z = recs_addr + (uint32_t)nxt * (uint32_t)sizeof(SlotRec);
+        r.w = st.tbase[g.slot_dc[cur]] | ((uint32_t)cur << 24);
+        st.tbls[s] = (uint32_t)g.slot_dc[cur] | ((uint32_t)g.slot_ac[cur] << 8);
     }
+    (void)staged_singles;
 }
 
-// Stage the LUT pool, the slot records and words [first_word, first_word + win_words) of the
-// destuffed scan (zero outside [0, total_words)).
+// Stage the decode tables and words [first_word, first_word + win_words) of the destuffed scan
+// (zero outside [0, total_words)).
 // Staging in two steps so that the first can run before the producer of the destuffed scan has
 // finished (programmatic dependent launch): the decode tables come from the upload block...
-// SINGLE (huff_write): pair entries are reduced to their first symbol on the way in.  Words
-// below kEntryMarkerLimit (table headers, markers) have empty pair fields and pass unchanged.
+// SINGLE (huff_write): per table only header + ONE primary LUT (the singles half of an AC table)
+// + secondary LUT are staged, back to back, so the pool costs the write kernel no more shared
+// memory than a plain table set; huff_sync takes the pool as it is.
 template <bool SINGLE>
 __device__ __forceinline__ void stage_tables(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
                                              const int WIN_WORDS)
 {
-    const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
-    const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
     uint4* ldst = s_dyn + WIN_WORDS / 4;
-    for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) {
-        uint4 v = __ldg(lsrc + i);
-        if (SINGLE) {
-            v.x = v.x < kEntryMarkerLimit ? v.x : first_symbol(v.x);
-            v.y = v.y < kEntryMarkerLimit ? v.y : first_symbol(v.y);
-            v.z = v.z < kEntryMarkerLimit ? v.z : first_symbol(v.z);
-            v.w = v.w < kEntryMarkerLimit ? v.w : first_symbol(v.w);
+    const uint32_t lut_addr = smem_addr(ldst);
+    if (!SINGLE) {
+        const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
+        const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
+        for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
+        if (threadIdx.x == 0) {
+            for (int t = 0; t < g.num_tables; ++t) st.tbase[t] = lut_addr + g.table_off[t] * 4u;
+            make_device_recs(g, st, false);
         }
-        ldst[i] = v;
+        return;
     }
-    if (threadIdx.x == 0) make_device_recs(g, st, smem_addr(ldst));
+    uint32_t at = 0; // 16-byte vectors staged so far (uniform)
+    for (int t = 0; t < g.num_tables; ++t) {
+        const uint32_t* hdr = b.lut_pool + g.table_off[t] - kLutHeader;
+        const uint4 h = __ldg(reinterpret_cast<const uint4*>(hdr)); // base16, n2, off2, has singles
+        const uint32_t n2_vec = (h.y + 3u) / 4u;
+        const uint4* lut1 = reinterpret_cast<const uint4*>(hdr + kLutHeader + (h.w ? kLut1Size : 0));
+        const uint4* lut2 = reinterpret_cast<const uint4*>(hdr + kLutHeader + h.z);
+        uint4* dst = ldst + at;
+        if (threadIdx.x == 0) {
+            dst[0] = make_uint4(h.x, h.y, (uint32_t)kLut1Size, 0u);
+            dst[1] = make_uint4(0u, 0u, 0u, 0u);
+            st.tbase[t] = lut_addr + (at + kLutHeader / 4) * 16u;
+        }
+        dst += kLutHeader / 4;
+        // continuation entries name the secondary LUT by its place in the pool: re-base them
+        const uint32_t pool_vec = (g.table_off[t] + h.z) / 4u;                 // secondary LUT in the pool
+        const uint32_t here_vec = at + (uint32_t)(kLutHeader + kLut1Size) / 4; // ... and in this staging
+        const uint32_t rebase = ((here_vec - pool_vec) & 0x7fffu) << 12;
+        auto fix = [rebase](uint32_t v) {
+            return (v & kEntryCont) ? ((v & ~(0x7fffu << 12)) | ((v + rebase) & (0x7fffu << 12))) : v;
+        };
+        for (uint32_t i = threadIdx.x; i < (uint32_t)kLut1Size / 4; i += blockDim.x) {
+            uint4 v = __ldg(lut1 + i);
+            v.x = fix(v.x), v.y = fix(v.y), v.z = fix(v.z), v.w = fix(v.w);
+            dst[i] = v;
+        }
+        dst += kLut1Size / 4;
+        for (uint32_t i = threadIdx.x; i < n2_vec; i += blockDim.x) dst[i] = __ldg(lut2 + i);
+        at += (uint32_t)(kLutHeader + kLut1Size) / 4 + n2_vec;
+    }
+    // tbase[] was written by thread 0 itself: no barrier needed before it builds the records
+    if (threadIdx.x == 0) make_device_recs(g, st, true);
 }
 // ...the window of the scan from the destuff kernel's output.  Ends with a barrier.
 __device__ __forceinline__ void stage_window(const ScanGeom& g, const ScanBufs& b,
@@ -145,9 +181,81 @@ struct DevMem {
     const HuffSlow* slow_;
     uint32_t recs_addr;
     uint32_t win_addr;
+    uint32_t lut_addr; // shared address of the staged LUT pool
     static constexpr uint32_t kWordStep = 4;
-    static constexpr bool kSingleEntries = false;
     __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
+    __device__ __forceinline__ uint32_t single_of(uint32_t tbl) const { return tbl + (uint32_t)kLut1Size * 4u; }
+    // continuation field: 16-byte units from the start of the staged LUT pool (dynamic shared memory
+    // behind the window; stage_tables<true> re-bases the field for its compact layout)
+    __device__ __forceinline__ uint32_t cont_table(uint32_t e) const { return lut_addr + ((e >> 8) & 0x7fff0u); }
+    // generic_step (huff_core.hpp) with every decision as a select: ptxas turns the C++ form into
+    // three branches per symbol.  Only the loop's back edge branches, on a predicate that is
+    // ready long before it issues.
+    template <bool WRITE>
+    __device__ __forceinline__ uint32_t step(uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch,
+                                             uint32_t& tbl, const SlotRec& r, uint32_t& w0, uint32_t& w1,
+                                             uint32_t& w2, uint32_t& wn, uint32_t& peek, uint32_t end,
+                                             uint32_t end_fast, uint32_t q_limit) const
+    {
+        uint32_t flags;
+        asm volatile(
+            "{\n\t"
+            ".reg .pred s, d, po, c, mv, go, ql;\n\t"
+            ".reg .b32 t, a, b, pn, qn, x2, ct;\n\t"
+            "shr.u32 t, %10, 27;\n\t"
+            "add.u32 pn, %1, t;\n\t"
+            "and.b32 t, %10, 127;\n\t"
+            "add.u32 qn, %2, t;\n\t"
+            // window: both candidates, then select; the registers slide off the chain
+            "shf.l.wrap.b32 a, %6, %5, pn;\n\t"
+            "shf.l.wrap.b32 b, %7, %6, pn;\n\t"
+            "xor.b32 t, pn, %1;\n\t"
+            "and.b32 t, t, 32;\n\t"
+            "setp.ne.u32 s, t, 0;\n\t"
+            "selp.b32 %9, b, a, s;\n\t"
+            "@s mov.b32 %5, %6;\n\t"
+            "@s mov.b32 %6, %7;\n\t"
+            "@s ld.shared.u32 %7, [%8];\n\t"
+            "@s add.u32 %8, %8, 4;\n\t"
+            // end of the data unit?
+            "xor.b32 t, qn, %2;\n\t"
+            "and.b32 t, t, 64;\n\t"
+            "setp.ne.u32 d, t, 0;\n\t"
+            // pairs allowed for the next probe: zig-zag index < 48 and far enough from `end`
+            "not.b32 t, qn;\n\t"
+            "and.b32 t, t, 48;\n\t"
+            "setp.ne.u32 po, t, 0;\n\t"
+            "setp.lt.and.u32 po, pn, %15, po;\n\t"
+            "and.b32 t, %10, 128;\n\t"
+            "setp.ne.u32 c, t, 0;\n\t"
+            // table of the next probe
+            "add.u32 x2, %11, %17;\n\t"
+            "selp.b32 t, %11, x2, po;\n\t"
+            "selp.b32 t, %12, t, d;\n\t"
+            "shr.u32 ct, %10, 8;\n\t"
+            "and.b32 ct, ct, 0x7fff0;\n\t"
+            "add.u32 ct, ct, %16;\n\t"
+            "selp.b32 %4, ct, t, c;\n\t"
+            // slot counter and MCU slot
+            "and.b32 t, qn, 0xffffffc0;\n\t"
+            "selp.b32 %2, t, qn, d;\n\t"
+            "selp.b32 %3, %13, %3, d;\n\t"
+            // loop control: moved && (cont || (pn < end && slot counter < q_limit))
+            "setp.ne.u32 mv, pn, %1;\n\t"
+            "setp.lt.u32 ql, %2, %18;\n\t"
+            "setp.lt.and.u32 go, pn, %14, ql;\n\t"
+            "or.pred go, go, c;\n\t"
+            "and.pred go, go, mv;\n\t"
+            "selp.u32 %0, 1, 0, go;\n\t"
+            "@mv or.b32 %0, %0, 2;\n\t"
+            "mov.b32 %1, pn;\n\t"
+            "}"
+            : "=&r"(flags), "+r"(pp), "+r"(qq), "+r"(ch), "=&r"(tbl), "+r"(w0), "+r"(w1), "+r"(w2), "+r"(wn),
+              "=&r"(peek)
+            : "r"(e), "r"(r.x), "r"(r.y), "r"(r.z), "r"(end), "r"(WRITE ? 0xffffffffu : end_fast),
+              "r"(lut_addr), "r"(WRITE ? 0u : (uint32_t)kLut1Size * 4u), "r"(WRITE ? q_limit : 0xffffffffu));
+        return flags;
+    }
     __device__ __forceinline__ uint32_t slot_handle(uint32_t c) const
     {
         return recs_addr + c * (uint32_t)sizeof(SlotRec);
@@ -194,7 +302,6 @@ struct DevMem {
 // odd number of words apart); huff_write turns the lists into data units afterwards, all lanes
 // working on one list at a time.
 struct WriteMem : DevMem {
-    static constexpr bool kSingleEntries = true; // huff_write stages the tables with first_symbol()
     mutable uint32_t list_ptr; // shared address of the next entry
     uint32_t slot0;            // first slot of this thread's half subsequence (segment relative)
     __device__ __forceinline__ void put(uint32_t slot, int v) const
@@ -212,9 +319,21 @@ struct GlobalMem {
     const HuffSlow* slow_;
     uint32_t recs_addr;
     const uint32_t* words;
+    uint32_t lut_addr;
     static constexpr uint32_t kWordStep = 1;
-    static constexpr bool kSingleEntries = false;
     __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
+    __device__ __forceinline__ uint32_t single_of(uint32_t tbl) const { return tbl + (uint32_t)kLut1Size * 4u; }
+    // continuation field: 16-byte units from the start of the staged LUT pool (dynamic shared memory
+    // behind the window; stage_tables<true> re-bases the field for its compact layout)
+    __device__ __forceinline__ uint32_t cont_table(uint32_t e) const { return lut_addr + ((e >> 8) & 0x7fff0u); }
+    template <bool WRITE>
+    __device__ __forceinline__ uint32_t step(uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch,
+                                             uint32_t& tbl, const SlotRec& r, uint32_t& w0, uint32_t& w1,
+                                             uint32_t& w2, uint32_t& wn, uint32_t& peek, uint32_t end,
+                                             uint32_t end_fast, uint32_t q_limit) const
+    {
+        return generic_step<WRITE>(*this, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
+    }
     __device__ __forceinline__ uint32_t slot_handle(uint32_t c) const
     {
         return recs_addr + c * (uint32_t)sizeof(SlotRec);
@@ -261,7 +380,7 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
 
     uint32_t k = 0, i = 0, seg_bits = 0;
     bool head = false;
-    DevMem M{&st, b.slow, smem_addr(st.recs), 0};
+    DevMem M{&st, b.slow, smem_addr(st.recs), 0, smem_addr(s_dyn + kSyncWinWords / 4)};
     if (active) {
         k = find_segment(b.segs, g.num_segments, (uint32_t)sub);
         const SegDesc seg = b.segs[k];
@@ -370,7 +489,8 @@ __device__ __forceinline__ void verify_and_repair(const ScanGeom& g, const ScanB
             if (boundary_ok(entries[kRecWords * (size_t)(j - 1)], entries[kRecWords * (size_t)j])) continue;
             const SegDesc seg = b.segs[*(volatile uint32_t*)(b.seg_idx + j)];
             const GlobalMem M{&st, b.slow, smem_addr(st.recs),
-                              b.destuffed + (size_t)seg.sub_off * kSubWords};
+                              b.destuffed + (size_t)seg.sub_off * kSubWords,
+                              smem_addr(s_dyn + kSyncWinWords / 4)};
             rewritten += relink_from(M, seg, entries, j);
         }
         slow_total += rewritten;
@@ -574,7 +694,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
             has = qe > qs;
         }
     }
-    const uint32_t lut_vec = (g.lut_pool_words + 3) / 4;
+    const uint32_t lut_vec = (g.lut_compact_words + 3) / 4;
     uint8_t* warp_mem = reinterpret_cast<uint8_t*>(s_dyn + win_words / 4 + lut_vec) + (size_t)warp * kWarpSmem;
     const uint32_t list_addr = smem_addr(warp_mem) + (uint32_t)lane * (kListStride * 4u);
     uint32_t list_end = list_addr;
@@ -583,6 +703,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
         M.st = &st;
         M.slow_ = b.slow;
         M.recs_addr = smem_addr(st.recs);
+        M.lut_addr = smem_addr(s_dyn + win_words / 4);
         M.win_addr = smem_addr(s_dyn) + (uint32_t)((int)((long long)seg.sub_off - (long long)sub0) * kSubBytes);
         M.list_ptr = list_addr;
         M.slot0 = qs;
@@ -635,6 +756,7 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
 {
     if (g.num_subs == 0) return cudaSuccess;
     const size_t lut_bytes = (size_t)((g.lut_pool_words + 3) / 4) * 16;
+    const size_t lut_write_bytes = (size_t)((g.lut_compact_words + 3) / 4) * 16;
     static PerDeviceOnce configured;
     configured.run([] {
         const int max_smem = 226 * 1024; // 227 KiB per CTA minus the static part
@@ -650,7 +772,7 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     const size_t budget = 225 * 1024;
     int warps = kWriteThreads / 32;
     auto write_smem = [&](int w) {
-        return (size_t)(w * kSubsPerWarp * kSubWords + kWinMargin) * 4 + lut_bytes + (size_t)w * kWarpSmem;
+        return (size_t)(w * kSubsPerWarp * kSubWords + kWinMargin) * 4 + lut_write_bytes + (size_t)w * kWarpSmem;
     };
     while (warps > 1 && write_smem(warps) + 1024 > budget) --warps;
     const uint32_t subs_per_cta = (uint32_t)warps * (uint32_t)kSubsPerWarp;

@@ -18,6 +18,17 @@ namespace {
 const uint8_t kNat[64] = {JB2_NATURAL_ORDER};
 }
 
+struct SinglesOnly : HostMem { // slot records point at the singles halves; single_of() stays there
+    JB2_HD uint32_t single_of(uint32_t tbl) const { return tbl; }
+    template <bool WRITE>
+    JB2_HD uint32_t step(uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch, uint32_t& tbl,
+                         const SlotRec& r, uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
+                         uint32_t& peek, uint32_t end, uint32_t end_fast, uint32_t q_limit) const
+    {
+        return generic_step<WRITE>(*this, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
+    }
+};
+
 extern "C" {
 
 // Parse only: returns status; fills a few numbers for tests.
@@ -63,9 +74,10 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     HuffSlow slow[kMaxTables];
     for (int t = 0; t < g.num_tables; ++t) g.table_off[t] = build_lut(sp.tables[t], pool, slow[t]);
     g.lut_pool_words = (uint32_t)pool.size();
-    SlotRec recs[kMaxDuPerMcu];
+    SlotRec recs[kMaxDuPerMcu], recs_write[kMaxDuPerMcu];
     uint32_t tbls[kMaxDuPerMcu];
     make_slot_recs(g, recs, tbls);
+    make_slot_recs(g, recs_write, tbls, true); // the write pass decodes with the singles halves
 
     // destuff: the contract of destuff_kernel, tile by tile from the host tile directory
     const uint32_t N = g.num_subs;
@@ -109,7 +121,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
     const uint32_t* words = reinterpret_cast<const uint32_t*>(dst.data());
     long long_codes = 0;
     auto mem_of = [&](const SegDesc& seg) {
-        HostMem m{pool.data(), recs, tbls, slow, words + (size_t)seg.sub_off * kSubWords};
+        HostMem m{pool.data(), recs, tbls, slow, words + (size_t)seg.sub_off * kSubWords, g.table_off};
         m.long_codes_ = &long_codes;
         return m;
     };
@@ -272,6 +284,7 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
         uint32_t first_du, q_limit;
         if (!segment_extent(g, seg_idx[j], first_du, q_limit)) continue;
         HostMem m = mem_of(seg);
+        m.recs_ = recs_write;
         m.coef_ = zz.data() + (size_t)first_du * 64;
         m.dc_ = dc.data() + first_du;
         for (uint32_t h = 0; h < (uint32_t)kWriteParts; ++h) // the threads of a subsequence
@@ -304,20 +317,6 @@ int emul_decode_scan(const uint8_t* data, size_t size, int scan_idx, int16_t* co
 // also the speculative ones the fix-point feeds it.  Decodes every subsequence of scan 0 from the
 // cold state and from `tries` pseudo-random entry states with both and returns the number of
 // differing records (0 expected), or a negative parse error.
-struct SingleMem : HostMem { // every primary entry reduced to its first symbol
-    JB2_HD uint32_t lut(uint32_t tbl, uint32_t i) const
-    {
-        const uint32_t e = lut_[(uint32_t)(tbl + i)];
-        return e < kEntryMarkerLimit ? e : first_symbol(e);
-    }
-    JB2_HD uint32_t probe(uint32_t tbl, uint32_t peek) const { return lut(tbl, peek >> (32 - kLutBits)); }
-    JB2_HD uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t pp, uint32_t pn) const
-    {
-        slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
-        return funnel_left_wrap(w0, w1, pn);
-    }
-};
-
 int emul_pair_equivalence(const uint8_t* data, size_t size, int tries, long* pairs_possible)
 {
     static ImagePlan plan;
@@ -331,9 +330,10 @@ int emul_pair_equivalence(const uint8_t* data, size_t size, int tries, long* pai
     long pairs = 0;
     for (uint32_t e : pool) pairs += e >= kEntryMarkerLimit && entry_skip2(e) != 0;
     if (pairs_possible) *pairs_possible = pairs;
-    SlotRec recs[kMaxDuPerMcu];
+    SlotRec recs[kMaxDuPerMcu], recs_single[kMaxDuPerMcu];
     uint32_t tbls[kMaxDuPerMcu];
     make_slot_recs(g, recs, tbls);
+    make_slot_recs(g, recs_single, tbls, true);
     const uint32_t N = g.num_subs;
     std::vector<uint8_t> dst((size_t)N * kSubBytes + 64, 0);
     {
@@ -356,9 +356,10 @@ int emul_pair_equivalence(const uint8_t* data, size_t size, int tries, long* pai
     uint32_t rng = 12345u;
     for (int k = 0; k < g.num_segments; ++k) {
         const SegDesc& seg = sp.segs[k];
-        HostMem pm{pool.data(), recs, tbls, slow, words + (size_t)seg.sub_off * kSubWords};
-        SingleMem sm;
+        HostMem pm{pool.data(), recs, tbls, slow, words + (size_t)seg.sub_off * kSubWords, g.table_off};
+        SinglesOnly sm;
         static_cast<HostMem&>(sm) = pm;
+        sm.recs_ = recs_single;
         const uint32_t n = subs_in_segment(seg);
         for (uint32_t i = 0; i < n; ++i)
             for (int t = 0; t <= tries; ++t) {

@@ -16,14 +16,17 @@
 
 using namespace jb2;
 
-static long g_steps = 0;
+static long g_steps = 0, g_long = 0;
 struct SimMem {
     const uint32_t* lut_;
     const SlotRec* recs_;
     const uint32_t* tbls_;
     const HuffSlow* slow_;
     const uint32_t* words_;
+    const uint32_t* table_off_;
     static constexpr uint32_t kWordStep = 1;
+    uint32_t single_of(uint32_t tbl) const { return tbl + (uint32_t)kLut1Size; }
+    uint32_t cont_table(uint32_t e) const { return entry_cont_vec16(e) * 4u; }
     uint32_t lut(uint32_t tbl, uint32_t i) const
     {
         if (i < (uint32_t)kLut1Size) ++g_steps;
@@ -35,15 +38,21 @@ struct SimMem {
     const HuffSlow& slow(uint32_t s) const { return slow_[s]; }
     uint32_t word_handle(uint32_t i) const { return i; }
     uint32_t word(uint32_t h) const { return words_[h]; }
-    static constexpr bool kSingleEntries = false;
     uint32_t probe(uint32_t tbl, uint32_t peek) const { return lut(tbl, peek >> (32 - kLutBits)); }
     uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t pp, uint32_t pn) const
     {
         slide_window_generic(*this, w0, w1, w2, wn, pp, pn);
         return funnel_left_wrap(w0, w1, pn);
     }
+    template <bool WRITE>
+    uint32_t step(uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch, uint32_t& tbl, const SlotRec& r,
+                  uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn, uint32_t& peek, uint32_t end,
+                  uint32_t end_fast, uint32_t q_limit) const
+    {
+        return generic_step<WRITE>(*this, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
+    }
     void put(uint32_t, int) const {}
-    void note_long_code() const {}
+    void note_long_code() const { ++g_long; }
 };
 
 struct Scan {
@@ -75,7 +84,7 @@ struct Sim {
         if (it != memo.end()) return it->second;
         const SegDesc& seg = s.segs[s.seg_of[j]];
         SimMem M{s.pool.data(), s.recs, s.tbls, s.slow,
-                 reinterpret_cast<const uint32_t*>(s.dst.data()) + (size_t)seg.sub_off * kSubWords};
+                 reinterpret_cast<const uint32_t*>(s.dst.data()) + (size_t)seg.sub_off * kSubWords, s.g.table_off};
         const uint32_t i = j - seg.sub_off, seg_bits = seg.nbytes * 8u;
         const uint32_t start = i * (uint32_t)kSubBits;
         uint32_t p = start + (gs & 31u), c = (gs >> 5) & 15u, q = (gs >> 9) & 63u;
@@ -406,6 +415,7 @@ int main(int argc, char** argv)
         st.cost_max = std::max(st.cost_max, cost);
         ++st.pass_hist[std::min(passes, 39)];
     }
+    fprintf(stderr, "long codes per 1000 probes: %.2f\n", 1000.0 * g_long / std::max(1l, g_steps));
     printf("%-60s chunks %ld passes avg %.2f max %d | cost(steps) avg %.0f max %ld | decodes/sub %.2f relink %ld\n",
            argv[1], st.chunks, (double)st.passes_sum / st.chunks, st.passes_max, (double)st.cost_sum / st.chunks,
            st.cost_max, (double)st.decodes / N, st.relink);
