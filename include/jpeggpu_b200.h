@@ -77,7 +77,29 @@ struct jpeggpu_b200_scan_stats {
     int kernel_launches;       /* launches jpeggpu_decoder_decode issues for this scan */
     /* byte offsets inside d_tmp of the intermediate buffers (valid after decode + sync) */
     size_t off_control, off_destuffed, off_coefficients, off_sync_records, off_slot_prefix;
+    /* written by the destuff kernel: the segment directory (16 bytes per restart segment:
+     * first subsequence, destuffed bytes, two reserved words) and the totals of the scan
+     * (struct jpeggpu_b200_scan_info) */
+    size_t off_segments, off_scan_info;
 };
+
+/* What the device found in the entropy-coded data of a scan (the destuff kernel locates the end of
+ * the scan and the restart markers itself; reference: the host walk src/reader.cpp:443-489 and
+ * src/decode_destuff.cu:212-344).  Lives at off_scan_info of the scratch buffer after a decode. */
+struct jpeggpu_b200_scan_info {
+    unsigned num_subsequences; /* N */
+    unsigned num_segments;     /* restart segments found */
+    unsigned scan_end;         /* offset, from the first entropy-coded byte, of the byte that ended the scan */
+    unsigned status;           /* JPEGGPU_B200_SCAN_* */
+};
+/* Copies the scan info of scan `scan` of the last decode out of d_tmp (a device-to-host copy on
+ * `stream` followed by a synchronisation of that stream: a diagnostic call, not part of the
+ * stream-ordered protocol). */
+enum jpeggpu_status jpeggpu_b200_read_scan_info(
+    jpeggpu_decoder_t decoder, int scan, const void* d_tmp, cudaStream_t stream,
+    struct jpeggpu_b200_scan_info* info);
+#define JPEGGPU_B200_SCAN_UNTERMINATED 1u /* the data ran out before a terminating marker (no EOI) */
+#define JPEGGPU_B200_SCAN_OVERFLOW 2u     /* more restart segments than the frame allows: damaged */
 
 /* Statistics of scan `scan` of the last parsed image; *num_scans (optional) gets the count. */
 enum jpeggpu_status jpeggpu_b200_get_scan_stats(
@@ -86,16 +108,25 @@ enum jpeggpu_status jpeggpu_b200_get_scan_stats(
 /* Bytes jpeggpu_decoder_transfer copies host-to-device for the last parsed image. */
 enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, size_t* bytes);
 
-/* Deferred entropy walk (on by default).  For a file that is one interleaved scan of all frame
- * components without DRI and that ends with EOI, jpeggpu_decoder_parse_header stops at the scan
- * header (its cost no longer grows with the file), jpeggpu_decoder_get_buffer_size answers from
- * upper bounds (<= 0.1 % above the exact plan), and jpeggpu_decoder_transfer enqueues the upload of
- * the scan bytes first and walks them on the host while the DMA is in flight.  Statuses the walk
- * can produce are then returned by transfer instead of parse_header.  The reference walks inside
- * parse_header (src/reader.cpp:443-489); `on` = 0 restores that order.
- * Scans of at least 1 MiB are walked by the calling thread plus up to three helper threads owned
- * by the decoder (started on first use, asleep otherwise; they read the file only while
- * jpeggpu_decoder_transfer runs); `on` = 2 keeps the deferred walk on the calling thread alone. */
+/* Who walks the entropy-coded bytes (to find the end of the scan and the restart markers).
+ *   3 (default)  the device.  For a file whose first scan holds all frame components and at least
+ *                64 KiB follow its header, jpeggpu_decoder_parse_header stops at the scan header
+ *                (its cost no longer grows with the file), jpeggpu_decoder_get_buffer_size answers
+ *                from upper bounds (the scan is planned as if it filled the rest of the file),
+ *                jpeggpu_decoder_transfer uploads everything behind the scan header, and the
+ *                destuff kernel finds the end of the scan and the restart segments with a
+ *                single-pass look-back.  What only the walk can detect - no terminating marker,
+ *                stray markers - is then NOT reported by parse_header; it is recorded in struct
+ *                jpeggpu_b200_scan_info (the decode stays memory safe and decodes what is there).
+ *                Smaller files, and files with several scans, are walked by parse_header.
+ *   0            the host, inside jpeggpu_decoder_parse_header, like the reference
+ *                (src/reader.cpp:443-489): every status of the reference at parse time.
+ *   1            the host, inside jpeggpu_decoder_transfer behind the upload of the bytes (files
+ *                that are one scan without DRI and end with EOI; others as 0); statuses of the
+ *                walk are returned by transfer.  Scans of at least 1 MiB are walked by the calling
+ *                thread plus up to three helper threads owned by the decoder (started on first
+ *                use, asleep otherwise; they read the file only while transfer runs).
+ *   2            as 1, on the calling thread alone. */
 enum jpeggpu_status jpeggpu_b200_set_deferred_walk(jpeggpu_decoder_t decoder, int on);
 
 /* Per-kernel device times. With profiling on, jpeggpu_decoder_decode records a CUDA event on the

@@ -33,7 +33,7 @@ API_SYMBOLS = [
     "jpeggpu_b200_get_scan_stats", "jpeggpu_b200_get_transfer_size",
     "jpeggpu_b200_set_profiling", "jpeggpu_b200_get_kernel_times", "jpeggpu_b200_kernel_name",
     "jpeggpu_b200_decode_batch", "jpeggpu_b200_parse_batch", "jpeggpu_b200_set_deferred_walk",
-    "jpeggpu_b200_decode_rgbi", "jpeggpu_b200_convert_rgbi",
+    "jpeggpu_b200_decode_rgbi", "jpeggpu_b200_convert_rgbi", "jpeggpu_b200_read_scan_info",
 ]
 
 MAX_KERNELS = 16
@@ -59,7 +59,14 @@ class ScanStats(C.Structure):
                 ("subsequence_bytes", C.c_int), ("kernel_launches", C.c_int),
                 ("off_control", C.c_size_t), ("off_destuffed", C.c_size_t),
                 ("off_coefficients", C.c_size_t), ("off_sync_records", C.c_size_t),
-                ("off_slot_prefix", C.c_size_t)]
+                ("off_slot_prefix", C.c_size_t), ("off_segments", C.c_size_t),
+                ("off_scan_info", C.c_size_t)]
+
+
+class ScanInfo(C.Structure):
+    """struct jpeggpu_b200_scan_info (include/jpeggpu_b200.h)"""
+    _fields_ = [("num_subsequences", C.c_uint), ("num_segments", C.c_uint), ("scan_end", C.c_uint),
+                ("status", C.c_uint)]
 
 
 class BatchItem(C.Structure):
@@ -118,6 +125,7 @@ def load_library(path=None):
     L.jpeggpu_b200_get_transfer_size.argtypes = [dec, C.POINTER(C.c_size_t)]
     L.jpeggpu_b200_set_profiling.argtypes = [dec, C.c_int]
     L.jpeggpu_b200_set_deferred_walk.argtypes = [dec, C.c_int]
+    L.jpeggpu_b200_read_scan_info.argtypes = [dec, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(ScanInfo)]
     L.jpeggpu_b200_get_kernel_times.argtypes = [dec, C.POINTER(C.c_float * MAX_KERNELS),
                                                 C.POINTER(C.c_int * MAX_KERNELS)]
     L.jpeggpu_b200_kernel_name.restype = C.c_char_p
@@ -220,8 +228,16 @@ class Decoder:
                "jpeggpu_b200_get_transfer_size")
         return n.value
 
+    def read_scan_info(self, d_tmp, scan=0, stream=0):
+        """What the device found in the entropy-coded data of the last decode (synchronises)."""
+        si = ScanInfo()
+        _check(self.lib.jpeggpu_b200_read_scan_info(self.handle, scan, d_tmp, stream, C.byref(si)),
+               "jpeggpu_b200_read_scan_info")
+        return si
+
     def set_deferred_walk(self, on):
-        """Deferred entropy walk (include/jpeggpu_b200.h); on by default."""
+        """Who walks the entropy-coded bytes: 0 host at parse time, 1/2 host inside transfer,
+        3 the device (default); include/jpeggpu_b200.h."""
         _check(self.lib.jpeggpu_b200_set_deferred_walk(self.handle, int(on)), "jpeggpu_b200_set_deferred_walk")
 
     def set_profiling(self, on):

@@ -47,7 +47,7 @@ constexpr int kSubWords = kSubBytes / 4;
 constexpr int kOverlapSubs = JB2_OVERLAP_SUBS;
 constexpr int kChunkSubs = 32 - kOverlapSubs; // subsequences whose records one sync warp owns
 
-// Destuff tiling (the host walk emits one TileDesc per tile, kernels_destuff.cu consumes them).
+// Destuff tiling.
 constexpr int kDestuffThreads = 256;
 constexpr int kDestuffBytesPerThread = 16;
 constexpr int kDestuffTile = kDestuffThreads * kDestuffBytesPerThread; // stuffed bytes per CTA
@@ -162,7 +162,18 @@ struct Mids {
 constexpr uint16_t kStateHead = 0x8000u;
 constexpr uint16_t kStateMask = 0x7fffu;
 
-struct TileDesc {         // one per kDestuffTile stuffed bytes, built by the host walk
+// Totals of a scan, written by the destuff tile that holds the end of the scan and read by every
+// later kernel: the host plans grids and buffers from upper bounds and need not know them.
+struct ScanInfo {
+    uint32_t num_subs;     // N
+    uint32_t num_segments; // restart segments (the last one closed by the end of the scan)
+    uint32_t scan_end;     // stuffed offset of the byte that ended the scan (marker code or end of data)
+    uint32_t status;       // kScan* flags
+};
+constexpr uint32_t kScanUnterminated = 1u; // the data ran out before a terminating marker
+constexpr uint32_t kScanOverflow = 2u;     // more segments / subsequences than planned (damaged stream)
+
+struct TileDesc {         // one per kDestuffTile stuffed bytes, built by the host walk (tests only)
     uint32_t kept_before; // destuffed data bytes of the scan before the tile's first byte
     uint32_t segs_before; // restart markers completed before the tile's first byte
 };
@@ -182,6 +193,9 @@ struct ScanGeom { // by-value kernel parameter describing one scan
     int num_segments;
     uint32_t num_subs;    // N
     uint32_t scan_bytes;  // stuffed bytes Sb
+    uint32_t scan_avail;  // bytes handed to the device from the start of the scan: Sb + the two
+                          // bytes of the marker that ends it (host walk), or everything up to
+                          // the end of the file (device walk)
     int num_tables;
     // per DU slot of the MCU
     uint8_t slot_dc[kMaxDuPerMcu]; // table slot of the DC table

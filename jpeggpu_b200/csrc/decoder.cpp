@@ -7,9 +7,7 @@
 //  * no memset (kernels clear what they need) and 7 launches per scan instead of ~40 stream
 //    operations;
 //  * cumulative scratch-size check (reference quirk Q7).
-#include "huff_lut.hpp"
-#include "kernels.hpp"
-#include "parser.hpp"
+#include "plan.hpp"
 
 #include <jpeggpu/jpeggpu.h>
 #include <jpeggpu_b200.h>
@@ -22,26 +20,6 @@
 #include <vector>
 
 using namespace jb2;
-
-namespace {
-
-size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
-
-struct ScanLayout {
-    // upload block (offsets inside the staging block == inside d_tmp)
-    size_t off_lut = 0, off_slow = 0, off_segs = 0, off_tiles = 0;
-    // uploaded entropy-coded bytes
-    size_t off_bytes = 0;
-    // work area (shared by all scans of the image; scans run back to back on one stream)
-    size_t off_ctrl = 0, off_destuffed = 0, off_coef = 0, off_dc = 0;
-    size_t off_entries = 0, off_qpos = 0, off_seg_idx = 0;
-    size_t coef_bytes = 0, dc_bytes = 0;
-    uint32_t num_chunks = 0, dc_tiles = 0, flag_words = 0, write_ctas = 0;
-    uint32_t destuffed_bytes = 0;
-    uint32_t num_dus = 0;
-};
-
-} // namespace
 
 struct jpeggpu_decoder {
     Logger log;
@@ -67,13 +45,7 @@ struct jpeggpu_decoder {
     } slots[kStagingSlots];
     int cur_slot = 0;
     uint8_t* staging = nullptr; // == slots[cur_slot].ptr
-    struct LutCache {
-        std::vector<uint8_t> key;
-        std::vector<uint32_t> pool;
-        HuffSlow slow[kMaxTables];
-        uint32_t table_off[kMaxTables];
-        uint32_t compact_words = 0;
-    } lut_cache[kMaxScans];
+    LutSet lut_cache[kMaxScans];
     std::vector<uint8_t> lut_key;
     StageTimer timer;
     WalkPool* walk_pool = nullptr; // helper threads of the deferred walk (large scans only)
@@ -171,11 +143,10 @@ struct jpeggpu_decoder {
     // file and plans from upper bounds; transfer enqueues the upload of the scan bytes FIRST and
     // walks them on the host while the DMA runs, then uploads the directories.  Anything that
     // needs exact counts earlier (scan statistics) just runs the walk on the spot.
-    bool defer_walk = true;
+    int walk_mode = kWalkDevice; // WalkMode (parser.hpp)
     jpeggpu_status plan_scratch();
-    void derive_counts(int s);
+    void set_destuffed_bytes(int s);
     jpeggpu_status finish_walk();
-    void fill_directories(int s);
     ScanBufs bufs(int s, void* d_tmp) const;
     jpeggpu_status rgbi_layout(int* cy, int* cb, int* cr) const;
     jpeggpu_status run(jpeggpu_img* img, int16_t* const* coef_planes, uint8_t* rgb, int rgb_pitch,
@@ -192,29 +163,10 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
     // scan slot is cached and keyed by the raw table specifications.
     for (int s = 0; s < plan.num_scans; ++s) {
         ScanPlan& sp = plan.scans[s];
-        LutCache& lc = lut_cache[s];
-        lut_key.clear();
-        for (int t = 0; t < sp.geom.num_tables; ++t) {
-            const HuffSpec& h = sp.tables[t];
-            lut_key.push_back(h.is_dc ? 1 : 0);
-            lut_key.insert(lut_key.end(), h.counts, h.counts + 16);
-            lut_key.insert(lut_key.end(), h.vals, h.vals + 256);
-        }
-        if (lc.key != lut_key) {
-            lc.pool.clear();
-            for (int t = 0; t < sp.geom.num_tables; ++t)
-                lc.table_off[t] = build_lut(sp.tables[t], lc.pool, lc.slow[t]);
-            while (lc.pool.size() & 3) lc.pool.push_back(0); // staged with 16-byte loads
-            lc.compact_words = 0; // what huff_write stages: header + one primary LUT + secondary
-            for (int t = 0; t < sp.geom.num_tables; ++t)
-                lc.compact_words += (uint32_t)(kLutHeader + kLut1Size) +
-                                    ((lc.pool[lc.table_off[t] - kLutHeader + 1] + 3u) & ~3u);
-            lc.key = lut_key;
-        }
-        for (int t = 0; t < sp.geom.num_tables; ++t) sp.geom.table_off[t] = lc.table_off[t];
-        sp.geom.lut_pool_words = (uint32_t)lc.pool.size();
-        sp.geom.lut_compact_words = lc.compact_words;
-        if (sp.geom.lut_pool_words > 40 * 1024) return JPEGGPU_NOT_SUPPORTED; // > 160 KiB of LUTs
+        LutSet& lc = lut_cache[s];
+        lut_key_of(sp, lut_key);
+        if (lc.key != lut_key) build_lut_set(sp, lut_key, lc);
+        if (!apply_lut_set(lc, sp.geom)) return JPEGGPU_NOT_SUPPORTED; // > 160 KiB of LUTs
     }
     for (int s = 0; s < plan.num_scans; ++s) {
         ScanLayout& L = layout[s];
@@ -223,44 +175,23 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
         off += align256((size_t)g.lut_pool_words * 4);
         L.off_slow = off;
         off += align256(sizeof(HuffSlow) * kMaxTables);
-        L.off_segs = off;
-        off += align256(sizeof(SegDesc) * (size_t)g.num_segments);
-        L.off_tiles = off;
-        off += align256(sizeof(TileDesc) * (((size_t)g.scan_bytes + kDestuffTile - 1) / kDestuffTile));
+        L.off_desc = off;
+        L.desc_words = destuff_desc_words(g);
+        off += align256((size_t)L.desc_words * 4);
     }
     upload_bytes = off;
     transfer_bytes = upload_bytes;
     for (int s = 0; s < plan.num_scans; ++s) {
         layout[s].off_bytes = off;
-        off += align256((size_t)plan.scans[s].geom.scan_bytes + 16);
-        transfer_bytes += plan.scans[s].geom.scan_bytes;
+        off += align256((size_t)plan.scans[s].geom.scan_avail + 16);
+        transfer_bytes += plan.scans[s].geom.scan_avail;
     }
     // work area: sized for the largest scan
     const size_t work_begin = off;
     size_t work_end = off;
     for (int s = 0; s < plan.num_scans; ++s) {
-        ScanLayout& L = layout[s];
-        const ScanGeom& g = plan.scans[s].geom;
-        const ScanPlan& sp = plan.scans[s];
-        size_t o = work_begin;
-        (void)sp;
-        derive_counts(s); // from bounds when the walk is deferred: the offsets below only grow
-        L.off_ctrl = o; // control block, sync mailboxes and DC flags are cleared as one range
-        o += align256(sizeof(Control) + ((size_t)L.flag_words + 4u * L.dc_tiles + 2u * L.write_ctas) * 4);
-        L.off_destuffed = o;
-        o += align256((size_t)g.num_subs * kSubBytes + 64);
-        L.off_coef = o;
-        L.coef_bytes = (size_t)L.num_dus * 128;
-        o += align256(L.coef_bytes);
-        L.off_dc = o;
-        L.dc_bytes = ((size_t)L.num_dus * 2 + 15) & ~(size_t)15;
-        o += align256(L.dc_bytes);
-        L.off_entries = o;
-        o += align256((size_t)g.num_subs * sizeof(SubEntry));
-        L.off_qpos = o;
-        o += align256(((size_t)g.num_subs + 1) * 4);
-        L.off_seg_idx = o;
-        o += align256((size_t)g.num_subs * 4);
+        const size_t o = plan_work_area(plan.scans[s].geom, work_begin, layout[s]);
+        set_destuffed_bytes(s);
         if (o > work_end) work_end = o;
     }
     total_bytes = work_end;
@@ -270,36 +201,18 @@ jpeggpu_status jpeggpu_decoder::plan_scratch()
     for (int s = 0; s < plan.num_scans; ++s) {
         const ScanLayout& L = layout[s];
         const ScanPlan& sp = plan.scans[s];
-        const LutCache& lc = lut_cache[s];
+        const LutSet& lc = lut_cache[s];
         memcpy(staging + L.off_lut, lc.pool.data(), (size_t)sp.geom.lut_pool_words * 4);
         memcpy(staging + L.off_slow, lc.slow, sizeof(HuffSlow) * (size_t)sp.geom.num_tables);
-        if (!plan.walk_pending) fill_directories(s);
+        memset(staging + L.off_desc, 0, (size_t)L.desc_words * 4);
     }
     return JPEGGPU_SUCCESS;
 }
 
-// Counts that follow from the number of subsequences / MCUs of scan s (no offsets).
-void jpeggpu_decoder::derive_counts(int s)
+void jpeggpu_decoder::set_destuffed_bytes(int s)
 {
-    ScanLayout& L = layout[s];
     const ScanPlan& sp = plan.scans[s];
-    const ScanGeom& g = sp.geom;
-    L.num_dus = (uint32_t)g.total_mcus * (uint32_t)g.dus_per_mcu;
-    L.destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
-    L.num_chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
-    L.dc_tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
-    L.flag_words = (L.num_chunks + 1u) & ~1u; // keeps the 64-bit words behind it aligned
-    L.write_ctas = g.num_subs / (32u / kWriteParts) + 1u; // huff_write runs >= one warp of subsequences per CTA
-}
-
-void jpeggpu_decoder::fill_directories(int s)
-{
-    const ScanLayout& L = layout[s];
-    const ScanPlan& sp = plan.scans[s];
-    if (!sp.segs.empty())
-        memcpy(staging + L.off_segs, sp.segs.data(), sizeof(SegDesc) * sp.segs.size());
-    if (!sp.tiles.empty())
-        memcpy(staging + L.off_tiles, sp.tiles.data(), sizeof(TileDesc) * sp.tiles.size());
+    layout[s].destuffed_bytes = sp.segs.empty() ? 0 : sp.segs.back().kept_before + sp.segs.back().nbytes;
 }
 
 // Runs the deferred walk (if one is pending): exact geometry into scans[0], counts re-derived
@@ -307,44 +220,19 @@ void jpeggpu_decoder::fill_directories(int s)
 jpeggpu_status jpeggpu_decoder::finish_walk()
 {
     if (!plan.walk_pending) return JPEGGPU_SUCCESS;
-    const uint32_t planned_bytes = plan.scans[0].geom.scan_bytes;
+    const uint32_t planned_bytes = plan.scans[0].geom.scan_avail;
     const jpeggpu_status st = finish_deferred_walk(plan, log, walk_threads ? walk_pool : nullptr);
     if (st != JPEGGPU_SUCCESS) {
         parsed = false;
         return st;
     }
-    transfer_bytes -= planned_bytes - plan.scans[0].geom.scan_bytes;
-    derive_counts(0);
-    fill_directories(0);
+    transfer_bytes -= planned_bytes - plan.scans[0].geom.scan_avail;
+    derive_counts(plan.scans[0].geom, layout[0]);
+    set_destuffed_bytes(0);
     return JPEGGPU_SUCCESS;
 }
 
-ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const
-{
-    uint8_t* base = static_cast<uint8_t*>(d_tmp);
-    const ScanLayout& L = layout[s];
-    ScanBufs b;
-    b.scan_bytes = base + L.off_bytes;
-    b.segs = reinterpret_cast<const SegDesc*>(base + L.off_segs);
-    b.lut_pool = reinterpret_cast<const uint32_t*>(base + L.off_lut);
-    b.slow = reinterpret_cast<const HuffSlow*>(base + L.off_slow);
-    b.tiles = reinterpret_cast<const TileDesc*>(base + L.off_tiles);
-    b.ctrl = reinterpret_cast<Control*>(base + L.off_ctrl);
-    b.chunk_state = reinterpret_cast<uint32_t*>(base + L.off_ctrl + sizeof(Control));
-    b.num_chunks = L.num_chunks;
-    b.dc_agg = reinterpret_cast<unsigned long long*>(b.chunk_state + L.flag_words);
-    b.write_agg = b.dc_agg + 2u * (size_t)L.dc_tiles;
-    b.clear_words = (uint32_t)(sizeof(Control) / 4) + L.flag_words + 4u * L.dc_tiles + 2u * L.write_ctas;
-    b.destuffed = reinterpret_cast<uint32_t*>(base + L.off_destuffed);
-    b.coef = reinterpret_cast<int16_t*>(base + L.off_coef);
-    b.coef_bytes = L.coef_bytes;
-    b.dc = reinterpret_cast<int16_t*>(base + L.off_dc);
-    b.dc_bytes = L.dc_bytes;
-    b.entries = reinterpret_cast<SubEntry*>(base + L.off_entries);
-    b.qpos = reinterpret_cast<uint32_t*>(base + L.off_qpos);
-    b.seg_idx = reinterpret_cast<uint32_t*>(base + L.off_seg_idx);
-    return b;
-}
+ScanBufs jpeggpu_decoder::bufs(int s, void* d_tmp) const { return make_bufs(layout[s], d_tmp); }
 
 #define JB2_CUDA(call)                                                                   \
     do {                                                                                 \
@@ -383,7 +271,7 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
                                     int rgb_pitch, void* d_tmp, size_t tmp_size, cudaStream_t stream)
 {
     if (!parsed) return JPEGGPU_INVALID_ARGUMENT;
-    if (plan.walk_pending) return JPEGGPU_INVALID_ARGUMENT; // decode without transfer
+    if (plan.walk_pending && !plan.device_walk) return JPEGGPU_INVALID_ARGUMENT; // decode without transfer
     if (!d_tmp || tmp_size < total_bytes) return JPEGGPU_INTERNAL_ERROR; // src/util.hpp:66-68
     if ((reinterpret_cast<uintptr_t>(d_tmp) & 255u) != 0) return JPEGGPU_INVALID_ARGUMENT;
     timer.n = 0;
@@ -395,7 +283,7 @@ jpeggpu_status jpeggpu_decoder::run(jpeggpu_img* img, int16_t* const* coef_plane
             JB2_CUDA(cudaMemsetAsync(b.coef, 0, b.coef_bytes, stream));
             JB2_CUDA(cudaMemsetAsync(b.dc, 0, b.dc_bytes, stream));
         }
-        if (g.scan_bytes == 0) // destuff (which clears the control range) will not run either
+        if (g.scan_avail == 0) // destuff (which clears the control range) will not run either
             JB2_CUDA(cudaMemsetAsync(b.ctrl, 0, (size_t)b.clear_words * 4, stream));
         JB2_CUDA(launch_destuff(g, b, stream, &timer));
         JB2_CUDA(launch_huffman(g, b, stream, &timer));
@@ -489,7 +377,7 @@ enum jpeggpu_status jpeggpu_decoder_parse_header(
 #ifdef JB2_PARSE_TIMING
     const auto t0 = std::chrono::steady_clock::now();
 #endif
-    jpeggpu_status st = parse_jpeg(data, size, decoder->plan, decoder->log, decoder->defer_walk);
+    jpeggpu_status st = parse_jpeg(data, size, decoder->plan, decoder->log, decoder->walk_mode);
     if (st != JPEGGPU_SUCCESS) return st;
 #ifdef JB2_PARSE_TIMING
     const auto t1 = std::chrono::steady_clock::now();
@@ -536,7 +424,7 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
     if (!d_tmp || tmp_size < decoder->total_bytes) return JPEGGPU_INTERNAL_ERROR;
     const Logger& log = decoder->log;
     uint8_t* base = static_cast<uint8_t*>(d_tmp);
-    if (decoder->plan.walk_pending) {
+    if (decoder->plan.walk_pending && !decoder->plan.device_walk) {
         // the big copy goes first; the host walks the same bytes while the DMA engine reads them
         const ScanPlan& sp = decoder->plan.scans[0];
         if (decoder->walk_threads && decoder->plan.file_size - sp.begin >= kWalkParallelMin) {
@@ -545,7 +433,7 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
             walk_pool_kick(decoder->walk_pool, decoder->plan);
         }
         if (cudaMemcpyAsync(base + decoder->layout[0].off_bytes, decoder->plan.file + sp.begin,
-                            sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream) != cudaSuccess) {
+                            sp.geom.scan_avail, cudaMemcpyHostToDevice, stream) != cudaSuccess) {
             (void)cudaGetLastError();
             walk_pool_cancel(decoder->walk_pool); // no helper may read the caller's buffer after we return
             decoder->parsed = false;
@@ -563,9 +451,9 @@ enum jpeggpu_status jpeggpu_decoder_transfer(
     if (decoder->mark_staging_in_flight(stream) != JPEGGPU_SUCCESS) return JPEGGPU_INTERNAL_ERROR;
     for (int s = 0; s < decoder->plan.num_scans; ++s) {
         const ScanPlan& sp = decoder->plan.scans[s];
-        if (sp.geom.scan_bytes == 0) continue;
+        if (sp.geom.scan_avail == 0) continue;
         JB2_CUDA(cudaMemcpyAsync(base + decoder->layout[s].off_bytes, decoder->plan.file + sp.begin,
-                                 sp.geom.scan_bytes, cudaMemcpyHostToDevice, stream));
+                                 sp.geom.scan_avail, cudaMemcpyHostToDevice, stream));
     }
     return JPEGGPU_SUCCESS;
 }
@@ -712,6 +600,24 @@ enum jpeggpu_status jpeggpu_b200_get_scan_stats(
     stats->off_coefficients = L.off_coef;
     stats->off_sync_records = L.off_entries;
     stats->off_slot_prefix = L.off_qpos;
+    stats->off_segments = L.off_segs;
+    stats->off_scan_info = L.off_info;
+    return JPEGGPU_SUCCESS;
+}
+
+enum jpeggpu_status jpeggpu_b200_read_scan_info(
+    jpeggpu_decoder_t decoder, int scan, const void* d_tmp, cudaStream_t stream,
+    struct jpeggpu_b200_scan_info* info)
+{
+    if (!decoder || !decoder->parsed || !d_tmp || !info) return JPEGGPU_INVALID_ARGUMENT;
+    if (scan < 0 || scan >= decoder->plan.num_scans) return JPEGGPU_INVALID_ARGUMENT;
+    static_assert(sizeof(ScanInfo) == sizeof(jpeggpu_b200_scan_info), "same four words");
+    const uint8_t* src = static_cast<const uint8_t*>(d_tmp) + decoder->layout[scan].off_info;
+    if (cudaMemcpyAsync(info, src, sizeof(*info), cudaMemcpyDeviceToHost, stream) != cudaSuccess ||
+        cudaStreamSynchronize(stream) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return JPEGGPU_INTERNAL_ERROR;
+    }
     return JPEGGPU_SUCCESS;
 }
 
@@ -729,7 +635,8 @@ enum jpeggpu_status jpeggpu_b200_get_transfer_size(jpeggpu_decoder_t decoder, si
 enum jpeggpu_status jpeggpu_b200_set_deferred_walk(jpeggpu_decoder_t decoder, int on)
 {
     if (!decoder) return JPEGGPU_INVALID_ARGUMENT;
-    decoder->defer_walk = on != 0;
+    if (on < 0 || on > 3) return JPEGGPU_INVALID_ARGUMENT;
+    decoder->walk_mode = on == 0 ? kWalkEager : on == 3 ? kWalkDevice : kWalkDeferred;
     decoder->walk_threads = on != 2;
     return JPEGGPU_SUCCESS;
 }

@@ -18,9 +18,14 @@ constexpr int kDcTile = 256;  // MCUs per CTA in the DC scan
 
 // Device pointers of one scan (all inside the caller's scratch buffer).
 struct ScanBufs {
-    const uint8_t* scan_bytes; // stuffed entropy-coded bytes (uploaded)
-    const SegDesc* segs;       // uploaded
-    const TileDesc* tiles;     // uploaded: one per kDestuffTile stuffed bytes
+    const uint8_t* scan_bytes; // stuffed entropy-coded bytes (uploaded); 16-byte aligned
+    uint32_t scan_lead;        // bytes at scan_bytes that precede the scan (batched upload of whole
+                               // files: the scan starts wherever it starts; 0 .. 15)
+    SegDesc* segs;             // segment directory, written by destuff
+    ScanInfo* info;            // totals of the scan, written by destuff
+    unsigned long long* destuff_desc; // look-back descriptors of destuff (2 words per tile) followed
+    uint32_t* destuff_ticket;         // by its ticket: zero when destuff starts (uploaded zeros, then
+    uint32_t destuff_words;           // re-zeroed by huff_sync); destuff_words 32-bit words in all
     const uint32_t* lut_pool;  // uploaded
     const HuffSlow* slow;      // uploaded
     Control* ctrl;             // zeroed by destuff

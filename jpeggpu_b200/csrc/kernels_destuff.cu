@@ -1,32 +1,47 @@
-// kernels_destuff.cu — byte unstuffing + restart-segment placement (reference stage a1,
-// src/decode_destuff.cu:37-148 + the three CUB scans at :220-316).
+// kernels_destuff.cu — byte unstuffing + restart-segment indexing, entirely on the device
+// (reference stage a1, src/decode_destuff.cu:37-148 + the three CUB scans at :220-316, AND the
+// host walk that feeds it, src/reader.cpp:443-489).
 //
-// One launch, 16-byte vector loads, no per-byte int arrays: each CTA takes one 4 KiB tile of
-// stuffed bytes.  The tile's prefix (data bytes and restart markers before it) comes from the
-// host walk that already visits every 0xff to find the end of the scan (parser.cpp walk_scan,
-// the reference's src/reader.cpp:443-489), so tiles are independent: classify, block scan,
-// compaction through shared memory, coalesced stores.  The kernel also clears the control block
-// and the sync mailboxes of the Huffman stage and writes the zero padding behind every segment.
+// One launch, one pass, 16-byte vector loads.  Each CTA takes a 4 KiB tile of stuffed bytes:
+// classify (data / stuffed 0xff00 / RSTn / fill / end of scan), block scan, compaction through
+// shared memory, coalesced stores.  What a tile needs to know about the bytes BEFORE it - how
+// many subsequences the closed restart segments occupy, how many bytes the open segment already
+// holds, how many segments were closed, whether the scan has ended - is a prefix over per-tile
+// aggregates {closings, bytes before the first closing, subsequences of the segments closed inside,
+// bytes after the last closing, ended}.  The combine is associative (not commutative), so the
+// prefix is a single-pass decoupled look-back: a tile publishes its aggregate, reads its
+// predecessors back to the nearest published inclusive prefix, publishes its own.  Tiles are
+// numbered by an atomic ticket, so a tile only ever waits for tiles that are already running.
+// The kernel also writes the segment directory (one SegDesc per restart segment), the zero padding
+// behind every segment, and - from the tile that holds the end of the scan - the totals every
+// later kernel reads (ScanInfo: subsequences, segments): the host never looks at the entropy-coded
+// bytes.  It also clears the control block and the sync mailboxes of the Huffman stage.
 // Output is the destuffed scan stored as big-endian 32-bit words (byte d lands at d ^ 3) so the
 // Huffman kernels read MSB-first words directly; segment k starts at segs[k].sub_off*kSubBytes.
-// Algorithmic bytes: Sb read + Sd written.
+// Algorithmic bytes: Sb read + Sd written + 16 B per tile of look-back traffic.
 #include "kernels.hpp"
 
 namespace jb2 {
 namespace {
 
+constexpr uint32_t kMaxClose = kDestuffTile / 2 + 1; // closings (RSTn / end of scan) in one tile
+
 struct Chunk {
     uint32_t keep; // bit i: byte i is a data byte
     uint32_t rst;  // bit i: byte i is the second byte of an RSTn marker
+    uint32_t term; // index of the first byte that ends the scan (16: none)
     uint8_t val[kDestuffBytesPerThread]; // emitted value of byte i (0xff for a stuffed 0x00)
 };
 
-// The per-byte rule of src/decode_destuff.cu:37-44 and :64-71.
+// The per-byte rule of src/decode_destuff.cu:37-44 and :64-71, plus what the reference's host
+// walk decides (src/reader.cpp:450-487): 0xff followed by anything but 0x00, RSTn or another
+// 0xff (fill) ends the scan.
 __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n,
                                          uint32_t base, Chunk& ck)
 {
     ck.keep = 0;
     ck.rst = 0;
+    ck.term = 16;
     if (base >= n) return;
     uint32_t w[4];
     if (base + 16 <= n) {
@@ -39,6 +54,7 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
     }
     uint32_t prev = base ? src[base - 1] : 0u;
     const uint32_t count = min(16u, n - base);
+    uint32_t term = 16;
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
         const uint32_t b = (w[i >> 2] >> (8 * (i & 3))) & 0xffu;
@@ -46,11 +62,14 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
         const bool after_ff = prev == 0xffu;
         const bool keep = in && (after_ff ? b == 0u : b != 0xffu);
         const bool rst = in && after_ff && b >= 0xd0u && b <= 0xd7u;
+        const bool end = in && after_ff && b != 0u && b != 0xffu && !rst;
         ck.keep |= (uint32_t)keep << i;
         ck.rst |= (uint32_t)rst << i;
+        term = (end && term == 16u) ? (uint32_t)i : term;
         ck.val[i] = after_ff ? 0xffu : (uint8_t)b;
         prev = b;
     }
+    ck.term = term;
 }
 
 // Inclusive block scan of a packed (kept | rst << 16) count; returns the exclusive value.
@@ -77,30 +96,221 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* w
     return before + inc - v;
 }
 
-__global__ void __launch_bounds__(kDestuffThreads)
-destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __restrict__ tiles,
-               const SegDesc* __restrict__ segs, int num_segments, uint8_t* __restrict__ dst,
-               uint32_t* __restrict__ clear, uint32_t clear_words)
+// ---- the prefix element and its combine ----------------------------------------------------
+struct Elem {
+    uint32_t nclose; // segment closings (RSTn markers, the end of the scan)
+    uint32_t head;   // data bytes before the first closing (all of them if there is none)
+    uint32_t inner;  // subsequences of the segments that begin AND end inside
+    uint32_t tail;   // data bytes after the last closing (0 if there is none)
+    uint32_t ended;  // the scan has ended
+};
+
+__device__ __forceinline__ uint32_t subs_of(uint32_t bytes)
+{
+    return (bytes + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes;
+}
+
+// L covers the bytes before R.  Nothing follows the end of the scan.
+__device__ __forceinline__ Elem combine(const Elem& L, const Elem& R)
+{
+    if (L.ended) return L;
+    Elem o;
+    o.ended = R.ended;
+    if (R.nclose == 0) {
+        o.nclose = L.nclose;
+        o.inner = L.inner;
+        o.head = L.nclose ? L.head : L.head + R.head;
+        o.tail = L.nclose ? L.tail + R.head : 0u;
+    } else if (L.nclose == 0) {
+        o.nclose = R.nclose;
+        o.head = L.head + R.head;
+        o.inner = R.inner;
+        o.tail = R.tail;
+    } else {
+        o.nclose = L.nclose + R.nclose;
+        o.head = L.head;
+        o.inner = L.inner + subs_of(L.tail + R.head) + R.inner;
+        o.tail = R.tail;
+    }
+    return o;
+}
+
+// Two 64-bit words per tile: {flag:2 | ended:1 | nclose:29 | head:32}, {flag:2 | inner:30 | tail:32}.
+// flag 1: the tile's own aggregate, 2: inclusive prefix.  Both words carry the flag, so a reader
+// can tell a half-written pair (the flags differ) and reads again.
+constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagPrefix = 2ull << 62;
+
+__device__ __forceinline__ void publish(unsigned long long* d, const Elem& e, unsigned long long flag)
+{
+    const unsigned long long w0 =
+        flag | ((unsigned long long)(e.ended & 1u) << 61) | ((unsigned long long)(e.nclose & 0x1fffffffu) << 32) | e.head;
+    const unsigned long long w1 = flag | ((unsigned long long)(e.inner & 0x3fffffffu) << 32) | e.tail;
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(d), "l"(w0) : "memory");
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(d + 1), "l"(w1) : "memory");
+}
+
+// Returns the flag (0: not ready or half written).
+__device__ __forceinline__ uint32_t peek_desc(const unsigned long long* d, Elem& e)
+{
+    unsigned long long w0, w1;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w0) : "l"(d) : "memory");
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w1) : "l"(d + 1) : "memory");
+    const uint32_t f0 = (uint32_t)(w0 >> 62), f1 = (uint32_t)(w1 >> 62);
+    e.ended = (uint32_t)(w0 >> 61) & 1u;
+    e.nclose = (uint32_t)(w0 >> 32) & 0x1fffffffu;
+    e.head = (uint32_t)w0;
+    e.inner = (uint32_t)(w1 >> 32) & 0x3fffffffu;
+    e.tail = (uint32_t)w1;
+    return f0 == f1 ? f0 : 0u;
+}
+
+__device__ __forceinline__ Elem shfl_down_elem(const Elem& e, int d)
+{
+    Elem o;
+    const uint32_t ce = __shfl_down_sync(0xffffffffu, e.nclose | (e.ended << 31), d);
+    o.nclose = ce & 0x7fffffffu;
+    o.ended = ce >> 31;
+    o.head = __shfl_down_sync(0xffffffffu, e.head, d);
+    o.inner = __shfl_down_sync(0xffffffffu, e.inner, d);
+    o.tail = __shfl_down_sync(0xffffffffu, e.tail, d);
+    return o;
+}
+
+// The combine of all tiles before `tile`: decoupled look-back by the whole CTA, thread t looks at
+// tile `tile - 1 - t` of the current window of kDestuffThreads tiles.  All tiles of an image are
+// resident at once and start together, so when a tile looks back its predecessors have published
+// aggregates but hardly any prefix: the look-back usually runs all the way to the start of the
+// scan, and a 32-wide window would make the last tile of a 12 MP scan wait for 11 round trips to
+// L2.  Called by every thread; the result is valid in every thread.
+struct LookBackSmem {
+    Elem warp_elem[kDestuffThreads / 32];
+    uint32_t warp_stop[kDestuffThreads / 32];
+    uint32_t warp_sum[kDestuffThreads / 32];
+};
+
+__device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32_t tile, LookBackSmem& sm)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kWarps = kDestuffThreads / 32;
+    Elem carry = {0u, 0u, 0u, 0u, 0u}; // combine of the tiles between the window and `tile`
+    for (uint32_t base = 0; base < tile; base += (uint32_t)kDestuffThreads) {
+        const uint32_t t = base + threadIdx.x;
+        Elem e = {0u, 0u, 0u, 0u, 0u};
+        uint32_t flag = 2u; // threads past tile 0 stand for the (empty) prefix before the scan
+        if (t < tile) {
+            // every earlier tile is running or done (tickets); the bound only matters if the
+            // descriptors were not zero when the kernel started (decode without transfer): the
+            // decode is then garbage, but it ends
+            const unsigned long long* d = desc + 2ull * (tile - 1u - t);
+            for (int spin = 0; (flag = peek_desc(d, e)) == 0u && spin < (1 << 16); ++spin) __nanosleep(32);
+            if (flag == 0u) {
+                flag = 2u;
+                e = Elem{0u, 0u, 0u, 0u, 1u};
+            }
+        }
+        // nearest tile with an inclusive prefix: nothing beyond it matters
+        const uint32_t has_prefix = __ballot_sync(0xffffffffu, flag == 2u);
+        if (lane == 0) sm.warp_stop[warp] = has_prefix ? (uint32_t)(warp * 32 + __ffs((int)has_prefix) - 1) : 0xffffffffu;
+        __syncthreads();
+        uint32_t stop = 0xffffffffu;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) stop = min(stop, sm.warp_stop[w]);
+        if (threadIdx.x > stop) e = Elem{0u, 0u, 0u, 0u, 0u};
+        Elem win;
+        if (!__syncthreads_or((int)(e.nclose | e.ended))) {
+            // no closing in the whole window (every scan without DRI): the heads just add up
+            const uint32_t sum = __reduce_add_sync(0xffffffffu, e.head);
+            if (lane == 0) sm.warp_sum[warp] = sum;
+            __syncthreads();
+            uint32_t total = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) total += sm.warp_sum[w];
+            win = Elem{0u, total, 0u, 0u, 0u};
+        } else {
+            // ordered tree reduction: lane l ends with E[31] o ... o E[l] (higher thread = earlier tile)
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const Elem far = shfl_down_elem(e, d);
+                if (lane + d < 32) e = combine(far, e);
+            }
+            if (lane == 0) sm.warp_elem[warp] = e;
+            __syncthreads();
+            win = sm.warp_elem[kWarps - 1];
+#pragma unroll
+            for (int w = kWarps - 2; w >= 0; --w) win = combine(win, sm.warp_elem[w]);
+        }
+        carry = combine(win, carry);
+        if (stop != 0xffffffffu) break; // an inclusive prefix was found (the start of the scan counts as one)
+        __syncthreads();                // the next window reuses the shared arrays
+    }
+    return carry;
+}
+
+struct DestuffArgs {
+    const uint8_t* src;        // stuffed bytes from the start of the scan
+    uint32_t n;                // bytes available (the scan may end earlier, at its terminating marker)
+    uint8_t* dst;              // destuffed scan
+    SegDesc* segs;             // out: segment directory
+    uint32_t seg_cap, sub_cap; // capacities of the directory / of dst in subsequences
+    unsigned long long* desc;  // look-back descriptors, 2 words per tile; zero on entry
+    uint32_t* ticket;          // zero on entry
+    ScanInfo* info;            // out
+    uint32_t* clear;           // control block + mailboxes of the later stages
+    uint32_t clear_words;
+};
+
+// (six CTAs per SM: every tile of a 12 MP scan is resident at once - a tile of a second wave would
+// spend the whole first wave waiting for its ticket)
+__global__ void __launch_bounds__(kDestuffThreads, 6)
+destuff_kernel(const DestuffArgs a)
 {
     __shared__ uint32_t warp_sums[kDestuffThreads / 32];
     __shared__ uint8_t stage[kDestuffTile];
-    __shared__ uint16_t seg_delta[kDestuffTile];
+    __shared__ uint16_t seg_of[kDestuffTile];  // closings before the staged byte, inside the tile
+    __shared__ uint32_t close_at[kMaxClose];   // data bytes of the tile before closing i
+    __shared__ uint32_t sub_rel[kMaxClose + 1]; // subsequences of the segments closed by closings 1..i-1
+    __shared__ uint32_t s_tile, s_term, s_flags, s_inner;
+    __shared__ LookBackSmem s_look;
 
     // first kernel of a scan (launched behind the upload copies): let huff_sync start its
     // prologue (tables, zero-fill of the coefficient buffer) right away
     grid_dependency_wait();
     grid_dependency_trigger();
-    for (uint32_t i = blockIdx.x * kDestuffThreads + threadIdx.x; i < clear_words;
+    for (uint32_t i = blockIdx.x * kDestuffThreads + threadIdx.x; i < a.clear_words;
          i += gridDim.x * kDestuffThreads)
-        clear[i] = 0u;
+        a.clear[i] = 0u;
+    if (threadIdx.x == 0) {
+        s_tile = atomicAdd(a.ticket, 1u);
+        s_term = kDestuffTile;
+        s_flags = 0u;
+    }
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    if (tile >= gridDim.x) return; // the ticket was not zero on entry (decode without transfer)
+    const uint32_t n = a.n;
+    const uint32_t tile_begin = tile * (uint32_t)kDestuffTile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
-    const TileDesc tile = tiles[blockIdx.x];
-    const uint32_t kept_base = tile.kept_before;
-    const uint32_t seg_base = tile.segs_before;
-
-    const uint32_t base = (blockIdx.x * kDestuffThreads + threadIdx.x) * kDestuffBytesPerThread;
+    const uint32_t base = tile_begin + threadIdx.x * kDestuffBytesPerThread;
     Chunk ck;
-    classify(src, n, base, ck);
+    classify(a.src, n, base, ck);
+    // The scan ends at its first terminating marker or, failing that, with the data: nothing at or
+    // behind that position counts.
+    const bool last_tile = tile_begin + (uint32_t)kDestuffTile >= n;
+    if (__syncthreads_or(ck.term < 16u || last_tile)) {
+        if (ck.term < 16u) atomicMin(&s_term, threadIdx.x * kDestuffBytesPerThread + ck.term);
+        __syncthreads();
+        uint32_t term = s_term;
+        if (term == (uint32_t)kDestuffTile && last_tile) {
+            term = n - tile_begin; // 1 .. kDestuffTile: the data ran out before a marker was seen
+            if (threadIdx.x == 0) s_flags = kScanUnterminated;
+        }
+        const uint32_t mine = threadIdx.x * kDestuffBytesPerThread;
+        const uint32_t live = term <= mine ? 0u : term - mine >= 16u ? 0xffffu : (1u << (term - mine)) - 1u;
+        ck.keep &= live;
+        ck.rst &= live;
+        if (threadIdx.x == 0) s_term = term;
+    }
     uint32_t tile_total;
     const uint32_t ex = block_exclusive_scan(__popc(ck.keep) | (__popc(ck.rst) << 16), warp_sums,
                                              tile_total);
@@ -109,26 +319,102 @@ destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __re
     for (int i = 0; i < 16; ++i) {
         if ((ck.keep >> i) & 1u) {
             stage[pos] = ck.val[i];
-            seg_delta[pos] = (uint16_t)seg;
+            seg_of[pos] = (uint16_t)seg;
             ++pos;
         }
-        seg += (ck.rst >> i) & 1u;
+        if ((ck.rst >> i) & 1u) close_at[seg++] = pos;
+    }
+    const uint32_t tile_kept = tile_total & 0xffffu;
+    const bool ends_here = s_term < (uint32_t)kDestuffTile || (last_tile && s_term == n - tile_begin);
+    uint32_t nclose = tile_total >> 16;
+    if (ends_here) { // the end of the scan closes the open segment
+        if (threadIdx.x == 0) close_at[nclose] = tile_kept;
+        ++nclose;
     }
     __syncthreads();
 
-    const uint32_t tile_kept = tile_total & 0xffffu;
-    if ((tile_total >> 16) == 0u && (int)seg_base < num_segments) {
-        // No restart marker inside the tile (every tile of a scan without DRI, most tiles
-        // otherwise): one segment, one contiguous run of output bytes.  Whole big-endian words
-        // are assembled from the staged bytes and stored with 4-byte stores; only the run's
-        // unaligned head and tail go byte by byte.
-        const SegDesc sd = segs[seg_base];
-        const uint32_t r0 = kept_base - sd.kept_before;               // index inside the segment
-        const uint32_t d0 = r0 + sd.sub_off * (uint32_t)kSubBytes;    // output position of stage[0]
+    // subsequences of the segments closed inside the tile by closings 1 .. nclose-1, as a running
+    // sum (restart markers are rare - one per MCU row in camera files - so one warp does it)
+    if (nclose <= 1) {
+        if (threadIdx.x < 2) sub_rel[threadIdx.x] = 0u;
+        if (threadIdx.x == 0) s_inner = 0u;
+    } else if (warp == 0) {
+        uint32_t run = 0;
+        for (uint32_t i0 = 1;; i0 += 32u) {
+            const uint32_t i = i0 + (uint32_t)lane;
+            uint32_t v = i < nclose ? subs_of(close_at[i] - close_at[i - 1]) : 0u, inc = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += up;
+            }
+            if (i <= nclose) sub_rel[i] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+            if (i0 + 31u >= nclose) break; // the chunk held index nclose: `run` is the aggregate's `inner`
+        }
+        if (lane == 0) s_inner = run;
+    }
+    __syncthreads();
+    // aggregate, look-back, inclusive prefix
+    Elem agg;
+    agg.nclose = nclose;
+    agg.head = nclose ? close_at[0] : tile_kept;
+    agg.inner = s_inner;
+    agg.tail = nclose ? tile_kept - close_at[nclose - 1] : 0u;
+    agg.ended = ends_here ? 1u : 0u;
+    unsigned long long* mine = a.desc + 2ull * tile;
+    if (threadIdx.x == 0 && tile != 0) publish(mine, agg, kFlagAgg);
+    const Elem before = tile ? look_back(a.desc, tile, s_look) : Elem{0u, 0u, 0u, 0u, 0u};
+    if (threadIdx.x == 0) {
+        const Elem incl = combine(before, agg);
+        publish(mine, incl, kFlagPrefix);
+        if (ends_here && !before.ended) {
+            // the end of the scan: totals for the later stages (the end closed the last segment)
+            const uint32_t subs = subs_of(incl.head) + incl.inner;
+            ScanInfo si;
+            si.num_subs = min(subs, a.sub_cap);
+            si.num_segments = min(incl.nclose, a.seg_cap);
+            si.scan_end = tile_begin + s_term;
+            si.status = s_flags | ((subs > a.sub_cap || incl.nclose > a.seg_cap) ? kScanOverflow : 0u);
+            *a.info = si;
+        }
+    }
+    if (before.ended) return; // bytes behind the end of the scan
+    const uint32_t closed0 = before.nclose ? subs_of(before.head) + before.inner : 0u; // subsequences
+    const uint32_t open0 = before.nclose ? before.tail : before.head; // bytes already in the open segment
+    const uint32_t segs0 = before.nclose;
+    const unsigned long long cap_bytes = (unsigned long long)a.sub_cap * kSubBytes;
+
+    // the segments this tile closes: directory entry + zero padding to a whole subsequence
+    const uint32_t first_subs = nclose ? subs_of(open0 + close_at[0]) : 0u;
+    for (uint32_t i = threadIdx.x; i < nclose; i += kDestuffThreads) {
+        const uint32_t nbytes = i ? close_at[i] - close_at[i - 1] : open0 + close_at[0];
+        const uint32_t sub_off = i ? closed0 + first_subs + sub_rel[i] : closed0;
+        const uint32_t g = segs0 + i;
+        if (g >= a.seg_cap || (unsigned long long)sub_off + subs_of(nbytes) > a.sub_cap) continue;
+        SegDesc sd;
+        sd.sub_off = sub_off;
+        sd.nbytes = nbytes;
+        sd.kept_before = 0;
+        sd.src_begin = 0;
+        a.segs[g] = sd;
+        const uint32_t d_end = sub_off * (uint32_t)kSubBytes + nbytes;
+        const uint32_t pad_end = (d_end + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes * (uint32_t)kSubBytes;
+        for (uint32_t z = d_end; z < pad_end; ++z) a.dst[z ^ 3u] = 0;
+    }
+
+    if (nclose == 0 || close_at[0] == tile_kept) {
+        // Every data byte of the tile belongs to the segment that was open on entry (every tile of
+        // a scan without DRI, most tiles otherwise): one contiguous run of output bytes.  Whole
+        // big-endian words are assembled from the staged bytes and stored with 4-byte stores;
+        // only the run's unaligned head and tail go byte by byte.
+        const unsigned long long d0l = (unsigned long long)closed0 * kSubBytes + open0;
+        if (d0l + tile_kept > cap_bytes) return; // a damaged stream outgrew the plan (flagged above)
+        const uint32_t d0 = (uint32_t)d0l;
         const uint32_t d_end = d0 + tile_kept;
         const uint32_t w_begin = (d0 + 3u) & ~3u, w_end = d_end & ~3u; // whole words [w_begin, w_end)
         if (w_begin < w_end) {
-            uint32_t* words = reinterpret_cast<uint32_t*>(dst);
+            uint32_t* words = reinterpret_cast<uint32_t*>(a.dst);
             for (uint32_t w = w_begin + 4u * threadIdx.x; w < w_end; w += 4u * kDestuffThreads) {
                 const uint32_t o = w - d0;
                 words[w >> 2] = ((uint32_t)stage[o] << 24) | ((uint32_t)stage[o + 1] << 16) |
@@ -142,26 +428,16 @@ destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __re
         if (threadIdx.x < edge) {
             const uint32_t d = threadIdx.x < head_end - d0 ? d0 + threadIdx.x
                                                            : tail_begin + (threadIdx.x - (head_end - d0));
-            dst[d ^ 3u] = stage[d - d0];
-        }
-        if (tile_kept != 0u && r0 + tile_kept == sd.nbytes) { // the segment ends in this tile: pad
-            const uint32_t pad_end = (d_end - 1u + (uint32_t)kSubBytes) / (uint32_t)kSubBytes * (uint32_t)kSubBytes;
-            for (uint32_t z = d_end + threadIdx.x; z < pad_end; z += kDestuffThreads) dst[z ^ 3u] = 0;
+            a.dst[d ^ 3u] = stage[d - d0];
         }
         return;
     }
     for (uint32_t o = threadIdx.x; o < tile_kept; o += kDestuffThreads) {
-        const uint32_t s = seg_base + seg_delta[o];
-        if ((int)s >= num_segments) continue; // cannot happen: host and device rules agree
-        const SegDesc sd = segs[s];
-        // data byte number k of the scan lands at k - kept_before + sub_off * kSubBytes
-        const uint32_t r = kept_base + o - sd.kept_before; // index inside the segment
-        const uint32_t d = r + sd.sub_off * (uint32_t)kSubBytes;
-        dst[d ^ 3u] = stage[o];
-        if (r + 1u == sd.nbytes) { // last byte of the segment: pad to a whole subsequence
-            const uint32_t pad_end = (d + (uint32_t)kSubBytes) / (uint32_t)kSubBytes * (uint32_t)kSubBytes;
-            for (uint32_t z = d + 1u; z < pad_end; ++z) dst[z ^ 3u] = 0;
-        }
+        const uint32_t s = seg_of[o];
+        unsigned long long d;
+        if (s == 0) d = (unsigned long long)closed0 * kSubBytes + open0 + o;
+        else d = (unsigned long long)(closed0 + first_subs + sub_rel[s]) * kSubBytes + (o - close_at[s - 1]);
+        if (d < cap_bytes && segs0 + s < a.seg_cap) a.dst[(uint32_t)d ^ 3u] = stage[o];
     }
 }
 
@@ -169,16 +445,25 @@ destuff_kernel(const uint8_t* __restrict__ src, uint32_t n, const TileDesc* __re
 
 cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
-    if (g.scan_bytes == 0) return cudaSuccess;
+    if (g.scan_avail == 0) return cudaSuccess;
     static PerDeviceOnce configured;
     configured.run([] { prefer_max_shared(destuff_kernel); });
-    const uint32_t tiles = (g.scan_bytes + kDestuffTile - 1) / kDestuffTile;
+    const uint32_t tiles = (g.scan_avail + kDestuffTile - 1) / kDestuffTile;
+    DestuffArgs a;
+    a.src = b.scan_bytes;
+    a.n = g.scan_avail;
+    a.dst = reinterpret_cast<uint8_t*>(b.destuffed);
+    a.segs = b.segs;
+    a.seg_cap = (uint32_t)g.num_segments;
+    a.sub_cap = g.num_subs;
+    a.desc = b.destuff_desc;
+    a.ticket = b.destuff_ticket;
+    a.info = b.info;
     // the control block, the mailboxes and the DC flags are contiguous (planner): one clear range
-    const uint32_t clear_words = b.clear_words;
+    a.clear = reinterpret_cast<uint32_t*>(b.ctrl);
+    a.clear_words = b.clear_words;
     tm->mark(stream, kIdDestuff);
-    destuff_kernel<<<tiles, kDestuffThreads, 0, stream>>>(
-        b.scan_bytes, g.scan_bytes, b.tiles, b.segs, g.num_segments,
-        reinterpret_cast<uint8_t*>(b.destuffed), reinterpret_cast<uint32_t*>(b.ctrl), clear_words);
+    destuff_kernel<<<tiles, kDestuffThreads, 0, stream>>>(a);
     return cudaGetLastError();
 }
 

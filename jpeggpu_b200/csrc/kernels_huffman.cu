@@ -161,11 +161,11 @@ __device__ __forceinline__ void stage_tables(const ScanGeom& g, const ScanBufs& 
     if (threadIdx.x == 0) make_device_recs(g, st, true);
 }
 // ...the window of the scan from the destuff kernel's output.  Ends with a barrier.
-__device__ __forceinline__ void stage_window(const ScanGeom& g, const ScanBufs& b,
+__device__ __forceinline__ void stage_window(const ScanBufs& b, uint32_t num_subs,
                                              long long first_word, const int WIN_WORDS)
 {
     uint32_t* win = reinterpret_cast<uint32_t*>(s_dyn);
-    const long long total_words = (long long)g.num_subs * kSubWords;
+    const long long total_words = (long long)num_subs * kSubWords;
     const uint4* src = reinterpret_cast<const uint4*>(b.destuffed);
     for (int i = threadIdx.x; i < WIN_WORDS / 4; i += blockDim.x) {
         const long long w = first_word + 4ll * i;
@@ -371,18 +371,18 @@ __device__ __forceinline__ void zero_fill(void* base, size_t bytes)
 
 // The warp's share of huff_sync: fix-point iteration over its chunk, mailbox exchange with the
 // chunk on its left, one record per owned subsequence.
-__device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
-                                           long long win_sub0, uint32_t chunk, int lane)
+__device__ __forceinline__ void sync_chunk(const ScanBufs& b, uint32_t num_subs, int num_segments,
+                                           SharedTables& st, long long win_sub0, uint32_t chunk, int lane)
 {
     const long long sub = (long long)chunk * kChunkSubs - kOverlapSubs + lane;
     const uint32_t chunk_first = chunk * (uint32_t)kChunkSubs;
-    const bool active = sub >= 0 && sub < (long long)g.num_subs;
+    const bool active = sub >= 0 && sub < (long long)num_subs;
 
     uint32_t k = 0, i = 0, seg_bits = 0;
     bool head = false;
     DevMem M{&st, b.slow, smem_addr(st.recs), 0, smem_addr(s_dyn + kSyncWinWords / 4)};
     if (active) {
-        k = find_segment(b.segs, g.num_segments, (uint32_t)sub);
+        k = find_segment(b.segs, num_segments, (uint32_t)sub);
         const SegDesc seg = b.segs[k];
         i = (uint32_t)sub - seg.sub_off;
         head = i == 0;
@@ -432,7 +432,7 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
     iterate(0);
 
     // mailbox: publish the exit state of the chunk's last subsequence, check the left neighbour
-    const uint32_t last_sub = umin(chunk_first + (uint32_t)kChunkSubs, g.num_subs) - 1u;
+    const uint32_t last_sub = umin(chunk_first + (uint32_t)kChunkSubs, num_subs) - 1u;
     const int last_lane = (int)(last_sub - chunk_first) + kOverlapSubs;
     volatile uint32_t* mailbox = b.chunk_state;
     if (lane == last_lane) mailbox[chunk] = 0x80000000u | entry_x(rec);
@@ -473,10 +473,9 @@ __device__ __forceinline__ void sync_chunk(const ScanGeom& g, const ScanBufs& b,
 // possible only when a mailbox wait timed out or a left neighbour re-published after it was
 // read, so this is a few hundred loads in practice; on adversarial streams it degenerates to a
 // serial decode, like the reference's TODO at src/decode_huffman.cu:475.
-__device__ __forceinline__ void verify_and_repair(const ScanGeom& g, const ScanBufs& b, SharedTables& st)
+__device__ __forceinline__ void verify_and_repair(const ScanBufs& b, uint32_t N, SharedTables& st)
 {
     volatile unsigned long long* entries = reinterpret_cast<volatile unsigned long long*>(b.entries);
-    const uint32_t N = g.num_subs;
     uint32_t stride = (uint32_t)kChunkSubs; // first round: only chunk boundaries can disagree
     uint32_t rounds = 0, slow_total = 0;
     for (;;) {
@@ -516,12 +515,16 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     zero_fill(b.dc, b.dc_bytes);
     grid_dependency_wait();
     grid_dependency_trigger();
-    stage_window(g, b, win_sub0 * kSubWords, kSyncWinWords);
+    // the totals of the scan come from the destuff kernel (the grid was sized from upper bounds)
+    const uint32_t num_subs = __ldcg(&b.info->num_subs);
+    const int num_segments = (int)__ldcg(&b.info->num_segments);
+    stage_window(b, num_subs, win_sub0 * kSubWords, kSyncWinWords);
     const unsigned long long t1 = now_ns();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t chunk = blockIdx.x * kSyncWarps + warp;
-    if (chunk * (uint32_t)kChunkSubs < g.num_subs) sync_chunk(g, b, st, win_sub0, chunk, lane); // warp-uniform
+    if (chunk * (uint32_t)kChunkSubs < num_subs) // warp-uniform
+        sync_chunk(b, num_subs, num_segments, st, win_sub0, chunk, lane);
     const unsigned long long t2 = now_ns();
 
     // last CTA out verifies the records of the whole scan
@@ -531,7 +534,11 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     __syncthreads();
     if (s_last) {
         __threadfence();
-        verify_and_repair(g, b, st);
+        verify_and_repair(b, num_subs, st);
+        // destuff is long done: re-arm its look-back descriptors and ticket for the next decode
+        // that runs on this scratch without a new transfer (transfer uploads them as zeros)
+        uint32_t* arm = reinterpret_cast<uint32_t*>(b.destuff_desc);
+        for (uint32_t i = threadIdx.x; i < b.destuff_words; i += blockDim.x) arm[i] = 0u;
     }
     if (lane == 0) {
         atomicMax(&b.ctrl->sync_stage_ns, (uint32_t)(t1 - t0));
@@ -644,6 +651,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
     grid_dependency_wait();
     grid_dependency_trigger();
     __syncthreads();
+    const uint32_t num_subs = __ldcg(&b.info->num_subs);
     const uint32_t cta = s_cta;
     const uint32_t sub0 = cta * subs_per_cta;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -653,7 +661,7 @@ huff_write(const ScanGeom g, const ScanBufs b)
     // that the CTAs after this one never wait for it
     unsigned long long rec = 0;
     uint32_t mid = 0, mid_next = 0, k = 0; // state at this part's start / at its end (h < last)
-    if (j < g.num_subs) {
+    if (j < num_subs) {
         const ulonglong2* rp = reinterpret_cast<const ulonglong2*>(b.entries) + (size_t)j * (kRecWords / 2);
         const ulonglong2 r = __ldcg(rp);
         rec = r.x;
@@ -673,19 +681,19 @@ huff_write(const ScanGeom g, const ScanBufs b)
         }
         k = __ldcg(b.seg_idx + j);
     }
-    const bool is_head = j < g.num_subs && (entry_g(rec) & kStateHead) != 0;
+    const bool is_head = j < num_subs && (entry_g(rec) & kStateHead) != 0;
     uint32_t q0 = cta_slot_prefix(cta, h == 0 ? entry_n(rec) : 0u, h == 0 && is_head, b.write_agg);
     q0 = __shfl_sync(0xffffffffu, q0, lane & ~(kWriteParts - 1)); // the sub's first thread has it
-    if (h == 0 && j < g.num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
+    if (h == 0 && j < num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
 
-    stage_window(g, b, (long long)sub0 * kSubWords, win_words);
+    stage_window(b, num_subs, (long long)sub0 * kSubWords, win_words);
     const unsigned long long t1 = now_ns();
 
     // this thread's half subsequence: placement, slot range [qs, qe)
     bool has = false;
     uint32_t first_du = 0, q_limit = 0, qs = 0, qe = 0, i = 0;
     SegDesc seg = {0, 0, 0, 0};
-    if (j < g.num_subs) {
+    if (j < num_subs) {
         seg = b.segs[k];
         i = j - seg.sub_off;
         if (segment_extent(g, k, first_du, q_limit)) {

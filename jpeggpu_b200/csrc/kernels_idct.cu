@@ -714,7 +714,7 @@ cudaError_t launch_ycc_to_rgbi(const PlanarIn& in, const RgbOut& out, cudaStream
 int count_launches(const ScanGeom& g, bool with_transpose)
 {
     int n = 0;
-    if (g.scan_bytes) n += 1;
+    if (g.scan_avail) n += 1;
     if (g.num_subs) n += 2;
     if (g.total_mcus) n += 1;
     n += 1; // idct

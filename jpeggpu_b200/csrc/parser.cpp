@@ -414,6 +414,7 @@ jpeggpu_status walk_scan(Cursor& cur, ScanPlan& sp, uint64_t start_off = 0)
     sp.end = (size_t)(cur.p - cur.begin);
     if (sp.end - sp.begin >= (1ull << 31) || sub_off >= (1ull << 31)) return JPEGGPU_NOT_SUPPORTED;
     sp.geom.scan_bytes = (uint32_t)(sp.end - sp.begin);
+    sp.geom.scan_avail = sp.geom.scan_bytes + 2u; // the marker the walk stopped at
     sp.geom.num_subs = (uint32_t)sub_off;
     sp.geom.num_segments = (int)sp.segs.size();
     sp.tiles.resize(((size_t)sp.geom.scan_bytes + kDestuffTile - 1) / kDestuffTile);
@@ -595,7 +596,7 @@ bool walk_parallel(WalkPool* pool, const ImagePlan& plan, Cursor& cur, ScanPlan&
 
 // Scan header + geometry. Statuses follow src/reader.cpp:305-441.
 jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logger& log,
-                        bool allow_defer)
+                        int walk)
 {
     if (!st.found_sof) return JPEGGPU_INVALID_JPEG;
     if (cur.left() < 3) return JPEGGPU_INVALID_JPEG;
@@ -691,12 +692,30 @@ jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logg
     ++plan.num_scans;
     // Deferred walk (parser.hpp): the one scan of the file, no DRI, EOI at the very end.
     const size_t left = cur.left();
-    if (allow_defer && plan.num_scans == 1 && ns == plan.num_comp && plan.restart_interval == 0 &&
+    if (walk == kWalkDevice && plan.num_scans == 1 && ns == plan.num_comp && left >= kDeferMinBytes &&
+        left < (1ull << 31) - 4096) {
+        // the scan is planned as if it filled the rest of the file; T.81 E.1.4: ceil(MCUs / Ri)
+        // restart segments (+ slack for stray markers in damaged files)
+        sp.begin = (size_t)(cur.p - cur.begin);
+        sp.end = (size_t)(cur.end - cur.begin);
+        g.scan_bytes = (uint32_t)(sp.end - sp.begin);
+        g.scan_avail = g.scan_bytes;
+        const int64_t expected = (total + g.restart_interval - 1) / g.restart_interval;
+        if (expected + kDeferSegSlack < (1ll << 28)) {
+            g.num_segments = (int)expected + kDeferSegSlack;
+            g.num_subs = (g.scan_bytes + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes + (uint32_t)g.num_segments;
+            plan.walk_pending = true;
+            plan.device_walk = true;
+            return JPEGGPU_SUCCESS;
+        }
+    }
+    if (walk == kWalkDeferred && plan.num_scans == 1 && ns == plan.num_comp && plan.restart_interval == 0 &&
         left >= kDeferMinBytes + 2 && left - 2 < (1ull << 31) - 4096 && cur.end[-2] == 0xff &&
         cur.end[-1] == 0xd9) {
         sp.begin = (size_t)(cur.p - cur.begin);
         sp.end = (size_t)(cur.end - 2 - cur.begin);
         g.scan_bytes = (uint32_t)(sp.end - sp.begin);
+        g.scan_avail = g.scan_bytes + 2u;
         g.num_segments = 1 + kDeferSegSlack;
         g.num_subs = (g.scan_bytes + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes + (uint32_t)kDeferSegSlack;
         plan.walk_pending = true;
@@ -706,7 +725,7 @@ jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logg
 }
 
 // The marker loop from the current position to EOI (or to a deferred scan).
-jpeggpu_status marker_loop(Cursor& cur, ImagePlan& plan, const Logger& log, bool allow_defer)
+jpeggpu_status marker_loop(Cursor& cur, ImagePlan& plan, const Logger& log, int walk)
 {
     ParseState& st = plan.st;
     for (;;) {
@@ -728,7 +747,7 @@ jpeggpu_status marker_loop(Cursor& cur, ImagePlan& plan, const Logger& log, bool
         } else if (m == 0xd9) {
             break;
         } else if (m == 0xda) {
-            s = read_sos(cur, plan, st, log, allow_defer);
+            s = read_sos(cur, plan, st, log, walk);
             if (s == JPEGGPU_SUCCESS && plan.walk_pending) return s; // resumed by finish_deferred_walk
         } else if (m == 0xdb) {
             s = read_dqt(cur, plan, log);
@@ -749,11 +768,12 @@ jpeggpu_status marker_loop(Cursor& cur, ImagePlan& plan, const Logger& log, bool
 }
 
 jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
-                          bool allow_defer)
+                          int walk)
 {
     Cursor cur{data, data, data + size};
     plan.st = ParseState{};
     plan.walk_pending = false;
+    plan.device_walk = false;
     ++plan.generation;
     plan.width = plan.height = plan.num_comp = 0;
     plan.restart_interval = 0;
@@ -765,7 +785,7 @@ jpeggpu_status parse_impl(const uint8_t* data, size_t size, ImagePlan& plan, con
     if (cur.left() < 2) return JPEGGPU_INVALID_JPEG;
     if (cur.u8() != 0xff || cur.u8() != 0xd8) return JPEGGPU_INVALID_JPEG;
     log.log("marker SOI\n");
-    return marker_loop(cur, plan, log, allow_defer);
+    return marker_loop(cur, plan, log, walk);
 }
 
 jpeggpu_status finish_impl(ImagePlan& plan, const Logger& log, WalkPool* pool)
@@ -774,6 +794,7 @@ jpeggpu_status finish_impl(ImagePlan& plan, const Logger& log, WalkPool* pool)
     const ScanGeom bound = sp.geom;
     Cursor cur{plan.file + sp.begin, plan.file, plan.file + plan.file_size};
     plan.walk_pending = false;
+    plan.device_walk = false;
     jpeggpu_status s = JPEGGPU_SUCCESS;
     if (!walk_parallel(pool, plan, cur, sp, &s)) {
         cur = Cursor{plan.file + sp.begin, plan.file, plan.file + plan.file_size};
@@ -783,19 +804,19 @@ jpeggpu_status finish_impl(ImagePlan& plan, const Logger& log, WalkPool* pool)
     }
     if (s != JPEGGPU_SUCCESS) return s;
     // the scratch plan was sized from the bounds
-    if (sp.geom.scan_bytes > bound.scan_bytes || sp.geom.num_subs > bound.num_subs ||
-        sp.geom.num_segments > bound.num_segments)
+    if (sp.geom.scan_bytes > bound.scan_bytes || sp.geom.scan_avail > bound.scan_avail ||
+        sp.geom.num_subs > bound.num_subs || sp.geom.num_segments > bound.num_segments)
         return JPEGGPU_INVALID_JPEG; // more stray restart markers than the slack allows
-    return marker_loop(cur, plan, log, false);
+    return marker_loop(cur, plan, log, kWalkEager);
 }
 
 } // namespace
 
 jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
-                          bool allow_defer)
+                          int walk)
 {
     try {
-        return parse_impl(data, size, plan, log, allow_defer);
+        return parse_impl(data, size, plan, log, walk);
     } catch (const std::bad_alloc&) {
         return JPEGGPU_OUT_OF_HOST_MEMORY;
     }

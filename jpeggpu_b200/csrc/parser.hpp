@@ -60,8 +60,11 @@ struct ImagePlan {
     size_t file_size = 0;
     ParseState st;
     // true: scans[0] holds an upper-bound geometry (scan_bytes, num_subs, num_segments) and empty
-    // directories; finish_deferred_walk() must run before the directories are used.
+    // directories; finish_deferred_walk() must run before host code uses exact counts.
     bool walk_pending = false;
+    // true (with walk_pending): the device finds the end of the scan and the restart segments
+    // itself (kernels_destuff.cu); no host walk is needed to decode.
+    bool device_walk = false;
     uint64_t generation = 0; // bumped by every parse: identifies the image a helper job belongs to
 };
 
@@ -76,8 +79,12 @@ struct Logger {
 // to the EOI at the end of the file, its geometry holds upper bounds, and the byte walk (the only
 // part of the parse whose cost grows with the file) is left to finish_deferred_walk(), which the
 // decoder runs inside jpeggpu_decoder_transfer while the upload of those bytes is in flight.
+// walk: kWalkEager, kWalkDeferred (rules above) or kWalkDevice: every file whose first scan holds
+// all frame components stops at the scan header, whatever follows; the scan is taken to reach to
+// the end of the file and the device locates its real end (the bytes behind it are uploaded too).
+enum WalkMode { kWalkEager = 0, kWalkDeferred = 1, kWalkDevice = 2 };
 jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
-                          bool allow_defer = false);
+                          int walk = kWalkEager);
 
 // Helper threads for the deferred walk of large scans.  The walk is memory bound on one core
 // (~35 GB/s: the previous upload has evicted the file from the caches), so scans of at least

@@ -70,6 +70,11 @@ class DecodeSession:
                                      self.scratch.numel(), s)
         return planes
 
+    def scan_info(self, scan=0):
+        """jpeggpu_b200_read_scan_info for the last decode on the current stream (synchronises)."""
+        return self.dec.read_scan_info(self.scratch.data_ptr(), scan,
+                                       torch.cuda.current_stream().cuda_stream)
+
     def read_scratch(self, offset, nbytes):
         return self.scratch[offset:offset + nbytes].cpu().numpy()
 

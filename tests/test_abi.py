@@ -112,27 +112,30 @@ def _stats_tuple(st):
             st.destuffed_bytes, st.num_subsequences, st.num_data_units)
 
 
+@pytest.mark.parametrize("mode", [1, 3], ids=["deferred_host_walk", "device_walk"])
 @pytest.mark.parametrize("tail", [b"", b"\x00" * 7], ids=["ends_with_eoi", "trailing_bytes"])
-def test_deferred_walk_plans_from_bounds(lib, tail):
-    """include/jpeggpu_b200.h jpeggpu_b200_set_deferred_walk: a single-scan file without DRI that
-    ends with EOI is planned from upper bounds at parse time; the exact counts (after the walk
-    that transfer or a statistics call triggers) equal those of the eager parse.  A file with
-    bytes behind EOI is not eligible and behaves exactly as before."""
+def test_deferred_walk_plans_from_bounds(lib, tail, mode):
+    """include/jpeggpu_b200.h jpeggpu_b200_set_deferred_walk: a single-scan file is planned from
+    upper bounds at parse time; the exact counts (after the host walk that a statistics call - or,
+    in mode 1, transfer - triggers) equal those of the eager parse.  Mode 1 (host walk behind the
+    upload) needs a file without DRI that ends with EOI: one with bytes behind EOI is parsed
+    eagerly.  Mode 3 (the device finds the end of the scan, the default) takes both."""
     data = inputs.pillow_jpeg(w=1600, h=1200, seed=5, mode="YCbCr", subsampling=2) + tail
     assert len(data) > 96 * 1024
     buf = np.frombuffer(data, dtype=np.uint8)
     eager, lazy = jb.Decoder(lib), jb.Decoder(lib)
     eager.set_deferred_walk(False)
+    lazy.set_deferred_walk(mode)
     ie = eager.parse_header(buf.ctypes.data, len(data), keepalive=buf)
     il = lazy.parse_header(buf.ctypes.data, len(data), keepalive=buf)
     assert bytes(ie) == bytes(il)
     exact, bound = eager.get_buffer_size(), lazy.get_buffer_size()
-    if tail:
+    if tail and mode == 1:
         assert bound == exact
     else:
         assert exact <= bound <= exact * 1.01
     assert _stats_tuple(lazy.scan_stats(0)) == _stats_tuple(eager.scan_stats(0))
-    assert abs(lazy.transfer_size() - eager.transfer_size()) <= 4096  # directory capacity slack
+    assert abs(lazy.transfer_size() - eager.transfer_size()) <= 8192  # capacity slack of the planned tables
     assert lazy.get_buffer_size() == bound  # the plan does not move after the walk
     eager.cleanup()
     lazy.cleanup()

@@ -6,7 +6,7 @@ TAG=${1:-r2}
 mkdir -p gpurun_out
 G=data/_gen
 FILES="$G/synth_4032x3024_s6510_q90.jpg $G/IMG_6510.JPG $G/synth_8064x6048_s48_q90.jpg $G/synth_1920x1080_s1_q90.jpg"
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.txt 2>&1; tail -3 gpurun_out/${TAG}_pytest_gpu.txt
+timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest_gpu.txt 2>&1; tail -3 gpurun_out/${TAG}_pytest_gpu.txt
 python tools/kernel_times.py $FILES > gpurun_out/${TAG}_kernel_times.txt 2>&1
 for v in jpeggpu_b200/lib/variants/*.so; do
   [ -f "$v" ] && JPEGGPU_B200_LIB=$v python tools/kernel_times.py $G/synth_4032x3024_s6510_q90.jpg $G/IMG_6510.JPG >> gpurun_out/${TAG}_kernel_times.txt 2>&1
