@@ -167,6 +167,48 @@ enum jpeggpu_status jpeggpu_b200_decode_batch(
     const size_t* tmp_size,
     int num_lanes);
 
+/* ---- fused batches: several images per kernel launch -------------------------------------------
+ * The lane helper above still pays, per image, five kernel launches, two copies and an event, and
+ * a 2 MP image fills a fraction of the GPU.  A fused batch decodes K images with ONE launch of each
+ * of the five kernels (a 2-D grid: image x CTA; per-image descriptors in device memory), one
+ * upload of the descriptor/table block, one memset and - when the files lie close together in one
+ * host allocation the caller has named (jpeggpu_b200_batch_set_host_arena), e.g. a pinned arena
+ * it filled - ONE copy of the whole span of files (otherwise one copy per file).  The device locates the end of every scan and its restart
+ * segments itself (walk mode 3 above), so the host only parses headers.
+ *
+ *   jpeggpu_b200_batch_create(&batch);
+ *   per batch:  jpeggpu_b200_batch_plan(batch, items, n, &arena_size);   host only; fills info/status
+ *               (caller provides >= arena_size bytes of device memory, 256-byte aligned, and the
+ *                output planes in items[i].img)
+ *               jpeggpu_b200_batch_decode(batch, items, n, d_arena, arena_size, stream);
+ *   jpeggpu_b200_batch_destroy(batch);
+ *
+ * Everything is enqueued on the caller's stream; nothing synchronises, except that batch_plan
+ * waits until the copies of the PREVIOUS decode of the same batch object have left its pinned
+ * staging block (use two or three batch objects round-robin to keep the device busy while the
+ * host plans).  Items the fused path cannot take - several scans, or any status other than
+ * JPEGGPU_SUCCESS at parse time - keep their status in items[i].status and are skipped by
+ * batch_decode (decode them with the per-image calls); batch_plan returns the first such status. */
+typedef struct jpeggpu_b200_batch* jpeggpu_b200_batch_t;
+enum jpeggpu_status jpeggpu_b200_batch_create(jpeggpu_b200_batch_t* batch);
+enum jpeggpu_status jpeggpu_b200_batch_destroy(jpeggpu_b200_batch_t batch);
+/* Optional: [base, base + bytes) is ONE host allocation (pinned for speed) that holds the files of
+ * the coming batches.  Batches whose files lie close together inside it are then uploaded with a
+ * single copy of the span from the first scan to the end of the last file; files outside it, or
+ * far apart, are copied one by one.  (Without this promise a span could cross unmapped memory.)
+ * bytes == 0 withdraws the promise. */
+enum jpeggpu_status jpeggpu_b200_batch_set_host_arena(jpeggpu_b200_batch_t batch, const void* base, size_t bytes);
+enum jpeggpu_status jpeggpu_b200_batch_plan(
+    jpeggpu_b200_batch_t batch, struct jpeggpu_b200_batch_item* items, int num_items, size_t* arena_size);
+enum jpeggpu_status jpeggpu_b200_batch_decode(
+    jpeggpu_b200_batch_t batch, struct jpeggpu_b200_batch_item* items, int num_items, void* d_arena,
+    size_t arena_size, cudaStream_t stream);
+/* After the stream has been synchronised: what the device found in item `index` of the last
+ * decode (see jpeggpu_b200_read_scan_info; synchronises `stream`). */
+enum jpeggpu_status jpeggpu_b200_batch_read_scan_info(
+    jpeggpu_b200_batch_t batch, int index, const void* d_arena, cudaStream_t stream,
+    struct jpeggpu_b200_scan_info* info);
+
 /* Host-only: parse every item with `num_threads` threads and fill info / status (lets a caller
  * size its output planes); *max_tmp_size (optional) receives the largest scratch requirement. */
 enum jpeggpu_status jpeggpu_b200_parse_batch(

@@ -34,6 +34,9 @@ API_SYMBOLS = [
     "jpeggpu_b200_set_profiling", "jpeggpu_b200_get_kernel_times", "jpeggpu_b200_kernel_name",
     "jpeggpu_b200_decode_batch", "jpeggpu_b200_parse_batch", "jpeggpu_b200_set_deferred_walk",
     "jpeggpu_b200_decode_rgbi", "jpeggpu_b200_convert_rgbi", "jpeggpu_b200_read_scan_info",
+    "jpeggpu_b200_batch_create", "jpeggpu_b200_batch_destroy", "jpeggpu_b200_batch_plan",
+    "jpeggpu_b200_batch_decode", "jpeggpu_b200_batch_read_scan_info",
+    "jpeggpu_b200_batch_set_host_arena",
 ]
 
 MAX_KERNELS = 16
@@ -126,6 +129,14 @@ def load_library(path=None):
     L.jpeggpu_b200_set_profiling.argtypes = [dec, C.c_int]
     L.jpeggpu_b200_set_deferred_walk.argtypes = [dec, C.c_int]
     L.jpeggpu_b200_read_scan_info.argtypes = [dec, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(ScanInfo)]
+    L.jpeggpu_b200_batch_create.argtypes = [C.POINTER(C.c_void_p)]
+    L.jpeggpu_b200_batch_destroy.argtypes = [C.c_void_p]
+    L.jpeggpu_b200_batch_set_host_arena.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    L.jpeggpu_b200_batch_plan.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_size_t)]
+    L.jpeggpu_b200_batch_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_size_t,
+                                            C.c_void_p]
+    L.jpeggpu_b200_batch_read_scan_info.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.POINTER(ScanInfo)]
     L.jpeggpu_b200_get_kernel_times.argtypes = [dec, C.POINTER(C.c_float * MAX_KERNELS),
                                                 C.POINTER(C.c_int * MAX_KERNELS)]
     L.jpeggpu_b200_kernel_name.restype = C.c_char_p

@@ -113,3 +113,60 @@ class BatchDecoder:
     def synchronize(self):
         for s in self.streams:
             s.synchronize()
+
+
+class FusedBatch:
+    """One jpeggpu_b200_batch_t (include/jpeggpu_b200.h "fused batches"): K images per kernel
+    launch.  plan() is host-only and returns the device arena size; decode() enqueues one upload of
+    descriptors + tables, one memset, the file bytes (one copy when the files are contiguous in
+    host memory) and five kernel launches on the caller's stream."""
+
+    def __init__(self, lib=None):
+        self.lib = lib or load_library()
+        self.handle = C.c_void_p()
+        st = self.lib.jpeggpu_b200_batch_create(C.byref(self.handle))
+        if st != SUCCESS:
+            raise JpegGpuError(st, "jpeggpu_b200_batch_create")
+
+    def set_host_arena(self, base, nbytes):
+        """Promise that [base, base + nbytes) is one host allocation holding the files: batches
+        whose files lie close together inside it are uploaded with a single copy."""
+        st = self.lib.jpeggpu_b200_batch_set_host_arena(self.handle, base, nbytes)
+        if st != SUCCESS:
+            raise JpegGpuError(st, "jpeggpu_b200_batch_set_host_arena")
+
+    def plan(self, items, count=None, strict=True):
+        """items: BatchItem array (or a slice made with ctypes pointer arithmetic); returns
+        (arena bytes, status of the first item the fused path cannot take)."""
+        n = len(items) if count is None else count
+        need = C.c_size_t()
+        st = self.lib.jpeggpu_b200_batch_plan(self.handle, items, n, C.byref(need))
+        if strict and st != SUCCESS:
+            raise JpegGpuError(st, "jpeggpu_b200_batch_plan")
+        return need.value, st
+
+    def decode(self, items, d_arena, arena_size, stream=0, count=None, strict=True):
+        n = len(items) if count is None else count
+        st = self.lib.jpeggpu_b200_batch_decode(self.handle, items, n, d_arena, arena_size, stream)
+        if strict and st != SUCCESS:
+            raise JpegGpuError(st, "jpeggpu_b200_batch_decode")
+        return st
+
+    def read_scan_info(self, index, d_arena, stream=0):
+        from . import ScanInfo
+        si = ScanInfo()
+        st = self.lib.jpeggpu_b200_batch_read_scan_info(self.handle, index, d_arena, stream, C.byref(si))
+        if st != SUCCESS:
+            raise JpegGpuError(st, "jpeggpu_b200_batch_read_scan_info")
+        return si
+
+    def close(self):
+        if self.handle:
+            self.lib.jpeggpu_b200_batch_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -45,6 +45,42 @@ struct ScanBufs {
     uint32_t* seg_idx;         // N
 };
 
+// ---- batched launches (jpeggpu_b200 batch API): one launch of each kernel for many images -----
+// A 2-D grid: blockIdx.y = image, blockIdx.x = CTA of that image; CTAs past the image's own count
+// leave at once.  The descriptor array lives in device memory (uploaded with the batch).
+enum BatchKernel { kBkDestuff = 0, kBkSync, kBkWrite, kBkDc, kBkIdct, kBkCount };
+struct BatchImage {
+    ScanGeom g;
+    ScanBufs b;
+    uint8_t* plane[kMaxComp]; // output planes, by scan component
+    int pitch[kMaxComp];
+    uint32_t q[kMaxComp][32]; // packed quantisers (kernels_idct.cu pack_quantisers)
+    uint32_t ctas[kBkCount];  // CTAs of every kernel for this image
+    uint32_t pad[3];
+};
+struct BatchLaunch {
+    const BatchImage* d_images;
+    uint32_t count;
+    uint32_t max_ctas[kBkCount];
+    uint32_t lut_pool_words_max;    // largest LUT pool / compact LUT set of the batch: sizes the
+    uint32_t lut_compact_words_max; // dynamic shared memory of the Huffman kernels
+};
+// Fills im.ctas and im.q (host side); `write_warps` = warps per huff_write CTA for this batch.
+void batch_image_grid(BatchImage& im, const uint8_t (&q)[kMaxComp][64], int write_warps);
+int batch_write_warps(uint32_t lut_compact_words_max);
+cudaError_t launch_batch(const BatchLaunch& bl, int write_warps, cudaStream_t stream);
+// per-stage pieces of the above (one translation unit per stage)
+uint32_t destuff_tiles(const ScanGeom& g, const ScanBufs& b);
+uint32_t huff_sync_ctas(uint32_t num_subs);
+uint32_t huff_write_ctas(uint32_t num_subs, int warps);
+uint32_t dc_scan_ctas(const ScanGeom& g);
+uint32_t idct_ctas(const ScanGeom& g);
+void idct_pack_quantisers(const uint8_t (&q)[kMaxComp][64], uint32_t (&out)[kMaxComp][32]);
+cudaError_t launch_destuff_batch(const BatchLaunch& bl, cudaStream_t stream);
+cudaError_t launch_huffman_batch(const BatchLaunch& bl, int write_warps, cudaStream_t stream);
+cudaError_t launch_dc_batch(const BatchLaunch& bl, cudaStream_t stream);
+cudaError_t launch_idct_batch(const BatchLaunch& bl, cudaStream_t stream);
+
 // Optional per-kernel timing (jpeggpu_b200_set_profiling): an event is recorded on the launching
 // stream before every kernel and one after the last; off by default and absent from timed runs.
 enum KernelId {
@@ -130,11 +166,11 @@ __device__ __forceinline__ void grid_dependency_trigger()
 #endif
 
 template <class... KArgs, class... Args>
-inline cudaError_t launch_dependent(void (*kernel)(KArgs...), unsigned grid, unsigned block,
+inline cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, unsigned block,
                                     size_t smem, cudaStream_t stream, Args&&... args)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
+    cfg.gridDim = grid;
     cfg.blockDim = dim3(block);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;

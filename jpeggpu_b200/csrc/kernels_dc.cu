@@ -112,9 +112,9 @@ constexpr unsigned long long kDcValid = 1ull << 32;
 // segment and itself.  Aggregates do not depend on other tiles, so there is no chain to wait
 // on: a CTA only waits for tiles that started before it (tile numbers are handed out by an
 // atomic ticket, so "earlier tile" == "already running or finished": no deadlock).
-__global__ void __launch_bounds__(kDcTile)
-dc_scan(const ScanGeom g, int16_t* __restrict__ dc, unsigned long long* __restrict__ agg,
-        uint32_t* __restrict__ ticket)
+__device__ __forceinline__ void dc_scan_body(const ScanGeom& g, int16_t* __restrict__ dc,
+                                             unsigned long long* __restrict__ agg,
+                                             uint32_t* __restrict__ ticket)
 {
     __shared__ Dc4 warp_val[kDcTile / 32];
     __shared__ uint32_t warp_flag[kDcTile / 32];
@@ -196,14 +196,46 @@ dc_scan(const ScanGeom g, int16_t* __restrict__ dc, unsigned long long* __restri
     }
 }
 
+__global__ void __launch_bounds__(kDcTile)
+dc_scan(const ScanGeom g, int16_t* __restrict__ dc, unsigned long long* __restrict__ agg,
+        uint32_t* __restrict__ ticket)
+{
+    dc_scan_body(g, dc, agg, ticket);
+}
+
+__global__ void __launch_bounds__(kDcTile)
+dc_scan_batch(const BatchImage* __restrict__ images)
+{
+    const BatchImage& im = images[blockIdx.y];
+    if (blockIdx.x >= im.ctas[kBkDc]) return;
+    __shared__ ScanGeom g;
+    {
+        static_assert(sizeof(ScanGeom) % 4 == 0, "copied word by word");
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(&im.g);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&g);
+        for (uint32_t i = threadIdx.x; i < sizeof(ScanGeom) / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    dc_scan_body(g, im.b.dc, im.b.dc_agg, &im.b.ctrl->dc_ticket);
+}
+
 } // namespace
+
+uint32_t dc_scan_ctas(const ScanGeom& g) { return ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile; }
+
+cudaError_t launch_dc_batch(const BatchLaunch& bl, cudaStream_t stream)
+{
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(dc_scan_batch); });
+    return launch_dependent(dc_scan_batch, dim3(bl.max_ctas[kBkDc], bl.count), kDcTile, 0, stream, bl.d_images);
+}
 
 cudaError_t launch_dc(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
 {
     if (g.total_mcus == 0) return cudaSuccess;
     static PerDeviceOnce configured;
     configured.run([] { prefer_max_shared(dc_scan); });
-    const uint32_t tiles = ((uint32_t)g.total_mcus + kDcTile - 1) / kDcTile;
+    const uint32_t tiles = dc_scan_ctas(g);
     tm->mark(stream, kIdDcScan);
     return launch_dependent(dc_scan, tiles, kDcTile, 0, stream, g, b.dc, b.dc_agg, &b.ctrl->dc_ticket);
 }

@@ -36,7 +36,8 @@ struct Chunk {
 // The per-byte rule of src/decode_destuff.cu:37-44 and :64-71, plus what the reference's host
 // walk decides (src/reader.cpp:450-487): 0xff followed by anything but 0x00, RSTn or another
 // 0xff (fill) ends the scan.
-__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n,
+// lead: bytes at the front of src that precede the scan (never data; the scan starts cold).
+__device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32_t n, uint32_t lead,
                                          uint32_t base, Chunk& ck)
 {
     ck.keep = 0;
@@ -58,8 +59,8 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
         const uint32_t b = (w[i >> 2] >> (8 * (i & 3))) & 0xffu;
-        const bool in = (uint32_t)i < count;
-        const bool after_ff = prev == 0xffu;
+        const bool in = (uint32_t)i < count && base + (uint32_t)i >= lead;
+        const bool after_ff = prev == 0xffu && base + (uint32_t)i > lead;
         const bool keep = in && (after_ff ? b == 0u : b != 0xffu);
         const bool rst = in && after_ff && b >= 0xd0u && b <= 0xd7u;
         const bool end = in && after_ff && b != 0u && b != 0xffu && !rst;
@@ -247,8 +248,9 @@ __device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32
 }
 
 struct DestuffArgs {
-    const uint8_t* src;        // stuffed bytes from the start of the scan
-    uint32_t n;                // bytes available (the scan may end earlier, at its terminating marker)
+    const uint8_t* src;        // 16-byte aligned; the scan starts `lead` bytes in
+    uint32_t lead;
+    uint32_t n;                // bytes at src (the scan may end earlier, at its terminating marker)
     uint8_t* dst;              // destuffed scan
     SegDesc* segs;             // out: segment directory
     uint32_t seg_cap, sub_cap; // capacities of the directory / of dst in subsequences
@@ -259,10 +261,7 @@ struct DestuffArgs {
     uint32_t clear_words;
 };
 
-// (six CTAs per SM: every tile of a 12 MP scan is resident at once - a tile of a second wave would
-// spend the whole first wave waiting for its ticket)
-__global__ void __launch_bounds__(kDestuffThreads, 6)
-destuff_kernel(const DestuffArgs a)
+__device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_t block, const uint32_t nblocks)
 {
     __shared__ uint32_t warp_sums[kDestuffThreads / 32];
     __shared__ uint8_t stage[kDestuffTile];
@@ -276,8 +275,8 @@ destuff_kernel(const DestuffArgs a)
     // prologue (tables, zero-fill of the coefficient buffer) right away
     grid_dependency_wait();
     grid_dependency_trigger();
-    for (uint32_t i = blockIdx.x * kDestuffThreads + threadIdx.x; i < a.clear_words;
-         i += gridDim.x * kDestuffThreads)
+    for (uint32_t i = block * kDestuffThreads + threadIdx.x; i < a.clear_words;
+         i += nblocks * kDestuffThreads)
         a.clear[i] = 0u;
     if (threadIdx.x == 0) {
         s_tile = atomicAdd(a.ticket, 1u);
@@ -286,14 +285,14 @@ destuff_kernel(const DestuffArgs a)
     }
     __syncthreads();
     const uint32_t tile = s_tile;
-    if (tile >= gridDim.x) return; // the ticket was not zero on entry (decode without transfer)
+    if (tile >= nblocks) return; // the ticket was not zero on entry (decode without transfer)
     const uint32_t n = a.n;
     const uint32_t tile_begin = tile * (uint32_t)kDestuffTile;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
     const uint32_t base = tile_begin + threadIdx.x * kDestuffBytesPerThread;
     Chunk ck;
-    classify(a.src, n, base, ck);
+    classify(a.src, n, a.lead, base, ck);
     // The scan ends at its first terminating marker or, failing that, with the data: nothing at or
     // behind that position counts.
     const bool last_tile = tile_begin + (uint32_t)kDestuffTile >= n;
@@ -374,7 +373,7 @@ destuff_kernel(const DestuffArgs a)
             ScanInfo si;
             si.num_subs = min(subs, a.sub_cap);
             si.num_segments = min(incl.nclose, a.seg_cap);
-            si.scan_end = tile_begin + s_term;
+            si.scan_end = tile_begin + s_term - a.lead;
             si.status = s_flags | ((subs > a.sub_cap || incl.nclose > a.seg_cap) ? kScanOverflow : 0u);
             *a.info = si;
         }
@@ -441,17 +440,12 @@ destuff_kernel(const DestuffArgs a)
     }
 }
 
-} // namespace
-
-cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
+DestuffArgs destuff_args(const ScanGeom& g, const ScanBufs& b)
 {
-    if (g.scan_avail == 0) return cudaSuccess;
-    static PerDeviceOnce configured;
-    configured.run([] { prefer_max_shared(destuff_kernel); });
-    const uint32_t tiles = (g.scan_avail + kDestuffTile - 1) / kDestuffTile;
     DestuffArgs a;
     a.src = b.scan_bytes;
-    a.n = g.scan_avail;
+    a.lead = b.scan_lead;
+    a.n = b.scan_lead + g.scan_avail;
     a.dst = reinterpret_cast<uint8_t*>(b.destuffed);
     a.segs = b.segs;
     a.seg_cap = (uint32_t)g.num_segments;
@@ -462,6 +456,66 @@ cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     // the control block, the mailboxes and the DC flags are contiguous (planner): one clear range
     a.clear = reinterpret_cast<uint32_t*>(b.ctrl);
     a.clear_words = b.clear_words;
+    return a;
+}
+
+// (six CTAs per SM: every tile of a 12 MP scan is resident at once - a tile of a second wave would
+// spend the whole first wave waiting for its ticket)
+__global__ void __launch_bounds__(kDestuffThreads, 6)
+destuff_kernel(const DestuffArgs a)
+{
+    destuff_body(a, blockIdx.x, gridDim.x);
+}
+
+__global__ void __launch_bounds__(kDestuffThreads, 6)
+destuff_batch_kernel(const BatchImage* __restrict__ images)
+{
+    const BatchImage& im = images[blockIdx.y];
+    const uint32_t nblocks = im.ctas[kBkDestuff];
+    if (blockIdx.x >= nblocks) return;
+    __shared__ DestuffArgs a;
+    if (threadIdx.x == 0) {
+        DestuffArgs t;
+        t.src = im.b.scan_bytes;
+        t.lead = im.b.scan_lead;
+        t.n = im.b.scan_lead + im.g.scan_avail;
+        t.dst = reinterpret_cast<uint8_t*>(im.b.destuffed);
+        t.segs = im.b.segs;
+        t.seg_cap = (uint32_t)im.g.num_segments;
+        t.sub_cap = im.g.num_subs;
+        t.desc = im.b.destuff_desc;
+        t.ticket = im.b.destuff_ticket;
+        t.info = im.b.info;
+        t.clear = reinterpret_cast<uint32_t*>(im.b.ctrl);
+        t.clear_words = im.b.clear_words;
+        a = t;
+    }
+    __syncthreads();
+    destuff_body(a, blockIdx.x, nblocks);
+}
+
+} // namespace
+
+uint32_t destuff_tiles(const ScanGeom& g, const ScanBufs& b)
+{
+    return (b.scan_lead + g.scan_avail + kDestuffTile - 1) / kDestuffTile;
+}
+
+cudaError_t launch_destuff_batch(const BatchLaunch& bl, cudaStream_t stream)
+{
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(destuff_batch_kernel); });
+    destuff_batch_kernel<<<dim3(bl.max_ctas[kBkDestuff], bl.count), kDestuffThreads, 0, stream>>>(bl.d_images);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
+{
+    if (g.scan_avail == 0) return cudaSuccess;
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(destuff_kernel); });
+    const uint32_t tiles = destuff_tiles(g, b);
+    const DestuffArgs a = destuff_args(g, b);
     tm->mark(stream, kIdDestuff);
     destuff_kernel<<<tiles, kDestuffThreads, 0, stream>>>(a);
     return cudaGetLastError();

@@ -357,12 +357,12 @@ struct GlobalMem {
     __device__ __forceinline__ void put(uint32_t, int) const {}
 };
 
-__device__ __forceinline__ void zero_fill(void* base, size_t bytes)
+__device__ __forceinline__ void zero_fill(void* base, size_t bytes, uint32_t block, uint32_t nblocks)
 {
     // bytes is a multiple of 16 (planner); every CTA clears one slice
     const size_t vecs = bytes / 16;
-    const size_t per_cta = (vecs + gridDim.x - 1) / gridDim.x;
-    const size_t begin = per_cta * blockIdx.x;
+    const size_t per_cta = (vecs + nblocks - 1) / nblocks;
+    const size_t begin = per_cta * block;
     const size_t end = begin + per_cta < vecs ? begin + per_cta : vecs;
     uint4* p = reinterpret_cast<uint4*>(base);
     const uint4 z = make_uint4(0u, 0u, 0u, 0u);
@@ -502,17 +502,17 @@ __device__ __forceinline__ void verify_and_repair(const ScanBufs& b, uint32_t N,
     if (threadIdx.x == 0) b.ctrl->link_rounds = rounds;
 }
 
-__global__ void __launch_bounds__(kHuffThreads, 1)
-huff_sync(const ScanGeom g, const ScanBufs b)
+__device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs& b, const uint32_t block,
+                                               const uint32_t nblocks)
 {
     __shared__ SharedTables st;
     __shared__ uint32_t s_last;
     const unsigned long long t0 = now_ns();
-    const long long win_sub0 = (long long)blockIdx.x * kSyncUseful - kOverlapSubs;
+    const long long win_sub0 = (long long)block * kSyncUseful - kOverlapSubs;
     // before the destuff kernel is done: tables into shared memory, zero-fill of the output
     stage_tables<false>(g, b, st, kSyncWinWords);
-    zero_fill(b.coef, b.coef_bytes);
-    zero_fill(b.dc, b.dc_bytes);
+    zero_fill(b.coef, b.coef_bytes, block, nblocks);
+    zero_fill(b.dc, b.dc_bytes, block, nblocks);
     grid_dependency_wait();
     grid_dependency_trigger();
     // the totals of the scan come from the destuff kernel (the grid was sized from upper bounds)
@@ -522,7 +522,7 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     const unsigned long long t1 = now_ns();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t chunk = blockIdx.x * kSyncWarps + warp;
+    const uint32_t chunk = block * kSyncWarps + warp;
     if (chunk * (uint32_t)kChunkSubs < num_subs) // warp-uniform
         sync_chunk(b, num_subs, num_segments, st, win_sub0, chunk, lane);
     const unsigned long long t2 = now_ns();
@@ -530,7 +530,7 @@ huff_sync(const ScanGeom g, const ScanBufs b)
     // last CTA out verifies the records of the whole scan
     __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) s_last = atomicAdd(&b.ctrl->sync_done, 1u) == gridDim.x - 1u ? 1u : 0u;
+    if (threadIdx.x == 0) s_last = atomicAdd(&b.ctrl->sync_done, 1u) == nblocks - 1u ? 1u : 0u;
     __syncthreads();
     if (s_last) {
         __threadfence();
@@ -545,6 +545,41 @@ huff_sync(const ScanGeom g, const ScanBufs b)
         atomicMax(&b.ctrl->sync_iter_ns, (uint32_t)(t2 - t1));
         if (s_last) b.ctrl->link_verify_ns = (uint32_t)(now_ns() - t2);
     }
+}
+
+// The scan descriptors of a batched launch travel through shared memory (by-value kernel
+// parameters live in the constant bank; a descriptor in global memory would be re-read at every use).
+struct __align__(16) BatchScan {
+    ScanGeom g;
+    ScanBufs b;
+};
+__device__ __forceinline__ void load_batch_scan(BatchScan& dst, const BatchImage& im)
+{
+    static_assert(sizeof(ScanGeom) % 4 == 0 && sizeof(ScanBufs) % 4 == 0, "copied word by word");
+    const uint32_t* sg = reinterpret_cast<const uint32_t*>(&im.g);
+    const uint32_t* sb = reinterpret_cast<const uint32_t*>(&im.b);
+    uint32_t* dg = reinterpret_cast<uint32_t*>(&dst.g);
+    uint32_t* db = reinterpret_cast<uint32_t*>(&dst.b);
+    for (uint32_t i = threadIdx.x; i < sizeof(ScanGeom) / 4; i += blockDim.x) dg[i] = __ldg(sg + i);
+    for (uint32_t i = threadIdx.x; i < sizeof(ScanBufs) / 4; i += blockDim.x) db[i] = __ldg(sb + i);
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kHuffThreads, 1)
+huff_sync(const ScanGeom g, const ScanBufs b)
+{
+    huff_sync_body(g, b, blockIdx.x, gridDim.x);
+}
+
+__global__ void __launch_bounds__(kHuffThreads, 1)
+huff_sync_batch(const BatchImage* __restrict__ images)
+{
+    const BatchImage& im = images[blockIdx.y];
+    const uint32_t nblocks = im.ctas[kBkSync];
+    if (blockIdx.x >= nblocks) return;
+    __shared__ BatchScan sc;
+    load_batch_scan(sc, im);
+    huff_sync_body(sc.g, sc.b, blockIdx.x, nblocks);
 }
 
 __device__ __forceinline__ unsigned long long ld_acquire64(const unsigned long long* p)
@@ -637,8 +672,7 @@ __device__ __forceinline__ uint32_t cta_slot_prefix(uint32_t cta, uint32_t n, bo
     return head ? 0u : incl - n;
 }
 
-__global__ void __launch_bounds__(kWriteThreads, 1)
-huff_write(const ScanGeom g, const ScanBufs b)
+__device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBufs& b)
 {
     __shared__ SharedTables st;
     __shared__ uint32_t s_cta;
@@ -758,35 +792,88 @@ huff_write(const ScanGeom g, const ScanBufs b)
     }
 }
 
+__global__ void __launch_bounds__(kWriteThreads, 1)
+huff_write(const ScanGeom g, const ScanBufs b)
+{
+    huff_write_body(g, b);
+}
+
+__global__ void __launch_bounds__(kWriteThreads, 1)
+huff_write_batch(const BatchImage* __restrict__ images)
+{
+    const BatchImage& im = images[blockIdx.y];
+    if (blockIdx.x >= im.ctas[kBkWrite]) return;
+    __shared__ BatchScan sc;
+    load_batch_scan(sc, im);
+    huff_write_body(sc.g, sc.b);
+}
+
 } // namespace
 
-cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
+namespace {
+size_t write_smem_bytes(int warps, size_t lut_write_bytes)
 {
-    if (g.num_subs == 0) return cudaSuccess;
-    const size_t lut_bytes = (size_t)((g.lut_pool_words + 3) / 4) * 16;
-    const size_t lut_write_bytes = (size_t)((g.lut_compact_words + 3) / 4) * 16;
+    return (size_t)(warps * kSubsPerWarp * kSubWords + kWinMargin) * 4 + lut_write_bytes + (size_t)warps * kWarpSmem;
+}
+void configure_huffman()
+{
     static PerDeviceOnce configured;
     configured.run([] {
         const int max_smem = 226 * 1024; // 227 KiB per CTA minus the static part
         prefer_max_shared(huff_sync, max_smem);
         prefer_max_shared(huff_write, max_smem);
+        prefer_max_shared(huff_sync_batch, max_smem);
+        prefer_max_shared(huff_write_batch, max_smem);
     });
-    const uint32_t chunks = (g.num_subs + kChunkSubs - 1) / kChunkSubs;
-    tm->mark(stream, kIdSync);
-    JB2_LAUNCH(launch_dependent(huff_sync, (chunks + kSyncWarps - 1) / kSyncWarps, kHuffThreads,
-                                kSyncWinWords * 4 + lut_bytes, stream, g, b));
-    // as many warps per CTA as the shared memory left by the LUT pool allows (each warp needs
-    // its coefficient lists)
+}
+} // namespace
+
+// As many warps per huff_write CTA as the shared memory left by the LUTs allows (each warp needs
+// its coefficient lists).
+int batch_write_warps(uint32_t lut_compact_words_max)
+{
+    const size_t lut_write_bytes = (size_t)((lut_compact_words_max + 3) / 4) * 16;
     const size_t budget = 225 * 1024;
     int warps = kWriteThreads / 32;
-    auto write_smem = [&](int w) {
-        return (size_t)(w * kSubsPerWarp * kSubWords + kWinMargin) * 4 + lut_write_bytes + (size_t)w * kWarpSmem;
-    };
-    while (warps > 1 && write_smem(warps) + 1024 > budget) --warps;
+    while (warps > 1 && write_smem_bytes(warps, lut_write_bytes) + 1024 > budget) --warps;
+    return warps;
+}
+
+uint32_t huff_sync_ctas(uint32_t num_subs)
+{
+    const uint32_t chunks = (num_subs + kChunkSubs - 1) / kChunkSubs;
+    return (chunks + kSyncWarps - 1) / kSyncWarps;
+}
+uint32_t huff_write_ctas(uint32_t num_subs, int warps)
+{
     const uint32_t subs_per_cta = (uint32_t)warps * (uint32_t)kSubsPerWarp;
+    return (num_subs + subs_per_cta - 1) / subs_per_cta;
+}
+
+cudaError_t launch_huffman_batch(const BatchLaunch& bl, int write_warps, cudaStream_t stream)
+{
+    configure_huffman();
+    const size_t lut_bytes = (size_t)((bl.lut_pool_words_max + 3) / 4) * 16;
+    const size_t lut_write_bytes = (size_t)((bl.lut_compact_words_max + 3) / 4) * 16;
+    JB2_LAUNCH(launch_dependent(huff_sync_batch, dim3(bl.max_ctas[kBkSync], bl.count), kHuffThreads,
+                                kSyncWinWords * 4 + lut_bytes, stream, bl.d_images));
+    return launch_dependent(huff_write_batch, dim3(bl.max_ctas[kBkWrite], bl.count), write_warps * 32,
+                            write_smem_bytes(write_warps, lut_write_bytes), stream, bl.d_images);
+}
+
+cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t stream, StageTimer* tm)
+{
+    if (g.num_subs == 0) return cudaSuccess;
+    configure_huffman();
+    const size_t lut_bytes = (size_t)((g.lut_pool_words + 3) / 4) * 16;
+    const size_t lut_write_bytes = (size_t)((g.lut_compact_words + 3) / 4) * 16;
+    tm->mark(stream, kIdSync);
+    JB2_LAUNCH(launch_dependent(huff_sync, huff_sync_ctas(g.num_subs), kHuffThreads,
+                                kSyncWinWords * 4 + lut_bytes, stream, g, b));
+    const int warps = batch_write_warps(g.lut_compact_words);
     tm->mark(stream, kIdWrite);
-    return launch_dependent(huff_write, (g.num_subs + subs_per_cta - 1) / subs_per_cta, warps * 32,
-                            write_smem(warps), stream, g, b);
+    return launch_dependent(huff_write, huff_write_ctas(g.num_subs, warps), warps * 32,
+                            write_smem_bytes(warps, lut_write_bytes), stream, g, b);
 }
 
 } // namespace jb2

@@ -14,6 +14,8 @@
 // Algorithmic bytes: 2*C coefficient bytes read + P sample bytes written.
 #include "kernels.hpp"
 
+#include <cstring>
+
 namespace jb2 {
 namespace {
 
@@ -280,12 +282,11 @@ __device__ __forceinline__ void store_unit(const ScanGeom& g, const int16_t* __r
     }
 }
 
-__global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
-idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
-            const PlaneDst out, const QPairs q)
+// s_q: the packed quantisers in shared memory (staged by the caller, before the barrier below)
+__device__ __forceinline__ void idct_body(const ScanGeom& g, const int16_t* __restrict__ coef,
+                                          const int16_t* __restrict__ dc, const PlaneDst& out,
+                                          uint32_t (*s_q)[32], const uint32_t block)
 {
-    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
-    stage_quantisers(s_q, q);
     grid_dependency_wait();
     grid_dependency_trigger();
     __syncthreads();
@@ -294,7 +295,7 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
     // the cp.async fetch of the next one is in flight (double-buffered tile per warp).
     __shared__ uint4 s_tile[kIdctThreads / 32][2][256];
     uint4* const tiles = s_tile[threadIdx.x >> 5][0];
-    const uint32_t first = blockIdx.x * (uint32_t)(kIdctThreads * kIdctUnits) + threadIdx.x;
+    const uint32_t first = block * (uint32_t)(kIdctThreads * kIdctUnits) + threadIdx.x;
     DuPos pos, nxt;
     pos.comp = nxt.comp = 0;
     pos.du = nxt.du = 0;
@@ -319,9 +320,40 @@ idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* _
     }
 #else
     DuPos pos;
-    if (!locate(g, blockIdx.x * kIdctThreads + threadIdx.x, pos)) return;
+    if (!locate(g, block * kIdctThreads + threadIdx.x, pos)) return;
     store_unit(g, coef, dc, out, pos, s_q[pos.comp], nullptr);
 #endif
+}
+
+__global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
+idct_kernel(const ScanGeom g, const int16_t* __restrict__ coef, const int16_t* __restrict__ dc,
+            const PlaneDst out, const QPairs q)
+{
+    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
+    stage_quantisers(s_q, q);
+    idct_body(g, coef, dc, out, s_q, blockIdx.x);
+}
+
+__global__ void __launch_bounds__(kIdctThreads, JB2_IDCT_MIN_CTAS)
+idct_batch_kernel(const BatchImage* __restrict__ images)
+{
+    const BatchImage& im = images[blockIdx.y];
+    if (blockIdx.x >= im.ctas[kBkIdct]) return;
+    __shared__ __align__(16) uint32_t s_q[kMaxComp][32];
+    __shared__ ScanGeom g;
+    __shared__ PlaneDst out;
+    {
+        static_assert(sizeof(ScanGeom) % 4 == 0, "copied word by word");
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(&im.g);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(&g);
+        for (uint32_t i = threadIdx.x; i < sizeof(ScanGeom) / 4; i += blockDim.x) dst[i] = __ldg(src + i);
+        for (int i = threadIdx.x; i < kMaxComp * 32; i += blockDim.x) s_q[i >> 5][i & 31] = __ldg(&im.q[i >> 5][i & 31]);
+        if (threadIdx.x < kMaxComp) {
+            out.ptr[threadIdx.x] = im.plane[threadIdx.x];
+            out.pitch[threadIdx.x] = im.pitch[threadIdx.x];
+        }
+    }
+    idct_body(g, im.b.coef, im.b.dc, out, s_q, blockIdx.x);
 }
 
 // Stand-alone transpose: coded order (zig-zag inside a DU) -> planar raster int16 (row length =
@@ -624,6 +656,47 @@ ycc_to_rgbi_kernel(const PlanarIn in, const RgbDst out)
 
 } // namespace
 
+uint32_t idct_ctas(const ScanGeom& g)
+{
+    const uint32_t per_cta = (uint32_t)(kIdctThreads * kIdctUnits);
+    return (g.du_prefix[g.num_comp] + per_cta - 1) / per_cta;
+}
+
+void idct_pack_quantisers(const uint8_t (&q)[kMaxComp][64], uint32_t (&out)[kMaxComp][32])
+{
+    const QPairs p = pack_quantisers(q);
+    memcpy(out, p.w, sizeof(p.w));
+}
+
+cudaError_t launch_idct_batch(const BatchLaunch& bl, cudaStream_t stream)
+{
+    static PerDeviceOnce configured;
+    configured.run([] { prefer_max_shared(idct_batch_kernel); });
+    return launch_dependent(idct_batch_kernel, dim3(bl.max_ctas[kBkIdct], bl.count), kIdctThreads, 0, stream,
+                            bl.d_images);
+}
+
+// Host side of a batched launch: the CTAs every kernel needs for one image, its packed quantisers.
+void batch_image_grid(BatchImage& im, const uint8_t (&q)[kMaxComp][64], int write_warps)
+{
+    im.ctas[kBkDestuff] = destuff_tiles(im.g, im.b);
+    im.ctas[kBkSync] = huff_sync_ctas(im.g.num_subs);
+    im.ctas[kBkWrite] = huff_write_ctas(im.g.num_subs, write_warps);
+    im.ctas[kBkDc] = dc_scan_ctas(im.g);
+    im.ctas[kBkIdct] = idct_ctas(im.g);
+    idct_pack_quantisers(q, im.q);
+}
+
+// destuff -> huff_sync -> huff_write -> dc_scan -> idct for every image of the batch: five launches.
+cudaError_t launch_batch(const BatchLaunch& bl, int write_warps, cudaStream_t stream)
+{
+    if (bl.count == 0) return cudaSuccess;
+    JB2_LAUNCH(launch_destuff_batch(bl, stream));
+    JB2_LAUNCH(launch_huffman_batch(bl, write_warps, stream));
+    JB2_LAUNCH(launch_dc_batch(bl, stream));
+    return launch_idct_batch(bl, stream);
+}
+
 cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& out,
                         cudaStream_t stream, StageTimer* tm)
 {
@@ -637,8 +710,7 @@ cudaError_t launch_idct(const ScanGeom& g, const ScanBufs& b, const OutPlanes& o
         dst.ptr[a] = out.ptr[a];
         dst.pitch[a] = out.pitch[a];
     }
-    const uint32_t per_cta = (uint32_t)(kIdctThreads * kIdctUnits);
-    return launch_dependent(idct_kernel, (total + per_cta - 1) / per_cta, kIdctThreads, 0,
+    return launch_dependent(idct_kernel, idct_ctas(g), kIdctThreads, 0,
                             stream, g, b.coef, b.dc, dst, pack_quantisers(out.q));
 }
 

@@ -692,8 +692,8 @@ jpeggpu_status read_sos(Cursor& cur, ImagePlan& plan, ParseState& st, const Logg
     ++plan.num_scans;
     // Deferred walk (parser.hpp): the one scan of the file, no DRI, EOI at the very end.
     const size_t left = cur.left();
-    if (walk == kWalkDevice && plan.num_scans == 1 && ns == plan.num_comp && left >= kDeferMinBytes &&
-        left < (1ull << 31) - 4096) {
+    if ((walk == kWalkDevice || walk == kWalkDeviceAlways) && plan.num_scans == 1 && ns == plan.num_comp &&
+        left >= (walk == kWalkDevice ? kDeferMinBytes : 2) && left < (1ull << 31) - 4096) {
         // the scan is planned as if it filled the rest of the file; T.81 E.1.4: ceil(MCUs / Ri)
         // restart segments (+ slack for stray markers in damaged files)
         sp.begin = (size_t)(cur.p - cur.begin);

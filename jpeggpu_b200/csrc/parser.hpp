@@ -82,7 +82,8 @@ struct Logger {
 // walk: kWalkEager, kWalkDeferred (rules above) or kWalkDevice: every file whose first scan holds
 // all frame components stops at the scan header, whatever follows; the scan is taken to reach to
 // the end of the file and the device locates its real end (the bytes behind it are uploaded too).
-enum WalkMode { kWalkEager = 0, kWalkDeferred = 1, kWalkDevice = 2 };
+// kWalkDeviceAlways: as kWalkDevice without the 64 KiB floor (batched decode: no per-file host walk).
+enum WalkMode { kWalkEager = 0, kWalkDeferred = 1, kWalkDevice = 2, kWalkDeviceAlways = 3 };
 jpeggpu_status parse_jpeg(const uint8_t* data, size_t size, ImagePlan& plan, const Logger& log,
                           int walk = kWalkEager);
 

@@ -74,7 +74,8 @@ inline bool apply_lut_set(const LutSet& ls, ScanGeom& g)
 
 inline uint32_t destuff_desc_words(const ScanGeom& g)
 {
-    const size_t tiles = ((size_t)g.scan_avail + kDestuffTile - 1) / kDestuffTile;
+    // (+ 15: a batched upload may start up to 15 bytes before the scan, kernels.hpp scan_lead)
+    const size_t tiles = ((size_t)g.scan_avail + 15 + kDestuffTile - 1) / kDestuffTile;
     return (uint32_t)(4 * tiles + 4); // two 64-bit words per tile + the ticket
 }
 

@@ -19,13 +19,19 @@ static inline uint32_t synth_hash(uint32_t x)
     return x;
 }
 
+/* hc = hash(hash(seed + octave * 0x9e3779b9) + channel): the part that does not depend on the cell */
+static inline float synth_lattice_hc(uint32_t hc, int cx, int cy)
+{
+    uint32_t h = synth_hash(hc + (uint32_t)cx);
+    h = synth_hash(h + (uint32_t)cy);
+    return (float)(h & 0xffff) / 65535.0f - 0.5f;
+}
+
 static inline float synth_lattice(uint32_t seed, int octave, int channel, int cx, int cy)
 {
     uint32_t h = synth_hash(seed + (uint32_t)octave * 0x9e3779b9u);
     h = synth_hash(h + (uint32_t)channel);
-    h = synth_hash(h + (uint32_t)cx);
-    h = synth_hash(h + (uint32_t)cy);
-    return (float)(h & 0xffff) / 65535.0f - 0.5f;
+    return synth_lattice_hc(h, cx, cy);
 }
 
 /* amp_scale multiplies all amplitudes (1.0 = the recipe). Returns malloc'ed w*h*3 bytes. */
@@ -43,15 +49,23 @@ static uint8_t* synth_image_rgb(int w, int h, uint32_t seed, float amp_scale)
             int cy = y / cell;
             float fy = (float)(y % cell) / (float)cell;
             for (int ch = 0; ch < 3; ++ch) {
+                const uint32_t hc = synth_hash(synth_hash(seed + (uint32_t)o * 0x9e3779b9u) + (uint32_t)ch);
+                if (cell == 1) {
+                    /* both interpolation weights are zero: the sum below reduces to the lattice
+                     * value itself, bit for bit (x + (y - x) * 0.0f == x for finite x, y) */
+                    for (int x = 0; x < w; ++x)
+                        row[x * 3 + ch] += amps[o] * amp_scale * synth_lattice_hc(hc, x, cy);
+                    continue;
+                }
                 int last_cx = -1;
                 float v00 = 0, v10 = 0, v01 = 0, v11 = 0;
                 for (int x = 0; x < w; ++x) {
                     int cx = x / cell;
                     if (cx != last_cx) {
-                        v00 = synth_lattice(seed, o, ch, cx, cy);
-                        v10 = synth_lattice(seed, o, ch, cx + 1, cy);
-                        v01 = synth_lattice(seed, o, ch, cx, cy + 1);
-                        v11 = synth_lattice(seed, o, ch, cx + 1, cy + 1);
+                        v00 = synth_lattice_hc(hc, cx, cy);
+                        v10 = synth_lattice_hc(hc, cx + 1, cy);
+                        v01 = synth_lattice_hc(hc, cx, cy + 1);
+                        v11 = synth_lattice_hc(hc, cx + 1, cy + 1);
                         last_cx = cx;
                     }
                     float fx = (float)(x % cell) / (float)cell;
