@@ -43,9 +43,21 @@ constexpr int kWinMargin = 4;                                   // words past th
 constexpr int kSyncWinWords = kSyncWinSubs * kSubWords + kWinMargin;
 constexpr int kWriteThreads = 160 * kWriteParts; // at most; kWriteParts threads per subsequence
 constexpr int kSubsPerWarp = 32 / kWriteParts;
-// non-zero coefficients one thread can meet in half a subsequence: each takes >= 2 bits, plus the
-// symbol that straddles the end
-constexpr int kListCap = kSubBits / (2 * kWriteParts) + 2;
+// Non-zero coefficients a write thread keeps in its shared-memory list.  Half a subsequence can
+// hold kSubBits / (2 * kWriteParts) + 2 of them in theory (2 bits each); real streams stay far
+// below (tools/sim/list_stats.cpp: mean 42-46, maximum 57-61 per 32 bytes on the test images), and
+// lists sized for the theoretical maximum cost 210 KB per CTA: one CTA per SM, four waves at
+// 48 MP.  A list that fills up sends the rest of its coefficients straight to global memory from
+// inside the symbol loop (fire-and-forget stores).  Measured on B200, huff_write for 12 MP /
+// IMG_6510 / 48 MP / 2 MP in us: no list 35.5 / 69.1 / 146.9 / 30.5, 16 entries 36.6 / 64.8 /
+// 144.7 / 31.1, 32 entries 37.1 / 50.8 / 131.2 / 32.6, 48 entries 38.4 / 50.3 / 134.3 / 34.5,
+// 64 entries 45.4 / 67.0 / 149.5 / 30.7, 130 entries (never overflows) 37.5 / 58 / 152 / 34:
+// the kernel sits on the scattered 2-byte stores whichever way they leave (~3 us per megapixel).
+#ifndef JB2_WRITE_LIST
+#define JB2_WRITE_LIST 32
+#endif
+constexpr int kListCap = JB2_WRITE_LIST < kSubBits / (2 * kWriteParts) + 2 ? JB2_WRITE_LIST
+                                                                         : kSubBits / (2 * kWriteParts) + 2;
 constexpr int kListStride = kListCap | 1;                          // words between the lanes' lists
 constexpr int kWarpListBytes = (32 * kListStride * 4 + 15) & ~15;
 constexpr int kWarpSmem = kWarpListBytes;                          // shared memory per write warp
@@ -303,12 +315,21 @@ struct DevMem {
 // working on one list at a time.
 struct WriteMem : DevMem {
     mutable uint32_t list_ptr; // shared address of the next entry
+    uint32_t list_limit;       // end of the list
     uint32_t slot0;            // first slot of this thread's half subsequence (segment relative)
+    int16_t* coef_seg;         // overflow: coefficient buffer / DC array at the first data unit of
+    int16_t* dc_seg;           // the restart segment
     __device__ __forceinline__ void put(uint32_t slot, int v) const
     {
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(list_ptr),
-                     "r"(((slot - slot0) << 16) | ((uint32_t)v & 0xffffu)));
-        list_ptr += 4u;
+        if (list_ptr != list_limit) {
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(list_ptr),
+                         "r"(((slot - slot0) << 16) | ((uint32_t)v & 0xffffu)));
+            list_ptr += 4u;
+        } else if ((slot & 63u) == 0) {
+            dc_seg[slot >> 6] = (int16_t)v;
+        } else {
+            coef_seg[slot] = (int16_t)v;
+        }
     }
 };
 
@@ -748,7 +769,10 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
         M.lut_addr = smem_addr(s_dyn + win_words / 4);
         M.win_addr = smem_addr(s_dyn) + (uint32_t)((int)((long long)seg.sub_off - (long long)sub0) * kSubBytes);
         M.list_ptr = list_addr;
+        M.list_limit = list_addr + (uint32_t)kListCap * 4u;
         M.slot0 = qs;
+        M.coef_seg = b.coef + (size_t)first_du * 64;
+        M.dc_seg = b.dc + first_du;
         write_part(M, seg, i, h, rec, mid, q0, q_limit);
         list_end = M.list_ptr;
     }
@@ -792,13 +816,13 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
     }
 }
 
-__global__ void __launch_bounds__(kWriteThreads, 1)
+__global__ void __launch_bounds__(kWriteThreads, 2)
 huff_write(const ScanGeom g, const ScanBufs b)
 {
     huff_write_body(g, b);
 }
 
-__global__ void __launch_bounds__(kWriteThreads, 1)
+__global__ void __launch_bounds__(kWriteThreads, 2)
 huff_write_batch(const BatchImage* __restrict__ images)
 {
     const BatchImage& im = images[blockIdx.y];
@@ -828,15 +852,21 @@ void configure_huffman()
 }
 } // namespace
 
-// As many warps per huff_write CTA as the shared memory left by the LUTs allows (each warp needs
-// its coefficient lists).
+// Warps per huff_write CTA: as many as let TWO CTAs share an SM (each warp needs its coefficient
+// lists, each CTA its own copy of the tables); with tables too large for that, as many as fit one.
 int batch_write_warps(uint32_t lut_compact_words_max)
 {
     const size_t lut_write_bytes = (size_t)((lut_compact_words_max + 3) / 4) * 16;
-    const size_t budget = 225 * 1024;
-    int warps = kWriteThreads / 32;
-    while (warps > 1 && write_smem_bytes(warps, lut_write_bytes) + 1024 > budget) --warps;
-    return warps;
+    const size_t per_sm = 228 * 1024, reserved = 1024 + 1024; // per-CTA reservation + static shared memory
+    auto fit = [&](size_t budget) {
+        int warps = kWriteThreads / 32;
+        while (warps > 0 && write_smem_bytes(warps, lut_write_bytes) + reserved > budget) --warps;
+        return warps;
+    };
+    const int two = fit(per_sm / 2);
+    if (two >= 4) return two;
+    const int one = fit(227 * 1024);
+    return one > 0 ? one : 1;
 }
 
 uint32_t huff_sync_ctas(uint32_t num_subs)

@@ -212,3 +212,44 @@ def test_deferred_and_eager_walk_agree(defer, tail):
             assert np.array_equal(t.cpu().numpy()[:, : info.sizes_x[c]], ref["pixels"][c]), (rep, c)
             assert np.array_equal(coefs[c].cpu().numpy(), ref["planes"][c]), (rep, c)
     sess.close()
+
+
+def test_write_list_overflow_path_is_bit_exact():
+    """huff_write keeps a bounded list of coefficients per thread (32 entries) and sends the
+    overflow straight to global memory.  Both paths run on ordinary images; this test shifts the
+    balance with a library built with 8-entry lists (-DJB2_WRITE_LIST=8, built here with nvcc)
+    in a subprocess, so that nearly every coefficient takes the overflow path."""
+    import os
+    import shutil
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    csrc = os.path.join(root, "jpeggpu_b200", "csrc")
+    out = os.path.join(root, "jpeggpu_b200", "lib", "variants", "lib_list8.so")
+    if not os.path.exists(out):
+        if shutil.which("nvcc") is None:
+            pytest.skip("variant library not built and nvcc not available")
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        srcs = ["kernels_destuff.cu", "kernels_huffman.cu", "kernels_dc.cu", "kernels_idct.cu",
+                "decoder.cpp", "parser.cpp", "batch.cpp"]
+        subprocess.run(["nvcc", "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a",
+                        "-Xcompiler", "-fPIC,-O3", "-I" + os.path.join(root, "include"), "-I" + csrc,
+                        "-DJB2_WRITE_LIST=8", "-shared", "-Xlinker", "-Bsymbolic", "-x", "cu",
+                        *[os.path.join(csrc, f) for f in srcs], "-lpthread", "-o", out], check=True)
+    code = (
+        "import numpy as np, inputs, oracle_bindings as ob\n"
+        "from jpeggpu_b200.torch_io import decode_file\n"
+        "for kw in (dict(w=1600, h=1200, seed=81, mode='YCbCr', subsampling=2, quality=92),\n"
+        "           dict(w=1200, h=900, seed=82, mode='YCbCr', subsampling=0, quality=100),\n"
+        "           dict(w=1280, h=720, seed=83, mode='YCbCr', subsampling=2, restart_blocks=40)):\n"
+        "    data = inputs.pillow_jpeg(**kw)\n"
+        "    ref = ob.decode(data)\n"
+        "    info, planes, coefs = decode_file(data, want_coefficients=True)\n"
+        "    for c in range(info.num_components):\n"
+        "        assert np.array_equal(coefs[c], ref['planes'][c]), (kw, c)\n"
+        "        assert np.array_equal(planes[c], ref['pixels'][c]), (kw, c)\n"
+        "print('ok')\n")
+    env = dict(os.environ, JPEGGPU_B200_LIB=out,
+               PYTHONPATH=os.pathsep.join([root, os.path.join(root, "tests"), os.path.join(root, "tools")]))
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
