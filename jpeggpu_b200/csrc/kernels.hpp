@@ -71,7 +71,7 @@ int batch_write_warps(uint32_t lut_compact_words_max);
 cudaError_t launch_batch(const BatchLaunch& bl, int write_warps, cudaStream_t stream);
 // per-stage pieces of the above (one translation unit per stage)
 uint32_t destuff_tiles(const ScanGeom& g, const ScanBufs& b);
-uint32_t huff_sync_ctas(uint32_t num_subs);
+uint32_t huff_sync_ctas(uint32_t num_subs, bool batch);
 uint32_t huff_write_ctas(uint32_t num_subs, int warps);
 uint32_t dc_scan_ctas(const ScanGeom& g);
 uint32_t idct_ctas(const ScanGeom& g);

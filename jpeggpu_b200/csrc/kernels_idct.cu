@@ -680,7 +680,7 @@ cudaError_t launch_idct_batch(const BatchLaunch& bl, cudaStream_t stream)
 void batch_image_grid(BatchImage& im, const uint8_t (&q)[kMaxComp][64], int write_warps)
 {
     im.ctas[kBkDestuff] = destuff_tiles(im.g, im.b);
-    im.ctas[kBkSync] = huff_sync_ctas(im.g.num_subs);
+    im.ctas[kBkSync] = huff_sync_ctas(im.g.num_subs, true);
     im.ctas[kBkWrite] = huff_write_ctas(im.g.num_subs, write_warps);
     im.ctas[kBkDc] = dc_scan_ctas(im.g);
     im.ctas[kBkIdct] = idct_ctas(im.g);

@@ -8,12 +8,5 @@ timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest_gpu.txt 
 tail -3 gpurun_out/${TAG}_bench_ours.err
 ( time python bench.py --impl reference --steps 50 --warmup 5 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err ) 2>&1 | grep real
 tail -3 gpurun_out/${TAG}_bench_reference.err
-python - <<'PY'
-import json,sys
-for arm in ("ours","reference"):
-    try:
-        d=json.loads(open(f"gpurun_out/%s_bench_%s.json" % ("", arm)).read())
-    except Exception as e:
-        print(arm, "no line", e); continue
-PY
+python tools/show_bench.py gpurun_out/${TAG}_bench_ours.json gpurun_out/${TAG}_bench_reference.json
 echo done
