@@ -101,6 +101,38 @@ enum jpeggpu_status jpeggpu_b200_read_scan_info(
 #define JPEGGPU_B200_SCAN_UNTERMINATED 1u /* the data ran out before a terminating marker (no EOI) */
 #define JPEGGPU_B200_SCAN_OVERFLOW 2u     /* more restart segments than the frame allows: damaged */
 
+/* Destuff kernel without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Runs the same destuff + restart-segment
+ * indexing kernel as jpeggpu_decoder_decode, but the kernel's scratch (look-back descriptors and
+ * tile ticket) lives in a static device array inside the library instead of the caller's d_tmp:
+ * the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and every GPU
+ * that loads the library holds 262 400 bytes for it until the process exits.
+ *   d_scan          device, 16-byte aligned: the entropy-coded bytes from the first byte behind the
+ *                   SOS header; bytes behind the terminating marker may follow (the kernel finds it)
+ *   scan_bytes      1 .. JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES; more -> JPEGGPU_INVALID_ARGUMENT
+ *                   and one line on stderr naming the limit
+ *   d_destuffed     device, 16-byte aligned, out: 16 * max_subsequences big-endian 32-bit words
+ *                   (destuffed byte d of the scan is byte d ^ 3); every restart segment starts on a
+ *                   64-byte subsequence and is zero padded to a whole one
+ *   d_segments      device, 16-byte aligned, out: max_segments entries
+ *   d_info          device, 16-byte aligned, out: totals; JPEGGPU_B200_SCAN_OVERFLOW in status if
+ *                   the scan needed more than max_subsequences / max_segments (what fits is written)
+ * Enqueues one memset (of the scratch) and one kernel on `stream`; the outputs are valid when the
+ * stream has reached that point.  All calls on a device share the one scratch array: calls whose
+ * GPU work can overlap (different streams without ordering between them) race and must be
+ * serialised by the caller.  Uses the device that is current in the calling thread. */
+#define JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES (64u << 20)
+struct jpeggpu_b200_segment {
+    unsigned first_subsequence; /* of the segment, in 64-byte subsequences of d_destuffed */
+    unsigned num_bytes;         /* destuffed data bytes of the segment */
+    unsigned reserved[2];
+};
+enum jpeggpu_status jpeggpu_b200_destuff_static(
+    const uint8_t* d_scan, size_t scan_bytes, uint32_t* d_destuffed, size_t max_subsequences,
+    struct jpeggpu_b200_segment* d_segments, size_t max_segments, struct jpeggpu_b200_scan_info* d_info,
+    cudaStream_t stream);
+
 /* Statistics of scan `scan` of the last parsed image; *num_scans (optional) gets the count. */
 enum jpeggpu_status jpeggpu_b200_get_scan_stats(
     jpeggpu_decoder_t decoder, int scan, struct jpeggpu_b200_scan_stats* stats, int* num_scans);

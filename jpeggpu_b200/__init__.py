@@ -36,7 +36,7 @@ API_SYMBOLS = [
     "jpeggpu_b200_decode_rgbi", "jpeggpu_b200_convert_rgbi", "jpeggpu_b200_read_scan_info",
     "jpeggpu_b200_batch_create", "jpeggpu_b200_batch_destroy", "jpeggpu_b200_batch_plan",
     "jpeggpu_b200_batch_decode", "jpeggpu_b200_batch_read_scan_info",
-    "jpeggpu_b200_batch_set_host_arena",
+    "jpeggpu_b200_batch_set_host_arena", "jpeggpu_b200_destuff_static",
 ]
 
 MAX_KERNELS = 16
@@ -70,6 +70,9 @@ class ScanInfo(C.Structure):
     """struct jpeggpu_b200_scan_info (include/jpeggpu_b200.h)"""
     _fields_ = [("num_subsequences", C.c_uint), ("num_segments", C.c_uint), ("scan_end", C.c_uint),
                 ("status", C.c_uint)]
+
+
+DESTUFF_STATIC_MAX_BYTES = 64 << 20  # JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES
 
 
 class BatchItem(C.Structure):
@@ -129,6 +132,8 @@ def load_library(path=None):
     L.jpeggpu_b200_set_profiling.argtypes = [dec, C.c_int]
     L.jpeggpu_b200_set_deferred_walk.argtypes = [dec, C.c_int]
     L.jpeggpu_b200_read_scan_info.argtypes = [dec, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(ScanInfo)]
+    L.jpeggpu_b200_destuff_static.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p,
+                                              C.c_size_t, C.c_void_p, C.c_void_p]
     L.jpeggpu_b200_batch_create.argtypes = [C.POINTER(C.c_void_p)]
     L.jpeggpu_b200_batch_destroy.argtypes = [C.c_void_p]
     L.jpeggpu_b200_batch_set_host_arena.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]

@@ -522,3 +522,110 @@ cudaError_t launch_destuff(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
 }
 
 } // namespace jb2
+
+// ---- destuff without any allocation ------------------------------------------------------------
+// jpeggpu_b200_destuff_static (include/jpeggpu_b200.h): the destuff kernel for callers that cannot
+// call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No
+// counterpart in the reference.  The look-back
+// descriptors and the tile ticket - the kernel's scratch - live in a file-scope device array of a
+// fixed size, so every GPU that loads the library holds kStaticScratchBytes until the process
+// exits.  The array's name is a host-side stand-in in host code: its device address comes from
+// cudaGetSymbolAddress, once per device with that device current.  Every call shares the array
+// (calls that overlap on the GPU race) and it keeps the last call's contents: the part a call uses
+// is cleared on the caller's stream in front of the kernel.
+#include <jpeggpu_b200.h>
+
+#include <cstdio>
+
+namespace jb2 {
+namespace {
+
+constexpr size_t kStaticMaxScanBytes = JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES;
+constexpr size_t kStaticMaxTiles = (kStaticMaxScanBytes + kDestuffTile - 1) / kDestuffTile;
+constexpr size_t kStaticHeaderWords = 32; // 256 bytes: word 0 holds the ticket
+constexpr size_t kStaticWords = kStaticHeaderWords + 2 * kStaticMaxTiles;
+constexpr size_t kStaticScratchBytes = kStaticWords * sizeof(unsigned long long); // 262 400
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) unsigned long long g_destuff_static_scratch[kStaticWords];
+
+static_assert(sizeof(jpeggpu_b200_segment) == sizeof(SegDesc), "the directory is handed out as is");
+static_assert(sizeof(jpeggpu_b200_scan_info) == sizeof(ScanInfo), "the totals are handed out as they are");
+
+__global__ void __launch_bounds__(kDestuffThreads, 6)
+destuff_static_kernel(const DestuffArgs a)
+{
+    destuff_body(a, blockIdx.x, gridDim.x);
+}
+
+std::mutex g_static_lock;
+unsigned long long* g_static_ptr[kStaticMaxDevices] = {};
+
+// Device address of the scratch array on the current device (looked up once per device).
+cudaError_t static_scratch(unsigned long long** out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> guard(g_static_lock);
+    if (!g_static_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_destuff_static_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        prefer_max_shared(destuff_static_kernel);
+        g_static_ptr[dev] = static_cast<unsigned long long*>(p);
+    }
+    *out = g_static_ptr[dev];
+    return cudaSuccess;
+}
+
+} // namespace
+} // namespace jb2
+
+extern "C" enum jpeggpu_status jpeggpu_b200_destuff_static(
+    const uint8_t* d_scan, size_t scan_bytes, uint32_t* d_destuffed, size_t max_subsequences,
+    struct jpeggpu_b200_segment* d_segments, size_t max_segments, struct jpeggpu_b200_scan_info* d_info,
+    cudaStream_t stream)
+{
+    using namespace jb2;
+    if (!d_scan || !d_destuffed || !d_segments || !d_info || scan_bytes == 0 || max_subsequences == 0 ||
+        max_segments == 0)
+        return JPEGGPU_INVALID_ARGUMENT;
+    if ((reinterpret_cast<uintptr_t>(d_scan) | reinterpret_cast<uintptr_t>(d_destuffed) |
+         reinterpret_cast<uintptr_t>(d_segments) | reinterpret_cast<uintptr_t>(d_info)) & 15u)
+        return JPEGGPU_INVALID_ARGUMENT;
+    if (scan_bytes > kStaticMaxScanBytes) {
+        std::fprintf(stderr,
+                     "jpeggpu_b200_destuff_static: %zu scan bytes exceed the %zu the static scratch is sized for "
+                     "(JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES)\n",
+                     scan_bytes, kStaticMaxScanBytes);
+        return JPEGGPU_INVALID_ARGUMENT;
+    }
+    // every destuffed byte offset must fit 32 bits
+    if (max_subsequences > 0xffffffffull / kSubBytes || max_segments > 0x1fffffffull) return JPEGGPU_INVALID_ARGUMENT;
+
+    unsigned long long* scratch = nullptr;
+    if (static_scratch(&scratch) != cudaSuccess) return JPEGGPU_INTERNAL_ERROR;
+    const uint32_t tiles = (uint32_t)((scan_bytes + kDestuffTile - 1) / kDestuffTile);
+    // ticket + the descriptors of this call's tiles start from zero
+    if (cudaMemsetAsync(scratch, 0, (kStaticHeaderWords + 2 * (size_t)tiles) * sizeof(unsigned long long), stream) !=
+        cudaSuccess)
+        return JPEGGPU_INTERNAL_ERROR;
+    DestuffArgs a;
+    a.src = d_scan;
+    a.lead = 0;
+    a.n = (uint32_t)scan_bytes;
+    a.dst = reinterpret_cast<uint8_t*>(d_destuffed);
+    a.segs = reinterpret_cast<SegDesc*>(d_segments);
+    a.seg_cap = (uint32_t)max_segments;
+    a.sub_cap = (uint32_t)max_subsequences;
+    a.desc = scratch + kStaticHeaderWords;
+    a.ticket = reinterpret_cast<uint32_t*>(scratch);
+    a.info = reinterpret_cast<ScanInfo*>(d_info);
+    a.clear = nullptr;
+    a.clear_words = 0;
+    destuff_static_kernel<<<tiles, kDestuffThreads, 0, stream>>>(a);
+    return cudaGetLastError() == cudaSuccess ? JPEGGPU_SUCCESS : JPEGGPU_INTERNAL_ERROR;
+}
