@@ -459,6 +459,22 @@ def ours_batch(rank, world, device, total_images, chunk, depth):
             "bytes": total_bytes, "matches_per_image_path": ok}
 
 
+def batch_shape(args, world):
+    """Images per fused batch and batches in flight.  Large batches amortise launches and the
+    descriptor upload; small ones shorten the fill and drain of the pipeline, which is what counts
+    when a rank has few images (measured on B200s, 4096 files: 1 GPU 128 x 3 -> 82 k images/s,
+    64 x 3 -> 81 k; 8 GPUs, 512 files per rank: 128 x 3 -> 487 k, 64 x 4 -> 554 k, 32 x 4 -> 578 k;
+    profiles/r2_k_batch_scale_8gpu.txt)."""
+    per_rank = max(1, args.batch_images // world)
+    chunk = args.batch_chunk
+    if chunk <= 0:
+        chunk = 32
+        while chunk < 128 and chunk * 16 < per_rank:
+            chunk *= 2
+    depth = args.batch_depth if args.batch_depth > 0 else (3 if chunk >= 128 else 4)
+    return chunk, depth
+
+
 def C_sizeof(t):
     import ctypes
     return ctypes.sizeof(t)
@@ -604,7 +620,8 @@ def run_ours(args):
     if args.batch_images > 0:
         del flush
         torch.cuda.empty_cache()
-        r = ours_batch(rank, world, device, args.batch_images, args.batch_chunk, args.batch_depth)
+        b_chunk, b_depth = batch_shape(args, world)
+        r = ours_batch(rank, world, device, args.batch_images, b_chunk, b_depth)
         if "seconds" in r:
             secs = max_over_ranks(r["seconds"], world)
             host_s = max_over_ranks(r["host_enqueue_seconds"], world)
@@ -614,7 +631,7 @@ def run_ours(args):
                      "workload": f"{args.batch_images} distinct stb {BATCH_W}x{BATCH_H} 4:2:0 q90 files (seeds 0..{args.batch_images - 1}), "
                                  f"pinned host memory, file i on rank i mod {world}",
                      "path": "jpeggpu_b200_batch_plan + jpeggpu_b200_batch_decode (fused: "
-                             f"{args.batch_chunk} images per kernel launch, {args.batch_depth} batches in flight per GPU)",
+                             f"{b_chunk} images per kernel launch, {b_depth} batches in flight per GPU)",
                      "timing": "wall clock, first enqueue to last stream sync, H2D of every file inside; max over ranks",
                      "host_enqueue_seconds_max_rank": round(host_s, 4),
                      "host_plan_seconds_rank0": round(r["plan_seconds"], 4),
@@ -926,8 +943,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch-images", type=int, default=4096, help="BASELINE config 5 (0 disables the leg)")
-    ap.add_argument("--batch-chunk", type=int, default=128, help="images per fused batch")
-    ap.add_argument("--batch-depth", type=int, default=3, help="fused batches in flight per GPU")
+    ap.add_argument("--batch-chunk", type=int, default=0,
+                    help="images per fused batch (0: from the images per rank, see batch_shape)")
+    ap.add_argument("--batch-depth", type=int, default=0, help="fused batches in flight per GPU (0: auto)")
     ap.add_argument("--reference-batch-images", type=int, default=1024,
                     help="images of the batch the reference arm's per-image loop decodes (bounded sample)")
     ap.add_argument("--no-configs", action="store_true", help="skip the side configurations and nvJPEG")
