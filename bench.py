@@ -223,7 +223,12 @@ def ncu_traffic(kernel):
         for r in rows:
             if r["kernel"] == kernel:
                 m = r["metrics"]
-                return int((float(m["dram__bytes_read.sum"]) + float(m["dram__bytes_write.sum"])) * 1e6)
+                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+                def as_bytes(v):
+                    num, _, unit = str(v).partition(" ")
+                    return float(num) * scale.get(unit.strip(), 1e6)
+                return int(as_bytes(m["dram__bytes_read.sum"]) + as_bytes(m["dram__bytes_write.sum"]))
     except Exception:
         pass
     return None
