@@ -242,13 +242,24 @@ struct CoefPlanes {
     int stride[kMaxComp];   // in int16 elements
 };
 
+// Diagnostic build (-DJB2_TIMELINE, tools/timeline.py): globaltimer stamps of every kernel's
+// first start / last end in front of the control block (never cleared by the kernels).
+#ifdef JB2_TIMELINE
+constexpr int kTimelineWords = 32;
+#else
+constexpr int kTimelineWords = 0;
+#endif
+
 // Control block at the front of the per-scan work area (zeroed every decode).
 struct Control {
+#ifdef JB2_TIMELINE
+    uint32_t tl[kTimelineWords];
+#endif
     uint32_t relinked;    // warp-boundary mismatches healed inside huff_sync
     uint32_t slow_repairs; // records rewritten by the sequential repair in huff_sync's last CTA
     uint32_t link_rounds;
     uint32_t link_verify_ns; // tail of the last huff_sync CTA: verification (+ repair) (diagnostics)
-    uint32_t reserved0;
+    uint32_t need_verify;    // a chunk's exit state changed after its right neighbour may have read it
     uint32_t write_stage_ns;  // slowest CTA of huff_write: staging / decode / flush (diagnostics)
     uint32_t write_decode_ns;
     uint32_t write_flush_ns;

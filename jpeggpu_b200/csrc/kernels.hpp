@@ -158,6 +158,25 @@ inline void prefer_max_shared(Kernel* k, int max_dynamic_bytes = 0)
 // the wait makes completion transitive: a prologue never runs before the grand-predecessor is
 // done.  Every thread of every kernel executes the wait.
 #if defined(__CUDACC__)
+// Timeline stamps (diagnostic build only): slot `idx` keeps the LATEST stamp, or with `first` the
+// EARLIEST one (stored inverted so that both are an atomicMax over a zeroed word).
+#ifdef JB2_TIMELINE
+__device__ __forceinline__ void tl_stamp(Control* c, int idx, bool first)
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    const uint32_t v = (uint32_t)t;
+    atomicMax(&c->tl[idx], first ? ~v : v);
+}
+#define JB2_TL(c, idx, first)                               \
+    do {                                                    \
+        if (threadIdx.x == 0 && (c)) tl_stamp((c), (idx), (first)); \
+    } while (0)
+#else
+#define JB2_TL(c, idx, first) \
+    do {                      \
+    } while (0)
+#endif
 __device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void grid_dependency_trigger()
 {

@@ -16,6 +16,8 @@
 // Algorithmic bytes: 4 per DU (read + write one int16); touched sectors are 32 B each.
 #include "kernels.hpp"
 
+#include <cstddef>
+
 namespace jb2 {
 namespace {
 
@@ -123,8 +125,13 @@ __device__ __forceinline__ void dc_scan_body(const ScanGeom& g, int16_t* __restr
     // the ticket does not depend on huff_write (the counter was cleared three kernels ago and
     // completion is transitive, kernels.hpp): take it while the predecessor is still draining
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+#ifdef JB2_TIMELINE
+    Control* const tl_ctrl = reinterpret_cast<Control*>(reinterpret_cast<char*>(ticket) - offsetof(Control, dc_ticket));
+#endif
+    JB2_TL(tl_ctrl, 10, true);
     grid_dependency_wait();
     grid_dependency_trigger();
+    JB2_TL(tl_ctrl, 11, true);
     __syncthreads();
     const uint32_t tile = s_tile;
     const uint32_t tile_mcu0 = tile * kDcTile;
@@ -172,7 +179,10 @@ __device__ __forceinline__ void dc_scan_body(const ScanGeom& g, int16_t* __restr
         carry.v[a] = 0;
         for (int w = 0; w < kDcTile / 32; ++w) carry.v[a] += s_red[w].v[a];
     }
-    if (!valid) return;
+    if (!valid) {
+        JB2_TL(tl_ctrl, 12, false);
+        return;
+    }
     // the tile carry applies only while no restart boundary has been seen inside the tile
     const bool fresh = (mcu / ri * ri) >= tile_mcu0;
     Dc4 pred; // predictor before this MCU
@@ -194,6 +204,7 @@ __device__ __forceinline__ void dc_scan_body(const ScanGeom& g, int16_t* __restr
             base[s] = (int16_t)value;
         }
     }
+    JB2_TL(tl_ctrl, 12, false);
 }
 
 __global__ void __launch_bounds__(kDcTile)

@@ -275,6 +275,7 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
     // prologue (tables, zero-fill of the coefficient buffer) right away
     grid_dependency_wait();
     grid_dependency_trigger();
+    JB2_TL(a.clear ? reinterpret_cast<Control*>(a.clear - kTimelineWords) : nullptr, 0, true);
     for (uint32_t i = block * kDestuffThreads + threadIdx.x; i < a.clear_words;
          i += nblocks * kDestuffThreads)
         a.clear[i] = 0u;
@@ -454,8 +455,8 @@ DestuffArgs destuff_args(const ScanGeom& g, const ScanBufs& b)
     a.ticket = b.destuff_ticket;
     a.info = b.info;
     // the control block, the mailboxes and the DC flags are contiguous (planner): one clear range
-    a.clear = reinterpret_cast<uint32_t*>(b.ctrl);
-    a.clear_words = b.clear_words;
+    a.clear = reinterpret_cast<uint32_t*>(b.ctrl) + kTimelineWords;
+    a.clear_words = b.clear_words - kTimelineWords;
     return a;
 }
 
@@ -465,6 +466,7 @@ __global__ void __launch_bounds__(kDestuffThreads, 6)
 destuff_kernel(const DestuffArgs a)
 {
     destuff_body(a, blockIdx.x, gridDim.x);
+    JB2_TL(reinterpret_cast<Control*>(a.clear - kTimelineWords), 1, false);
 }
 
 __global__ void __launch_bounds__(kDestuffThreads, 6)
@@ -486,8 +488,8 @@ destuff_batch_kernel(const BatchImage* __restrict__ images)
         t.desc = im.b.destuff_desc;
         t.ticket = im.b.destuff_ticket;
         t.info = im.b.info;
-        t.clear = reinterpret_cast<uint32_t*>(im.b.ctrl);
-        t.clear_words = im.b.clear_words;
+        t.clear = reinterpret_cast<uint32_t*>(im.b.ctrl) + kTimelineWords;
+        t.clear_words = im.b.clear_words - kTimelineWords;
         a = t;
     }
     __syncthreads();

@@ -45,6 +45,16 @@ constexpr int kSyncWarps = kHuffThreads / 32;
 #define JB2_SYNC_WARPS_BATCH 8
 #endif
 constexpr int kSyncWarpsBatch = JB2_SYNC_WARPS_BATCH;
+// Diagnostic knobs (tests build variants): how long a chunk waits for its left neighbour's exit
+// state, and whether the last CTA verifies the chunk boundaries even when no chunk asked for it.
+#ifndef JB2_MAILBOX_SPINS
+#define JB2_MAILBOX_SPINS (1 << 18)
+#endif
+#ifndef JB2_ALWAYS_VERIFY
+#define JB2_ALWAYS_VERIFY 0
+#endif
+constexpr int kMailboxSpins = JB2_MAILBOX_SPINS;
+constexpr bool kAlwaysVerify = JB2_ALWAYS_VERIFY != 0;
 constexpr int kWinMargin = 4;                                   // words past the last subsequence
 __host__ __device__ constexpr int sync_useful(int warps) { return warps * kChunkSubs; } // records written per CTA
 __host__ __device__ constexpr int sync_win_words(int warps)                             // words staged per CTA
@@ -464,19 +474,25 @@ __device__ __forceinline__ void sync_chunk(const ScanBufs& b, uint32_t num_subs,
     };
     iterate(0);
 
-    // mailbox: publish the exit state of the chunk's last subsequence, check the left neighbour
+    // mailbox: publish the exit state of the chunk's last subsequence, check the left neighbour.
+    // A chunk reads its left mailbox once.  The value it read is final unless the left chunk
+    // re-publishes a DIFFERENT exit state afterwards (its own entry changed and the change did not
+    // die out inside its 26 subsequences), or the wait timed out: only then can a chunk boundary
+    // disagree, and only then does the last CTA have to verify (and repair) the records.
     const uint32_t last_sub = umin(chunk_first + (uint32_t)kChunkSubs, num_subs) - 1u;
     const int last_lane = (int)(last_sub - chunk_first) + kOverlapSubs;
     volatile uint32_t* mailbox = b.chunk_state;
-    if (lane == last_lane) mailbox[chunk] = 0x80000000u | entry_x(rec);
+    const uint32_t first_exit = entry_x(rec);
+    if (lane == last_lane) mailbox[chunk] = 0x80000000u | first_exit;
     if (chunk > 0) {
         uint32_t left = 0;
         if (lane == kOverlapSubs && !head) {
-            for (int spin = 0; spin < (1 << 18); ++spin) {
+            for (int spin = 0; spin < kMailboxSpins; ++spin) {
                 left = mailbox[chunk - 1];
                 if (left) break;
                 __nanosleep(100);
             }
+            if (left == 0) atomicOr(&b.ctrl->need_verify, 1u); // went on with its own guess
         }
         left = __shfl_sync(0xffffffffu, left, kOverlapSubs);
         const uint16_t assumed = (uint16_t)__shfl_sync(0xffffffffu, (uint32_t)entry, kOverlapSubs);
@@ -486,7 +502,10 @@ __device__ __forceinline__ void sync_chunk(const ScanBufs& b, uint32_t num_subs,
                 atomicAdd(&b.ctrl->relinked, 1u);
             }
             iterate(kOverlapSubs);
-            if (lane == last_lane) mailbox[chunk] = 0x80000000u | entry_x(rec);
+            if (lane == last_lane && entry_x(rec) != first_exit) {
+                mailbox[chunk] = 0x80000000u | entry_x(rec);
+                atomicOr(&b.ctrl->need_verify, 1u); // the right neighbour may hold the old value
+            }
         }
     }
     if (active && lane >= kOverlapSubs) {
@@ -543,6 +562,7 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     __shared__ SharedTables st;
     __shared__ uint32_t s_last;
     const unsigned long long t0 = now_ns();
+    JB2_TL(b.ctrl, 2, true);
     const long long win_sub0 = (long long)block * kUseful - kOverlapSubs;
     // before the destuff kernel is done: tables into shared memory, zero-fill of the output
     stage_tables<false>(g, b, st, kWinWords);
@@ -550,11 +570,14 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     zero_fill(b.dc, b.dc_bytes, block, nblocks);
     grid_dependency_wait();
     grid_dependency_trigger();
+    JB2_TL(b.ctrl, 3, true);
+    JB2_TL(b.ctrl, 4, false);
     // the totals of the scan come from the destuff kernel (the grid was sized from upper bounds)
     const uint32_t num_subs = __ldcg(&b.info->num_subs);
     const int num_segments = (int)__ldcg(&b.info->num_segments);
     stage_window(b, num_subs, win_sub0 * kSubWords, kWinWords);
     const unsigned long long t1 = now_ns();
+    JB2_TL(b.ctrl, 13, false);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t chunk = block * WARPS + warp;
@@ -567,9 +590,11 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     __syncthreads();
     if (threadIdx.x == 0) s_last = atomicAdd(&b.ctrl->sync_done, 1u) == nblocks - 1u ? 1u : 0u;
     __syncthreads();
+    JB2_TL(b.ctrl, 5, false);
     if (s_last) {
         __threadfence();
-        verify_and_repair(b, num_subs, st, kWinWords);
+        if (kAlwaysVerify || __ldcg(&b.ctrl->need_verify)) verify_and_repair(b, num_subs, st, kWinWords); // block-uniform
+        JB2_TL(b.ctrl, 14, false);
         // destuff is long done: re-arm its look-back descriptors and ticket for the next decode
         // that runs on this scratch without a new transfer (transfer uploads them as zeros)
         uint32_t* arm = reinterpret_cast<uint32_t*>(b.destuff_desc);
@@ -580,6 +605,7 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
         atomicMax(&b.ctrl->sync_iter_ns, (uint32_t)(t2 - t1));
         if (s_last) b.ctrl->link_verify_ns = (uint32_t)(now_ns() - t2);
     }
+    JB2_TL(b.ctrl, 6, false);
 }
 
 // The scan descriptors of a batched launch travel through shared memory (by-value kernel
@@ -712,6 +738,7 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
     __shared__ SharedTables st;
     __shared__ uint32_t s_cta;
     const unsigned long long t0 = now_ns();
+    JB2_TL(b.ctrl, 7, true);
     const uint32_t subs_per_cta = blockDim.x / kWriteParts;
     const int win_words = (int)(subs_per_cta * kSubWords + kWinMargin);
     // before huff_sync is done (the control block was cleared two kernels ago): ticket, tables
@@ -719,6 +746,8 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
     stage_tables<true>(g, b, st, win_words);
     grid_dependency_wait();
     grid_dependency_trigger();
+    JB2_TL(b.ctrl, 15, true);
+    JB2_TL(b.ctrl, 8, false);
     __syncthreads();
     const uint32_t num_subs = __ldcg(&b.info->num_subs);
     const uint32_t cta = s_cta;
@@ -828,6 +857,7 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
         atomicMax(&b.ctrl->write_decode_ns, (uint32_t)(t2 - t1));
         atomicMax(&b.ctrl->write_flush_ns, (uint32_t)(now_ns() - t2));
     }
+    JB2_TL(b.ctrl, 9, false);
 }
 
 __global__ void __launch_bounds__(kWriteThreads, 2)

@@ -14,7 +14,7 @@ import oracle_bindings as ob
 
 pytestmark = pytest.mark.gpu
 
-CTRL_NAMES = ["relinked", "slow_repairs", "link_rounds"]
+CTRL_NAMES = ["relinked", "slow_repairs", "link_rounds", "link_verify_ns", "need_verify"]
 
 
 def with_fill_bytes(data: bytes):
@@ -173,3 +173,23 @@ def test_truncated_file_is_flagged_by_the_device():
     top = planes[0][: 16 * 40].cpu().numpy()[:, : ref["pixels"][0].shape[1]]
     assert np.array_equal(top, ref["pixels"][0][: 16 * 40])
     sess.close()
+
+
+@pytest.mark.parametrize("which", ["stb 12 MP", "IMG_6510", "stb 48 MP", "stb 2 MP"])
+def test_sync_needs_no_repair_on_any_bench_configuration(which):
+    """BASELINE.json's single-image configurations: the sequential repair must not run
+    (slow_repairs == 0: it is bit-exact but many times slower), and the chunks whose guess of the
+    entry state had to be replaced by the left neighbour's (relinked) stay a small share: each of
+    them costs its warp a second fix-point iteration."""
+    data = {"stb 12 MP": lambda: inputs.synth(4032, 3024, 6510), "IMG_6510": inputs.img6510,
+            "stb 48 MP": lambda: inputs.synth(8064, 6048, 48), "stb 2 MP": lambda: inputs.synth(1920, 1080, 1)}[which]()
+    if data is None:
+        pytest.skip("input file not staged")
+    info, got, segs, ctrl, recs, st = decode_and_read(data, 3)
+    chunks = (int(info[0]) + 25) // 26
+    assert ctrl["slow_repairs"] == 0 and ctrl["link_rounds"] == 0, ctrl
+    assert ctrl["relinked"] <= max(4, chunks // 4), (ctrl, chunks)
+    g, x = recs[:, 0], recs[:, 1]
+    head = (g & 0x8000) != 0
+    chained = ~head[1:]
+    assert np.array_equal(g[1:][chained] & 0x7fff, x[:-1][chained])

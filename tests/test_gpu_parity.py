@@ -214,18 +214,16 @@ def test_deferred_and_eager_walk_agree(defer, tail):
     sess.close()
 
 
-def test_write_list_overflow_path_is_bit_exact():
-    """huff_write keeps a bounded list of coefficients per thread (32 entries) and sends the
-    overflow straight to global memory.  Both paths run on ordinary images; this test shifts the
-    balance with a library built with 8-entry lists (-DJB2_WRITE_LIST=8, built here with nvcc)
-    in a subprocess, so that nearly every coefficient takes the overflow path."""
+def _run_with_variant(name, define, code):
+    """Run `code` in a subprocess against a variant of the library (jpeggpu_b200/csrc/Makefile:
+    variants; built here with nvcc if build() has not)."""
     import os
     import shutil
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     csrc = os.path.join(root, "jpeggpu_b200", "csrc")
-    out = os.path.join(root, "jpeggpu_b200", "lib", "variants", "lib_list8.so")
+    out = os.path.join(root, "jpeggpu_b200", "lib", "variants", name)
     if not os.path.exists(out):
         if shutil.which("nvcc") is None:
             pytest.skip("variant library not built and nvcc not available")
@@ -234,22 +232,58 @@ def test_write_list_overflow_path_is_bit_exact():
                 "decoder.cpp", "parser.cpp", "batch.cpp"]
         subprocess.run(["nvcc", "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a",
                         "-Xcompiler", "-fPIC,-O3", "-I" + os.path.join(root, "include"), "-I" + csrc,
-                        "-DJB2_WRITE_LIST=8", "-shared", "-Xlinker", "-Bsymbolic", "-x", "cu",
+                        define, "-shared", "-Xlinker", "-Bsymbolic", "-x", "cu",
                         *[os.path.join(csrc, f) for f in srcs], "-lpthread", "-o", out], check=True)
-    code = (
-        "import numpy as np, inputs, oracle_bindings as ob\n"
-        "from jpeggpu_b200.torch_io import decode_file\n"
-        "for kw in (dict(w=1600, h=1200, seed=81, mode='YCbCr', subsampling=2, quality=92),\n"
-        "           dict(w=1200, h=900, seed=82, mode='YCbCr', subsampling=0, quality=100),\n"
-        "           dict(w=1280, h=720, seed=83, mode='YCbCr', subsampling=2, restart_blocks=40)):\n"
-        "    data = inputs.pillow_jpeg(**kw)\n"
-        "    ref = ob.decode(data)\n"
-        "    info, planes, coefs = decode_file(data, want_coefficients=True)\n"
-        "    for c in range(info.num_components):\n"
-        "        assert np.array_equal(coefs[c], ref['planes'][c]), (kw, c)\n"
-        "        assert np.array_equal(planes[c], ref['pixels'][c]), (kw, c)\n"
-        "print('ok')\n")
     env = dict(os.environ, JPEGGPU_B200_LIB=out,
                PYTHONPATH=os.pathsep.join([root, os.path.join(root, "tests"), os.path.join(root, "tools")]))
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stderr[-2000:]
+    return r.stdout
+
+
+VARIANT_DECODES = (
+    "import numpy as np, inputs, oracle_bindings as ob\n"
+    "from jpeggpu_b200.torch_io import decode_file\n"
+    "for kw in (dict(w=1600, h=1200, seed=81, mode='YCbCr', subsampling=2, quality=92),\n"
+    "           dict(w=1200, h=900, seed=82, mode='YCbCr', subsampling=0, quality=100),\n"
+    "           dict(w=1280, h=720, seed=83, mode='YCbCr', subsampling=2, restart_blocks=40)):\n"
+    "    data = inputs.pillow_jpeg(**kw)\n"
+    "    ref = ob.decode(data)\n"
+    "    info, planes, coefs = decode_file(data, want_coefficients=True)\n"
+    "    for c in range(info.num_components):\n"
+    "        assert np.array_equal(coefs[c], ref['planes'][c]), (kw, c)\n"
+    "        assert np.array_equal(planes[c], ref['pixels'][c]), (kw, c)\n")
+
+
+def test_write_list_overflow_path_is_bit_exact():
+    """huff_write keeps a bounded list of coefficients per thread (32 entries) and sends the
+    overflow straight to global memory.  Both paths run on ordinary images; this test shifts the
+    balance with a library built with 8-entry lists (-DJB2_WRITE_LIST=8) in a subprocess, so that
+    nearly every coefficient takes the overflow path."""
+    _run_with_variant("lib_list8.so", "-DJB2_WRITE_LIST=8", VARIANT_DECODES + "print('ok')\n")
+
+
+def test_verify_and_repair_path_is_bit_exact():
+    """huff_sync's last CTA verifies (and repairs) the chunk boundaries only when a chunk asks for
+    it: its exit state changed after the right neighbour may have read it, or the wait for the
+    left neighbour timed out.  On ordinary runs nobody asks (need_verify == 0, asserted in
+    test_gpu_destuff.py).  A library whose mailbox wait gives up at once (-DJB2_MAILBOX_SPINS=1)
+    makes most chunks go on with their own guess: the verification then has real work, and the
+    repaired records must give the oracle's coefficients.  The control block must show that the
+    path ran."""
+    code = VARIANT_DECODES + (
+        "from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes\n"
+        "import torch\n"
+        "data = inputs.pillow_jpeg(w=1600, h=1200, seed=84, mode='YCbCr', subsampling=2, quality=95)\n"
+        "sess = DecodeSession('cuda:0'); sess.parse(pinned_bytes(data)); planes = sess.alloc_planes()\n"
+        "sess.transfer(); sess.decode(planes); torch.cuda.synchronize()\n"
+        "st = sess.dec.scan_stats(0)\n"
+        "ctrl = sess.read_scratch(st.off_control, 64).view(np.uint32)\n"
+        "ref = ob.decode(data)\n"
+        "for c, t in enumerate(planes):\n"
+        "    assert np.array_equal(t.cpu().numpy()[:, :ref['pixels'][c].shape[1]], ref['pixels'][c]), c\n"
+        "print('ctrl', int(ctrl[0]), int(ctrl[1]), int(ctrl[2]), int(ctrl[4]))\n"
+        "assert int(ctrl[4]) == 1, 'no chunk asked for the verification'\n"
+        "print('ok')\n")
+    out = _run_with_variant("lib_spin1.so", "-DJB2_MAILBOX_SPINS=1", code)
+    print(out)

@@ -12,7 +12,7 @@ import torch
 import gen_inputs
 from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
 
-NAMES = ["relinked", "slow_repairs", "link_rounds", "link_verify_ns", "reserved0", "write_stage_ns",
+NAMES = ["relinked", "slow_repairs", "link_rounds", "link_verify_ns", "need_verify", "write_stage_ns",
          "write_decode_ns", "write_flush_ns", "sync_stage_ns", "sync_iter_ns", "reserved1",
          "reserved2", "dc_ticket", "write_ticket", "sync_done"]
 
