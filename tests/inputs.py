@@ -60,6 +60,28 @@ def pillow_jpeg(w, h, seed, mode="YCbCr", subsampling=2, quality=85, restart_blo
 
 
 # Named inputs of the golden fixtures (tests/golden/reference_digests.json, tools/make_golden.py).
+def four_scan_6mp():
+    """BASELINE config 3 at its stated size: 3008x2000, four components, one scan each, DHT before
+    every SOS, 1x1 sampling (the one non-interleaved structure the reference decodes).
+    Written by tests/jpeg_transcode.py from the coefficient planes of Pillow's interleaved CMYK
+    file; the transcode takes ~20 s of Python, so the file is kept under data/_gen."""
+    import jpeg_transcode as jt
+    import oracle_bindings as ob
+    path = os.path.join(gen_inputs.GEN, "pil_cmyk_3008x2000_s39_four_scans.jpg")
+    if os.path.exists(path):
+        return read(path)
+    src = pillow_jpeg(w=3008, h=2000, seed=39, mode="CMYK")
+    ref = ob.decode(src)
+    assert ref["status"] == 0
+    data = jt.transcode(src, ref["planes"], [[0], [1], [2], [3]], restart_interval=0, dht_every_scan=True)
+    os.makedirs(gen_inputs.GEN, exist_ok=True)
+    tmp = path + f".tmp{os.getpid()}"
+    with open(tmp, "wb") as f:
+        f.write(data)
+    os.replace(tmp, path)
+    return data
+
+
 NAMED = {
     "IMG_6510": lambda: img6510(),
     "stb_4032x3024_s6510_q90": lambda: synth(4032, 3024, 6510, 90),
@@ -67,6 +89,11 @@ NAMED = {
     "stb_3008x2000_s2_q95": lambda: synth(3008, 2000, 2, 95),
     "stb_3001x1999_s3_q90": lambda: synth(3001, 1999, 3, 90),
     "stb_1920x1080_s1_q90": lambda: synth(1920, 1080, 1, 90),
+    # BASELINE config 4 (48 MP, one restart segment) and its harder twin: amplitudes x8 make the
+    # scan 18.3 MB, more than one sync_subsequences CTA of the reference covers
+    "pil_cmyk_3008x2000_four_scans": four_scan_6mp,
+    "stb_8064x6048_s48_q90": lambda: synth(8064, 6048, 48, 90),
+    "stb_8064x6048_s48_q90_a8": lambda: synth(8064, 6048, 48, 90, 8.0),
     "pil_422_3008x2000": lambda: pillow_jpeg(w=3008, h=2000, seed=12, mode="YCbCr", subsampling=1),
     "pil_444_1504x1000": lambda: pillow_jpeg(w=1504, h=1000, seed=11, mode="YCbCr", subsampling=0),
     "pil_gray_3008x2000": lambda: pillow_jpeg(w=3008, h=2000, seed=14, mode="L"),

@@ -16,11 +16,12 @@ def _cases():
     d = inputs.img6510()
     if d is not None:
         out.append(("IMG_6510", d))
-    for (w, h, seed, q) in [(4032, 3024, 6510, 90), (3008, 2000, 1, 90), (3008, 2000, 2, 95),
-                            (3001, 1999, 3, 90)]:
-        d = inputs.synth(w, h, seed, q)
+    # (8064x6048: BASELINE config 4; amplitude 8: its > 16 MiB twin)
+    for (w, h, seed, q, amp) in [(4032, 3024, 6510, 90, 1.0), (3008, 2000, 1, 90, 1.0), (3008, 2000, 2, 95, 1.0),
+                                 (3001, 1999, 3, 90, 1.0), (8064, 6048, 48, 90, 1.0), (8064, 6048, 48, 90, 8.0)]:
+        d = inputs.synth(w, h, seed, q, amp)
         if d is not None:
-            out.append((f"stb{w}x{h}q{q}", d))
+            out.append((f"stb{w}x{h}q{q}" + ("" if amp == 1.0 else f"a{amp:g}"), d))
     out.append(("pil422", inputs.pillow_jpeg(w=3008, h=2000, seed=12, mode="YCbCr", subsampling=1)))
     out.append(("pilgray", inputs.pillow_jpeg(w=3008, h=2000, seed=14, mode="L")))
     out.append(("pilrst", inputs.pillow_jpeg(w=1008, h=752, seed=17, mode="YCbCr", subsampling=2,

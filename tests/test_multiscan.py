@@ -68,6 +68,31 @@ def test_gpu_decodes_transcoded_file(name):
 
 
 @pytest.mark.gpu
+def test_reference_agrees_on_6mp_four_component_four_scan_file():
+    import ref_bindings as rb
+    if not rb.available():
+        pytest.skip("oracle/_ref/libjpeggpu_ref.so not built")
+    from jpeggpu_b200.torch_io import decode_file
+    data = inputs.four_scan_6mp()
+    orc = ob.decode(data)
+    assert orc["status"] == 0 and orc["info"].num_scans == 4
+    oi = orc["info"]
+    info, planes, coefs = decode_file(data, want_coefficients=True)
+    assert info.num_components == 4 and (info.sizes_x[0], info.sizes_y[0]) == (3008, 2000)
+    cw = [c.shape[1] for c in coefs]
+    ch = [c.shape[0] for c in coefs]
+    comps = [[oi.scans[s].comp_idx[a] for a in range(oi.scans[s].num_components)] for s in range(oi.num_scans)]
+    st, rinfo, rplanes, rcoefs = rb.decode_with_reference(
+        data, [oi.scans[s].num_segments for s in range(oi.num_scans)], cw, ch, comps)
+    assert st == 0, st
+    for c in range(4):
+        assert np.array_equal(rplanes[c], orc["pixels"][c]), f"oracle samples differ from reference, comp {c}"
+        assert np.array_equal(rplanes[c], planes[c]), f"product samples differ from reference, comp {c}"
+        if rcoefs is not None:
+            assert np.array_equal(rcoefs[c], coefs[c]), f"product coefficients differ from reference, comp {c}"
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", ["444_three_scans", "cmyk_four_scans"])
 def test_reference_agrees_on_non_interleaved_1x1_scans(name):
     """The reference handles non-interleaved scans only for 1x1 sampling and only when every
