@@ -150,12 +150,15 @@ __device__ __forceinline__ void publish(unsigned long long* d, const Elem& e, un
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(d + 1), "l"(w1) : "memory");
 }
 
-// Returns the flag (0: not ready or half written).
-__device__ __forceinline__ uint32_t peek_desc(const unsigned long long* d, Elem& e)
+// (one 16-byte load; it may tear, which the flags in both words reveal)
+__device__ __forceinline__ void load_desc(const unsigned long long* d, unsigned long long& w0,
+                                          unsigned long long& w1)
 {
-    unsigned long long w0, w1;
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w0) : "l"(d) : "memory");
-    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w1) : "l"(d + 1) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(d) : "memory");
+}
+// Returns the flag (0: not ready or half written).
+__device__ __forceinline__ uint32_t unpack_desc(unsigned long long w0, unsigned long long w1, Elem& e)
+{
     const uint32_t f0 = (uint32_t)(w0 >> 62), f1 = (uint32_t)(w1 >> 62);
     e.ended = (uint32_t)(w0 >> 61) & 1u;
     e.nclose = (uint32_t)(w0 >> 32) & 0x1fffffffu;
@@ -177,12 +180,16 @@ __device__ __forceinline__ Elem shfl_down_elem(const Elem& e, int d)
     return o;
 }
 
-// The combine of all tiles before `tile`: decoupled look-back by the whole CTA, thread t looks at
-// tile `tile - 1 - t` of the current window of kDestuffThreads tiles.  All tiles of an image are
-// resident at once and start together, so when a tile looks back its predecessors have published
-// aggregates but hardly any prefix: the look-back usually runs all the way to the start of the
-// scan, and a 32-wide window would make the last tile of a 12 MP scan wait for 11 round trips to
-// L2.  Called by every thread; the result is valid in every thread.
+// The combine of all tiles before `tile`: decoupled look-back by the whole CTA.  All tiles of an
+// image are resident at once and start together, so when a tile looks back its predecessors have
+// published aggregates but hardly any inclusive prefix: the look-back usually runs all the way to
+// the start of the scan.  Every thread therefore takes kLookK descriptors of a window of
+// kDestuffThreads * kLookK tiles and has all its loads in flight at once: one round trip to L2 and
+// one block-wide reduction cover 1024 tiles (every tile of a 4 MiB scan).  Thread t, element j
+// looks at distance t*kLookK + j behind `tile`: a thread's elements are consecutive tiles, so it
+// combines them itself before the warps reduce.
+// Called by every thread; the result is valid in every thread.
+constexpr int kLookK = 4;
 struct LookBackSmem {
     Elem warp_elem[kDestuffThreads / 32];
     uint32_t warp_stop[kDestuffThreads / 32];
@@ -193,34 +200,71 @@ __device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kWarps = kDestuffThreads / 32;
-    Elem carry = {0u, 0u, 0u, 0u, 0u}; // combine of the tiles between the window and `tile`
-    for (uint32_t base = 0; base < tile; base += (uint32_t)kDestuffThreads) {
-        const uint32_t t = base + threadIdx.x;
-        Elem e = {0u, 0u, 0u, 0u, 0u};
-        uint32_t flag = 2u; // threads past tile 0 stand for the (empty) prefix before the scan
-        if (t < tile) {
-            // every earlier tile is running or done (tickets); the bound only matters if the
-            // descriptors were not zero when the kernel started (decode without transfer): the
-            // decode is then garbage, but it ends
-            const unsigned long long* d = desc + 2ull * (tile - 1u - t);
-            for (int spin = 0; (flag = peek_desc(d, e)) == 0u && spin < (1 << 16); ++spin) __nanosleep(32);
-            if (flag == 0u) {
-                flag = 2u;
-                e = Elem{0u, 0u, 0u, 0u, 1u};
-            }
+    constexpr uint32_t kWindow = (uint32_t)kDestuffThreads * kLookK;
+    const Elem none = {0u, 0u, 0u, 0u, 0u};
+    Elem carry = none; // combine of the tiles between the window and `tile`
+    for (uint32_t base = 0; base < tile; base += kWindow) {
+        Elem e[kLookK];
+        uint32_t dist[kLookK];
+        uint32_t pending = 0, nearest = 0xffffffffu; // nearest distance holding an inclusive prefix
+#pragma unroll
+        for (int j = 0; j < kLookK; ++j) {
+            dist[j] = base + threadIdx.x * (uint32_t)kLookK + (uint32_t)j;
+            e[j] = none;
+            if (dist[j] < tile) pending |= 1u << j;
+            else if (dist[j] == tile) nearest = dist[j]; // the (empty) prefix before the scan
         }
-        // nearest tile with an inclusive prefix: nothing beyond it matters
-        const uint32_t has_prefix = __ballot_sync(0xffffffffu, flag == 2u);
-        if (lane == 0) sm.warp_stop[warp] = has_prefix ? (uint32_t)(warp * 32 + __ffs((int)has_prefix) - 1) : 0xffffffffu;
+        // every earlier tile is running or done (tickets); the bound only matters if the
+        // descriptors were not zero when the kernel started (decode without transfer): the
+        // decode is then garbage, but it ends
+        for (int spin = 0; pending && spin < (1 << 16); ++spin) {
+            // all loads first: a test of a loaded flag between them would serialise the round trips
+            unsigned long long w0[kLookK], w1[kLookK];
+#pragma unroll
+            for (int j = 0; j < kLookK; ++j) {
+                w0[j] = w1[j] = 0ull;
+                if ((pending >> j) & 1u) load_desc(desc + 2ull * (tile - 1u - dist[j]), w0[j], w1[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < kLookK; ++j) {
+                if (!((pending >> j) & 1u)) continue;
+                Elem got;
+                const uint32_t flag = unpack_desc(w0[j], w1[j], got);
+                if (flag == 0u) continue;
+                e[j] = got;
+                pending &= ~(1u << j);
+                if (flag == 2u) nearest = min(nearest, dist[j]);
+            }
+            if (pending) __nanosleep(32);
+        }
+        if (pending) { // gave up: end the scan here
+#pragma unroll
+            for (int j = 0; j < kLookK; ++j)
+                if ((pending >> j) & 1u) {
+                    e[j] = Elem{0u, 0u, 0u, 0u, 1u};
+                    nearest = min(nearest, dist[j]);
+                }
+        }
+        // nothing beyond the nearest inclusive prefix matters
+        nearest = __reduce_min_sync(0xffffffffu, nearest);
+        if (lane == 0) sm.warp_stop[warp] = nearest;
         __syncthreads();
         uint32_t stop = 0xffffffffu;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) stop = min(stop, sm.warp_stop[w]);
-        if (threadIdx.x > stop) e = Elem{0u, 0u, 0u, 0u, 0u};
+        uint32_t busy = 0;
+#pragma unroll
+        for (int j = 0; j < kLookK; ++j) {
+            if (dist[j] > stop) e[j] = none;
+            busy |= e[j].nclose | e[j].ended;
+        }
         Elem win;
-        if (!__syncthreads_or((int)(e.nclose | e.ended))) {
+        if (!__syncthreads_or((int)busy)) {
             // no closing in the whole window (every scan without DRI): the heads just add up
-            const uint32_t sum = __reduce_add_sync(0xffffffffu, e.head);
+            uint32_t mine = 0;
+#pragma unroll
+            for (int j = 0; j < kLookK; ++j) mine += e[j].head;
+            const uint32_t sum = __reduce_add_sync(0xffffffffu, mine);
             if (lane == 0) sm.warp_sum[warp] = sum;
             __syncthreads();
             uint32_t total = 0;
@@ -228,13 +272,18 @@ __device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32
             for (int w = 0; w < kWarps; ++w) total += sm.warp_sum[w];
             win = Elem{0u, total, 0u, 0u, 0u};
         } else {
-            // ordered tree reduction: lane l ends with E[31] o ... o E[l] (higher thread = earlier tile)
+            // ordered reduction (a higher element, lane or warp = a larger distance = an earlier
+            // tile): the thread's own elements, then a tree over the lanes: lane 0 ends with
+            // E[31] o ... o E[0]
+            Elem mine = e[0];
+#pragma unroll
+            for (int j = 1; j < kLookK; ++j) mine = combine(e[j], mine);
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
-                const Elem far = shfl_down_elem(e, d);
-                if (lane + d < 32) e = combine(far, e);
+                const Elem far = shfl_down_elem(mine, d);
+                if (lane + d < 32) mine = combine(far, mine);
             }
-            if (lane == 0) sm.warp_elem[warp] = e;
+            if (lane == 0) sm.warp_elem[warp] = mine;
             __syncthreads();
             win = sm.warp_elem[kWarps - 1];
 #pragma unroll
@@ -275,7 +324,10 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
     // prologue (tables, zero-fill of the coefficient buffer) right away
     grid_dependency_wait();
     grid_dependency_trigger();
-    JB2_TL(a.clear ? reinterpret_cast<Control*>(a.clear - kTimelineWords) : nullptr, 0, true);
+#ifdef JB2_TIMELINE
+    Control* const tl_ctrl = a.clear ? reinterpret_cast<Control*>(a.clear - kTimelineWords) : nullptr;
+#endif
+    JB2_TL(tl_ctrl, 0, true);
     for (uint32_t i = block * kDestuffThreads + threadIdx.x; i < a.clear_words;
          i += nblocks * kDestuffThreads)
         a.clear[i] = 0u;
@@ -287,6 +339,7 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
     __syncthreads();
     const uint32_t tile = s_tile;
     if (tile >= nblocks) return; // the ticket was not zero on entry (decode without transfer)
+    JB2_TL(tl_ctrl, 16, false); // latest ticket
     const uint32_t n = a.n;
     const uint32_t tile_begin = tile * (uint32_t)kDestuffTile;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -315,56 +368,70 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
     const uint32_t ex = block_exclusive_scan(__popc(ck.keep) | (__popc(ck.rst) << 16), warp_sums,
                                              tile_total);
     uint32_t pos = ex & 0xffffu, seg = ex >> 16;
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        if ((ck.keep >> i) & 1u) {
-            stage[pos] = ck.val[i];
-            seg_of[pos] = (uint16_t)seg;
-            ++pos;
-        }
-        if ((ck.rst >> i) & 1u) close_at[seg++] = pos;
-    }
     const uint32_t tile_kept = tile_total & 0xffffu;
     const bool ends_here = s_term < (uint32_t)kDestuffTile || (last_tile && s_term == n - tile_begin);
     uint32_t nclose = tile_total >> 16;
-    if (ends_here) { // the end of the scan closes the open segment
-        if (threadIdx.x == 0) close_at[nclose] = tile_kept;
-        ++nclose;
-    }
-    __syncthreads();
-
-    // subsequences of the segments closed inside the tile by closings 1 .. nclose-1, as a running
-    // sum (restart markers are rare - one per MCU row in camera files - so one warp does it)
-    if (nclose <= 1) {
-        if (threadIdx.x < 2) sub_rel[threadIdx.x] = 0u;
-        if (threadIdx.x == 0) s_inner = 0u;
-    } else if (warp == 0) {
-        uint32_t run = 0;
-        for (uint32_t i0 = 1;; i0 += 32u) {
-            const uint32_t i = i0 + (uint32_t)lane;
-            uint32_t v = i < nclose ? subs_of(close_at[i] - close_at[i - 1]) : 0u, inc = v;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
-                if (lane >= d) inc += up;
-            }
-            if (i <= nclose) sub_rel[i] = run + inc - v;
-            run += __shfl_sync(0xffffffffu, inc, 31);
-            if (i0 + 31u >= nclose) break; // the chunk held index nclose: `run` is the aggregate's `inner`
-        }
-        if (lane == 0) s_inner = run;
-    }
-    __syncthreads();
-    // aggregate, look-back, inclusive prefix
-    Elem agg;
-    agg.nclose = nclose;
-    agg.head = nclose ? close_at[0] : tile_kept;
-    agg.inner = s_inner;
-    agg.tail = nclose ? tile_kept - close_at[nclose - 1] : 0u;
-    agg.ended = ends_here ? 1u : 0u;
     unsigned long long* mine = a.desc + 2ull * tile;
-    if (threadIdx.x == 0 && tile != 0) publish(mine, agg, kFlagAgg);
+    Elem agg;
+    if (nclose == 0 && !ends_here) { // block-uniform
+        // Nothing closes inside the tile (every tile but the last of a scan without DRI, most tiles
+        // otherwise): the aggregate is the byte count, known right after the block scan.  Publish
+        // it BEFORE the bytes are staged - the tiles behind this one are waiting for it.
+        agg = Elem{0u, tile_kept, 0u, 0u, 0u};
+        if (threadIdx.x == 0 && tile != 0) publish(mine, agg, kFlagAgg);
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if ((ck.keep >> i) & 1u) stage[pos++] = ck.val[i];
+        __syncthreads();
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if ((ck.keep >> i) & 1u) {
+                stage[pos] = ck.val[i];
+                seg_of[pos] = (uint16_t)seg;
+                ++pos;
+            }
+            if ((ck.rst >> i) & 1u) close_at[seg++] = pos;
+        }
+        if (ends_here) { // the end of the scan closes the open segment
+            if (threadIdx.x == 0) close_at[nclose] = tile_kept;
+            ++nclose;
+        }
+        __syncthreads();
+
+        // subsequences of the segments closed inside the tile by closings 1 .. nclose-1, as a running
+        // sum (restart markers are rare - one per MCU row in camera files - so one warp does it)
+        if (nclose <= 1) {
+            if (threadIdx.x < 2) sub_rel[threadIdx.x] = 0u;
+            if (threadIdx.x == 0) s_inner = 0u;
+        } else if (warp == 0) {
+            uint32_t run = 0;
+            for (uint32_t i0 = 1;; i0 += 32u) {
+                const uint32_t i = i0 + (uint32_t)lane;
+                uint32_t v = i < nclose ? subs_of(close_at[i] - close_at[i - 1]) : 0u, inc = v;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
+                    if (lane >= d) inc += up;
+                }
+                if (i <= nclose) sub_rel[i] = run + inc - v;
+                run += __shfl_sync(0xffffffffu, inc, 31);
+                if (i0 + 31u >= nclose) break; // the chunk held index nclose: `run` is the aggregate's `inner`
+            }
+            if (lane == 0) s_inner = run;
+        }
+        __syncthreads();
+        agg.nclose = nclose;
+        agg.head = close_at[0];
+        agg.inner = s_inner;
+        agg.tail = tile_kept - close_at[nclose - 1];
+        agg.ended = ends_here ? 1u : 0u;
+        if (threadIdx.x == 0 && tile != 0) publish(mine, agg, kFlagAgg);
+    }
+    JB2_TL(tl_ctrl, 17, false); // latest aggregate
+    JB2_TL(tl_ctrl, 18, true);  // earliest aggregate
     const Elem before = tile ? look_back(a.desc, tile, s_look) : Elem{0u, 0u, 0u, 0u, 0u};
+    JB2_TL(tl_ctrl, 19, false); // latest look-back done
     if (threadIdx.x == 0) {
         const Elem incl = combine(before, agg);
         publish(mine, incl, kFlagPrefix);

@@ -24,8 +24,10 @@ SLOTS = {0: ("destuff first CTA past the dependency wait", True), 1: ("destuff l
          14: ("sync verify done (last CTA)", False), 6: ("sync end", False),
          7: ("write first CTA start (prologue)", True), 15: ("write first CTA past the wait", True),
          8: ("write last CTA past the wait", False), 9: ("write end", False),
+         16: ("destuff last ticket taken", False), 18: ("destuff first aggregate published", True),
+         17: ("destuff last aggregate published", False), 19: ("destuff last look-back done", False),
          10: ("dc first CTA start", True), 11: ("dc first CTA past the wait", True), 12: ("dc end", False)}
-ORDER = [0, 2, 1, 3, 4, 13, 7, 5, 14, 6, 15, 8, 10, 9, 11, 12]
+ORDER = [0, 16, 18, 17, 19, 2, 1, 3, 4, 13, 7, 5, 14, 6, 15, 8, 10, 9, 11, 12]
 
 
 def main():
