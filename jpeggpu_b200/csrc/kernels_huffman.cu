@@ -88,6 +88,42 @@ static_assert(kSubBytes <= 128, "slot offsets inside half a subsequence must fit
 static_assert(sync_win_words(kSyncWarps) % 4 == 0 && sync_win_words(kSyncWarpsBatch) % 4 == 0 && kSubWords % 4 == 0,
               "window must be uint4 sized");
 
+// Bulk staging (Blackwell/Hopper copy engine): the decode tables of huff_sync and the scan window of
+// both kernels are contiguous in global memory, so ONE cp.async.bulk each, completed on an mbarrier,
+// replaces the per-thread 16-byte load/store loops (3456 + 3620 of them per huff_sync CTA); the
+// table copy then overlaps the zero-fill of the coefficient buffer.  -DJB2_BULK_STAGE=0 restores
+// the loops.
+#ifndef JB2_BULK_STAGE
+#define JB2_BULK_STAGE 1
+#endif
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "JB2_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra JB2_DONE;\n"
+                 "bra JB2_WAIT;\n"
+                 "JB2_DONE:\n"
+                 "}" ::"r"(bar), "r"(parity)
+                 : "memory");
+}
+
 struct __align__(16) SharedTables {
     SlotRec recs[kMaxDuPerMcu]; // device handles: shared-memory byte addresses
     uint32_t tbls[kMaxDuPerMcu];
@@ -149,14 +185,23 @@ __device__ __forceinline__ void make_device_recs(const ScanGeom& g, SharedTables
 // memory than a plain table set; huff_sync takes the pool as it is.
 template <bool SINGLE>
 __device__ __forceinline__ void stage_tables(const ScanGeom& g, const ScanBufs& b, SharedTables& st,
-                                             const int WIN_WORDS)
+                                             const int WIN_WORDS, const uint32_t bar_tables = 0)
 {
     uint4* ldst = s_dyn + WIN_WORDS / 4;
     const uint32_t lut_addr = smem_addr(ldst);
     if (!SINGLE) {
         const uint32_t lut_vec = (g.lut_pool_words + 3) / 4; // pool is padded to 16 B by the planner
         const uint4* lsrc = reinterpret_cast<const uint4*>(b.lut_pool);
-        for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
+        if (JB2_BULK_STAGE) {
+            // one bulk copy, waited for in stage_window (bar_tables: 0 = none in flight)
+            if (threadIdx.x == 0) {
+                mbar_init(bar_tables, 1);
+                mbar_expect_tx(bar_tables, lut_vec * 16u);
+                bulk_g2s(lut_addr, lsrc, lut_vec * 16u, bar_tables);
+            }
+        } else {
+            for (uint32_t i = threadIdx.x; i < lut_vec; i += blockDim.x) ldst[i] = __ldg(lsrc + i);
+        }
         if (threadIdx.x == 0) {
             for (int t = 0; t < g.num_tables; ++t) st.tbase[t] = lut_addr + g.table_off[t] * 4u;
             make_device_recs(g, st, false);
@@ -198,11 +243,37 @@ __device__ __forceinline__ void stage_tables(const ScanGeom& g, const ScanBufs& 
 }
 // ...the window of the scan from the destuff kernel's output.  Ends with a barrier.
 __device__ __forceinline__ void stage_window(const ScanBufs& b, uint32_t num_subs,
-                                             long long first_word, const int WIN_WORDS)
+                                             long long first_word, const int WIN_WORDS,
+                                             const uint32_t bar_window = 0, const uint32_t bar_tables = 0)
 {
     uint32_t* win = reinterpret_cast<uint32_t*>(s_dyn);
     const long long total_words = (long long)num_subs * kSubWords;
     const uint4* src = reinterpret_cast<const uint4*>(b.destuffed);
+    if (JB2_BULK_STAGE && bar_window) {
+        // words [lo, hi) of the window exist in the scan (all multiples of 4): one bulk copy; the
+        // rest (first and last CTA of a scan only) is zero
+        long long lo_l = first_word < 0 ? -first_word : 0;
+        if (lo_l > WIN_WORDS) lo_l = WIN_WORDS;
+        long long hi_l = total_words - first_word < WIN_WORDS ? total_words - first_word : WIN_WORDS;
+        if (hi_l < lo_l) hi_l = lo_l; // a window behind the end of the scan (grids are sized from bounds)
+        const int lo = (int)lo_l, hi = (int)hi_l;
+        if (threadIdx.x == 0) {
+            mbar_init(bar_window, 1);
+            if (hi > lo) {
+                // the scan was written by the previous grid through the generic proxy
+                asm volatile("fence.proxy.async;" ::: "memory");
+                mbar_expect_tx(bar_window, (uint32_t)(hi - lo) * 4u);
+                bulk_g2s(smem_addr(win + lo), b.destuffed + first_word + lo, (uint32_t)(hi - lo) * 4u, bar_window);
+            }
+        }
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = threadIdx.x; i < lo / 4; i += blockDim.x) reinterpret_cast<uint4*>(win)[i] = z;
+        for (int i = hi / 4 + threadIdx.x; i < WIN_WORDS / 4; i += blockDim.x) reinterpret_cast<uint4*>(win)[i] = z;
+        __syncthreads(); // the barrier words are initialised
+        if (hi > lo) mbar_wait(bar_window, 0);
+        if (bar_tables) mbar_wait(bar_tables, 0);
+        return;
+    }
     for (int i = threadIdx.x; i < WIN_WORDS / 4; i += blockDim.x) {
         const long long w = first_word + 4ll * i;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
@@ -564,11 +635,14 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     constexpr int kUseful = sync_useful(WARPS), kWinWords = sync_win_words(WARPS);
     __shared__ SharedTables st;
     __shared__ uint32_t s_last;
+    __shared__ __align__(8) unsigned long long s_bar[2];
+    const uint32_t bar_tables = JB2_BULK_STAGE ? smem_addr(&s_bar[0]) : 0u;
+    const uint32_t bar_window = JB2_BULK_STAGE ? smem_addr(&s_bar[1]) : 0u;
     const unsigned long long t0 = now_ns();
     JB2_TL(b.ctrl, 2, true);
     const long long win_sub0 = (long long)block * kUseful - kOverlapSubs;
     // before the destuff kernel is done: tables into shared memory, zero-fill of the output
-    stage_tables<false>(g, b, st, kWinWords);
+    stage_tables<false>(g, b, st, kWinWords, bar_tables);
     zero_fill(b.coef, b.coef_bytes, block, nblocks);
     zero_fill(b.dc, b.dc_bytes, block, nblocks);
     grid_dependency_wait();
@@ -578,7 +652,7 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     // the totals of the scan come from the destuff kernel (the grid was sized from upper bounds)
     const uint32_t num_subs = __ldcg(&b.info->num_subs);
     const int num_segments = (int)__ldcg(&b.info->num_segments);
-    stage_window(b, num_subs, win_sub0 * kSubWords, kWinWords);
+    stage_window(b, num_subs, win_sub0 * kSubWords, kWinWords, bar_window, bar_tables);
     const unsigned long long t1 = now_ns();
     JB2_TL(b.ctrl, 13, false);
 
@@ -740,6 +814,7 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
 {
     __shared__ SharedTables st;
     __shared__ uint32_t s_cta;
+    __shared__ __align__(8) unsigned long long s_bar;
     const unsigned long long t0 = now_ns();
     JB2_TL(b.ctrl, 7, true);
     const uint32_t subs_per_cta = blockDim.x / kWriteParts;
@@ -787,7 +862,7 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
     q0 = __shfl_sync(0xffffffffu, q0, lane & ~(kWriteParts - 1)); // the sub's first thread has it
     if (h == 0 && j < num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
 
-    stage_window(b, num_subs, (long long)sub0 * kSubWords, win_words);
+    stage_window(b, num_subs, (long long)sub0 * kSubWords, win_words, JB2_BULK_STAGE ? smem_addr(&s_bar) : 0u);
     const unsigned long long t1 = now_ns();
 
     // this thread's half subsequence: placement, slot range [qs, qe)
