@@ -45,6 +45,18 @@ constexpr int kSyncWarps = kHuffThreads / 32;
 #define JB2_SYNC_WARPS_BATCH 8
 #endif
 constexpr int kSyncWarpsBatch = JB2_SYNC_WARPS_BATCH;
+// + one warp per CTA that zero-fills the CTA's slice of the coefficient buffer and of the DC array
+// (huff_write scatters the non-zero values into them).  Measured on B200, 12 MP, bench.py
+// ms_per_step: 0 = every thread fills in the prologue, in competition with the destuff kernel
+// (both done at 15-16 us, destuff alone takes 11.7) 0.1293; 1 = the extra warp fills while the
+// others iterate (they are latency bound, the store path is idle) 0.1270 / 0.1256 on a second
+// box; 2 = the extra warp fills in the prologue, at a quarter of the store rate of mode 0, and is
+// idle afterwards 0.1243 on that second box.
+#ifndef JB2_FILL_WARP
+#define JB2_FILL_WARP 2
+#endif
+constexpr int kSyncThreads = (kSyncWarps + (JB2_FILL_WARP ? 1 : 0)) * 32;
+constexpr int kSyncThreadsBatch = (kSyncWarpsBatch + (JB2_FILL_WARP ? 1 : 0)) * 32;
 // Diagnostic knobs (tests build variants): how long a chunk waits for its left neighbour's exit
 // state, and whether the last CTA verifies the chunk boundaries even when no chunk asked for it.
 #ifndef JB2_MAILBOX_SPINS
@@ -473,7 +485,9 @@ struct GlobalMem {
     __device__ __forceinline__ void put(uint32_t, int) const {}
 };
 
-__device__ __forceinline__ void zero_fill(void* base, size_t bytes, uint32_t block, uint32_t nblocks)
+// Slice `block` of `nblocks` of a buffer, cleared by `nthreads` threads of which this is `tid`.
+__device__ __forceinline__ void zero_fill(void* base, size_t bytes, uint32_t block, uint32_t nblocks,
+                                          uint32_t tid, uint32_t nthreads)
 {
     // bytes is a multiple of 16 (planner); every CTA clears one slice
     const size_t vecs = bytes / 16;
@@ -482,7 +496,7 @@ __device__ __forceinline__ void zero_fill(void* base, size_t bytes, uint32_t blo
     const size_t end = begin + per_cta < vecs ? begin + per_cta : vecs;
     uint4* p = reinterpret_cast<uint4*>(base);
     const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    for (size_t i = begin + threadIdx.x; i < end; i += blockDim.x) p[i] = z;
+    for (size_t i = begin + tid; i < end; i += nthreads) p[i] = z;
 }
 
 // The warp's share of huff_sync: fix-point iteration over its chunk, mailbox exchange with the
@@ -641,10 +655,17 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     const unsigned long long t0 = now_ns();
     JB2_TL(b.ctrl, 2, true);
     const long long win_sub0 = (long long)block * kUseful - kOverlapSubs;
-    // before the destuff kernel is done: tables into shared memory, zero-fill of the output
+    // before the destuff kernel is done: tables into shared memory
     stage_tables<false>(g, b, st, kWinWords, bar_tables);
-    zero_fill(b.coef, b.coef_bytes, block, nblocks);
-    zero_fill(b.dc, b.dc_bytes, block, nblocks);
+    if (!JB2_FILL_WARP) {
+        zero_fill(b.coef, b.coef_bytes, block, nblocks, threadIdx.x, blockDim.x);
+        zero_fill(b.dc, b.dc_bytes, block, nblocks, threadIdx.x, blockDim.x);
+    }
+    if (JB2_FILL_WARP == 2 && (threadIdx.x >> 5) == WARPS) {
+        zero_fill(b.coef, b.coef_bytes, block, nblocks, threadIdx.x & 31u, 32u);
+        zero_fill(b.dc, b.dc_bytes, block, nblocks, threadIdx.x & 31u, 32u);
+    }
+    JB2_TL(b.ctrl, 20, false); // latest prologue done
     grid_dependency_wait();
     grid_dependency_trigger();
     JB2_TL(b.ctrl, 3, true);
@@ -658,7 +679,15 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t chunk = block * WARPS + warp;
-    if (chunk * (uint32_t)kChunkSubs < num_subs) // warp-uniform
+    if (JB2_FILL_WARP == 2 && warp == WARPS) {
+    } else if (JB2_FILL_WARP && warp == WARPS) {
+        // (mode 1: the extra warp fills while the other warps iterate)
+        zero_fill(b.coef, b.coef_bytes, block, nblocks, (uint32_t)lane, 32u);
+        zero_fill(b.dc, b.dc_bytes, block, nblocks, (uint32_t)lane, 32u);
+#ifdef JB2_TIMELINE
+        if (lane == 0) tl_stamp(b.ctrl, 21, false);
+#endif
+    } else if (chunk * (uint32_t)kChunkSubs < num_subs) // warp-uniform
         sync_chunk(b, num_subs, num_segments, st, win_sub0, chunk, lane, kWinWords);
     const unsigned long long t2 = now_ns();
 
@@ -703,13 +732,13 @@ __device__ __forceinline__ void load_batch_scan(BatchScan& dst, const BatchImage
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(kHuffThreads, 1)
+__global__ void __launch_bounds__(kSyncThreads, 1)
 huff_sync(const ScanGeom g, const ScanBufs b)
 {
     huff_sync_body<kSyncWarps>(g, b, blockIdx.x, gridDim.x);
 }
 
-__global__ void __launch_bounds__(kSyncWarpsBatch * 32, 1)
+__global__ void __launch_bounds__(kSyncThreadsBatch, 1)
 huff_sync_batch(const BatchImage* __restrict__ images)
 {
     const BatchImage& im = images[blockIdx.y];
@@ -1023,7 +1052,7 @@ cudaError_t launch_huffman_batch(const BatchLaunch& bl, int write_warps, cudaStr
     configure_huffman();
     const size_t lut_bytes = (size_t)((bl.lut_pool_words_max + 3) / 4) * 16;
     const size_t lut_write_bytes = (size_t)((bl.lut_compact_words_max + 3) / 4) * 16;
-    JB2_LAUNCH(launch_dependent(huff_sync_batch, dim3(bl.max_ctas[kBkSync], bl.count), kSyncWarpsBatch * 32,
+    JB2_LAUNCH(launch_dependent(huff_sync_batch, dim3(bl.max_ctas[kBkSync], bl.count), kSyncThreadsBatch,
                                 sync_win_words(kSyncWarpsBatch) * 4 + lut_bytes, stream, bl.d_images));
     return launch_dependent(huff_write_batch, dim3(bl.max_ctas[kBkWrite], bl.count), write_warps * 32,
                             write_smem_bytes(write_warps, lut_write_bytes), stream, bl.d_images);
@@ -1036,7 +1065,7 @@ cudaError_t launch_huffman(const ScanGeom& g, const ScanBufs& b, cudaStream_t st
     const size_t lut_bytes = (size_t)((g.lut_pool_words + 3) / 4) * 16;
     const size_t lut_write_bytes = (size_t)((g.lut_compact_words + 3) / 4) * 16;
     tm->mark(stream, kIdSync);
-    JB2_LAUNCH(launch_dependent(huff_sync, huff_sync_ctas(g.num_subs, false), kHuffThreads,
+    JB2_LAUNCH(launch_dependent(huff_sync, huff_sync_ctas(g.num_subs, false), kSyncThreads,
                                 sync_win_words(kSyncWarps) * 4 + lut_bytes, stream, g, b));
     const int warps = single_write_warps(g.num_subs, g.lut_compact_words);
     tm->mark(stream, kIdWrite);

@@ -19,6 +19,8 @@ from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
 # slot -> (label, stored inverted)
 SLOTS = {0: ("destuff first CTA past the dependency wait", True), 1: ("destuff last CTA end", False),
          2: ("sync first CTA start (prologue: tables, zero-fill)", True),
+         20: ("sync last CTA done with its prologue", False),
+         21: ("sync last fill warp done (zero-fill of coefficients + DC)", False),
          3: ("sync first CTA past the wait", True), 4: ("sync last CTA past the wait", False),
          13: ("sync last window staged", False), 5: ("sync last CTA done with its chunks", False),
          14: ("sync verify done (last CTA)", False), 6: ("sync end", False),
@@ -27,7 +29,7 @@ SLOTS = {0: ("destuff first CTA past the dependency wait", True), 1: ("destuff l
          16: ("destuff last ticket taken", False), 18: ("destuff first aggregate published", True),
          17: ("destuff last aggregate published", False), 19: ("destuff last look-back done", False),
          10: ("dc first CTA start", True), 11: ("dc first CTA past the wait", True), 12: ("dc end", False)}
-ORDER = [0, 16, 18, 17, 19, 2, 1, 3, 4, 13, 7, 5, 14, 6, 15, 8, 10, 9, 11, 12]
+ORDER = [0, 16, 18, 17, 19, 2, 20, 1, 3, 4, 13, 7, 21, 5, 14, 6, 15, 8, 10, 9, 11, 12]
 
 
 def main():
