@@ -29,7 +29,7 @@ def main():
               (f"   ref dev {rv['device_ms']:.4f} e2e {rv['e2e_ms']:.4f} ms   x{rv['device_ms'] / v['device_ms']:.2f} / x{rv['e2e_ms'] / v['e2e_ms']:.2f}" if "device_ms" in rv else ""))
     b, rb = o.get("batch"), (r or {}).get("batch")
     if b:
-        print("batch:", {k: b[k] for k in b if k in ("images_per_s", "seconds", "images", "host_enqueue_seconds_max_rank", "matches_per_image_path", "unavailable")})
+        print("batch:", {k: b[k] for k in b if k in ("images_per_s", "seconds", "images", "host_busy_seconds_slowest_thread", "host_threads_per_gpu", "path", "matches_per_image_path", "unavailable")})
     if rb:
         print("ref batch:", {k: rb[k] for k in rb if k in ("images_per_s", "seconds", "images")})
     print("stages:", {k: v["ms"] for k, v in o["stages"].items()})
