@@ -52,11 +52,14 @@ constexpr int kSyncWarpsBatch = JB2_SYNC_WARPS_BATCH;
 // others iterate (they are latency bound, the store path is idle) 0.1270 / 0.1256 on a second
 // box; 2 = the extra warp fills in the prologue, at a quarter of the store rate of mode 0, and is
 // idle afterwards 0.1243 on that second box.
+// When the coefficient buffer does not fit the L2 cache the writers clear their own stretches
+// instead (ScanBufs::fill_in_write, huff_write_body) and the extra warp has nothing to do.
 #ifndef JB2_FILL_WARP
 #define JB2_FILL_WARP 2
 #endif
-constexpr int kSyncThreads = (kSyncWarps + (JB2_FILL_WARP ? 1 : 0)) * 32;
-constexpr int kSyncThreadsBatch = (kSyncWarpsBatch + (JB2_FILL_WARP ? 1 : 0)) * 32;
+constexpr int kFillWarps = (JB2_FILL_WARP == 1 || JB2_FILL_WARP == 2) ? 1 : 0;
+constexpr int kSyncThreads = (kSyncWarps + kFillWarps) * 32;
+constexpr int kSyncThreadsBatch = (kSyncWarpsBatch + kFillWarps) * 32;
 // Diagnostic knobs (tests build variants): how long a chunk waits for its left neighbour's exit
 // state, and whether the last CTA verifies the chunk boundaries even when no chunk asked for it.
 #ifndef JB2_MAILBOX_SPINS
@@ -657,11 +660,11 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     const long long win_sub0 = (long long)block * kUseful - kOverlapSubs;
     // before the destuff kernel is done: tables into shared memory
     stage_tables<false>(g, b, st, kWinWords, bar_tables);
-    if (!JB2_FILL_WARP) {
+    if (JB2_FILL_WARP == 0 && !b.fill_in_write) {
         zero_fill(b.coef, b.coef_bytes, block, nblocks, threadIdx.x, blockDim.x);
         zero_fill(b.dc, b.dc_bytes, block, nblocks, threadIdx.x, blockDim.x);
     }
-    if (JB2_FILL_WARP == 2 && (threadIdx.x >> 5) == WARPS) {
+    if (JB2_FILL_WARP == 2 && (threadIdx.x >> 5) == WARPS && !b.fill_in_write) {
         zero_fill(b.coef, b.coef_bytes, block, nblocks, threadIdx.x & 31u, 32u);
         zero_fill(b.dc, b.dc_bytes, block, nblocks, threadIdx.x & 31u, 32u);
     }
@@ -680,10 +683,12 @@ __device__ __forceinline__ void huff_sync_body(const ScanGeom& g, const ScanBufs
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t chunk = block * WARPS + warp;
     if (JB2_FILL_WARP == 2 && warp == WARPS) {
-    } else if (JB2_FILL_WARP && warp == WARPS) {
+    } else if (JB2_FILL_WARP == 1 && warp == WARPS) {
+        if (!b.fill_in_write) {
         // (mode 1: the extra warp fills while the other warps iterate)
         zero_fill(b.coef, b.coef_bytes, block, nblocks, (uint32_t)lane, 32u);
         zero_fill(b.dc, b.dc_bytes, block, nblocks, (uint32_t)lane, 32u);
+        }
 #ifdef JB2_TIMELINE
         if (lane == 0) tl_stamp(b.ctrl, 21, false);
 #endif
@@ -839,6 +844,25 @@ __device__ __forceinline__ uint32_t cta_slot_prefix(uint32_t cta, uint32_t n, bo
     return head ? 0u : incl - n;
 }
 
+// Zero coefficient slots [A, B) (int16 indices into the coefficient buffer) and the DC entries of
+// the data units that begin inside, with the whole warp (A and B are warp-uniform).
+__device__ __forceinline__ void warp_zero_slots(int16_t* __restrict__ coef, int16_t* __restrict__ dc,
+                                                uint32_t A, uint32_t B, uint32_t lane)
+{
+    if (A >= B) return;
+    for (uint32_t du = (A + 63u) / 64u + lane; du < (B + 63u) / 64u; du += 32u) dc[du] = 0;
+    const uint32_t A8 = (A + 7u) & ~7u, B8 = B & ~7u; // whole 16-byte vectors: [A8, B8)
+    if (A8 >= B8) {
+        for (uint32_t s = A + lane; s < B; s += 32u) coef[s] = 0;
+        return;
+    }
+    if (A + lane < A8) coef[A + lane] = 0;
+    if (B8 + lane < B) coef[B8 + lane] = 0;
+    uint4* p = reinterpret_cast<uint4*>(coef);
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (uint32_t v = (A8 >> 3) + lane; v < (B8 >> 3); v += 32u) p[v] = z;
+}
+
 __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBufs& b)
 {
     __shared__ SharedTables st;
@@ -906,6 +930,49 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
             qe = umin(h + 1 < (uint32_t)kWriteParts ? q0 + (mid_next >> 16) : q0 + entry_n(rec), q_limit);
             has = qe > qs;
         }
+    }
+    // Zero-fill of the output by the writers themselves, for buffers that do not fit L2.  The slot ranges of consecutive threads
+    // tile the coefficient buffer (the slot prefix sum says where each one starts), so every warp
+    // clears exactly the stretch its 32 threads are about to scatter into - 20 KB of coalesced
+    // stores - and the lines are still in L2 when the scattered 2-byte stores arrive.  Clearing the
+    // whole buffer up front (huff_sync's extra warp) is cheaper while the buffer fits L2 (12 MP:
+    // decode 128.7 us against 132.1 with this path), but at 48 MP (146 MB) every scattered store
+    // became a DRAM read-modify-write: 354 -> 320 us with this path.
+    // What no thread will write is cleared too: the last thread of a restart segment clears up to
+    // the first data unit of the next segment that holds data (or the end of the buffer), the very
+    // first thread from the start of the buffer.
+    if (b.fill_in_write) { // block-uniform
+        uint32_t fs = 0, fe = 0; // this thread's stretch, in global slots
+        bool mine = false;
+        if (j < num_subs && q_limit != 0) {
+            const uint32_t base = first_du * 64u;
+            const uint32_t q_begin = h ? q0 + (mid >> 16) : q0;
+            const uint32_t q_end = h + 1 < (uint32_t)kWriteParts ? q0 + (mid_next >> 16) : q0 + entry_n(rec);
+            fs = base + umin(q_begin, q_limit);
+            fe = base + umin(q_end, q_limit);
+            if (j == 0 && h == 0) fs = 0;
+            const uint32_t seg_subs = (seg.nbytes + (uint32_t)kSubBytes - 1u) / (uint32_t)kSubBytes;
+            if (i + 1 == seg_subs && h + 1 == (uint32_t)kWriteParts) {
+                // last thread of the segment: up to the next segment that holds data
+                const uint32_t nseg = __ldcg(&b.info->num_segments);
+                uint32_t k2 = k + 1, du2 = 0, lim2 = 0;
+                while (k2 < nseg && b.segs[k2].nbytes == 0) ++k2;
+                fe = (k2 < nseg && segment_extent(g, k2, du2, lim2)) ? du2 * 64u : (uint32_t)(b.coef_bytes / 2);
+            }
+            mine = true;
+        }
+        const uint32_t next_fs = __shfl_down_sync(0xffffffffu, fs, 1);
+        const bool chained = mine && (lane == 31 || fe == next_fs);
+        if (__all_sync(0xffffffffu, chained)) {
+            warp_zero_slots(b.coef, b.dc, __shfl_sync(0xffffffffu, fs, 0), __shfl_sync(0xffffffffu, fe, 31),
+                            (uint32_t)lane);
+        } else {
+            // a warp with idle threads (end of the scan) or a surplus segment: stretch by stretch
+            for (int l = 0; l < 32; ++l)
+                warp_zero_slots(b.coef, b.dc, __shfl_sync(0xffffffffu, fs, l), __shfl_sync(0xffffffffu, fe, l),
+                                (uint32_t)lane);
+        }
+        __syncwarp();
     }
     const uint32_t lut_vec = (g.lut_compact_words + 3) / 4;
     uint8_t* warp_mem = reinterpret_cast<uint8_t*>(s_dyn + win_words / 4 + lut_vec) + (size_t)warp * kWarpSmem;

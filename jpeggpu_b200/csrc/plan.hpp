@@ -15,6 +15,13 @@ namespace jb2 {
 
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+// Coefficient buffers above this size are cleared by huff_write itself (the 126 MB L2 of a B200
+// no longer holds the zero-filled lines until the scattered stores arrive).
+#ifndef JB2_FILL_IN_WRITE_BYTES
+#define JB2_FILL_IN_WRITE_BYTES (80ull << 20)
+#endif
+constexpr size_t kFillInWriteBytes = JB2_FILL_IN_WRITE_BYTES;
+
 struct ScanLayout {
     // upload block (offsets inside the staging block == inside the scratch buffer); the look-back
     // descriptors and the ticket of destuff travel as zeros with it
@@ -140,6 +147,7 @@ inline ScanBufs make_bufs(const ScanLayout& L, void* base_ptr)
     b.destuffed = reinterpret_cast<uint32_t*>(base + L.off_destuffed);
     b.coef = reinterpret_cast<int16_t*>(base + L.off_coef);
     b.coef_bytes = L.coef_bytes;
+    b.fill_in_write = L.coef_bytes > kFillInWriteBytes ? 1u : 0u;
     b.dc = reinterpret_cast<int16_t*>(base + L.off_dc);
     b.dc_bytes = L.dc_bytes;
     b.entries = reinterpret_cast<SubEntry*>(base + L.off_entries);

@@ -287,3 +287,126 @@ def test_verify_and_repair_path_is_bit_exact():
         "print('ok')\n")
     out = _run_with_variant("lib_spin1.so", "-DJB2_MAILBOX_SPINS=1", code)
     print(out)
+
+
+def _poisoned_decode(data, walk_mode=3):
+    """Decode with every byte of the scratch buffer set to garbage first (the transfer then writes
+    what it uploads): whatever the kernels read must have been written by this decode."""
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    sess = DecodeSession()
+    sess.dec.set_deferred_walk(walk_mode)
+    info = sess.parse(pinned_bytes(data))
+    sess.scratch.fill_(0xC3)
+    sess.transfer()
+    planes = sess.alloc_planes()
+    sess.decode(planes)
+    coefs = sess.decode_coefficients()
+    torch.cuda.synchronize()
+    out = ([t.cpu().numpy()[:, : info.sizes_x[c]] for c, t in enumerate(planes)], [c.cpu().numpy() for c in coefs])
+    sess.close()
+    return out
+
+
+POISON_CASES = {
+    "no_dri": dict(w=1600, h=1200, seed=101, mode="YCbCr", subsampling=2, quality=92),
+    "dri_1": dict(w=800, h=600, seed=102, mode="YCbCr", subsampling=2, quality=90, restart_blocks=1),
+    "dri_37": dict(w=1600, h=1200, seed=103, mode="YCbCr", subsampling=1, quality=95, restart_blocks=37),
+    "grey_tiny": dict(w=40, h=24, seed=104, mode="L"),
+    "444_q100": dict(w=1200, h=900, seed=105, mode="YCbCr", subsampling=0, quality=100),
+    "flat_q20": dict(w=2048, h=1536, seed=106, mode="YCbCr", subsampling=2, quality=20),
+}
+
+
+@pytest.mark.parametrize("name", list(POISON_CASES))
+@pytest.mark.parametrize("walk_mode", [3, 0], ids=["device_walk", "host_walk"])
+def test_nothing_is_read_that_this_decode_did_not_write(name, walk_mode):
+    """huff_write clears exactly the stretch of the coefficient buffer each warp scatters into
+    (plus what nobody writes); a stretch left out would show up as 0xC3C3 coefficients."""
+    data = inputs.pillow_jpeg(**POISON_CASES[name])
+    ref = ob.decode(data)
+    assert ref["status"] == 0
+    planes, coefs = _poisoned_decode(data, walk_mode)
+    for c in range(len(planes)):
+        assert np.array_equal(coefs[c], ref["planes"][c]), (name, c)
+        assert np.array_equal(planes[c], ref["pixels"][c]), (name, c)
+
+
+def test_restart_segments_without_data_are_cleared():
+    """Two restart markers back to back leave a segment without a single subsequence: its data
+    units hold zero coefficients (samples 128) whatever the scratch held before, like in the
+    reference, which clears the whole buffer first.  (The oracle reads an empty segment as a run
+    of one bits, so the expectation is built from the intact file: 640x480 4:2:0 with one MCU row
+    per restart segment - the other rows decode as before, DC prediction restarts per segment.)"""
+    data = inputs.pillow_jpeg(w=640, h=480, seed=107, mode="YCbCr", subsampling=2, quality=90, restart_blocks=40)
+    st, info = ob.parse(data)
+    sc = info.scans[0]
+    scan = bytearray(data[sc.begin:sc.end])
+    # drop the entropy-coded bytes of the third and fourth restart segment (keep their markers)
+    marks = [i for i in range(len(scan) - 1) if scan[i] == 0xff and 0xd0 <= scan[i + 1] <= 0xd7]
+    assert len(marks) == 29
+    cut = bytes(scan[:marks[1] + 2]) + bytes(scan[marks[2]:marks[2] + 2]) + bytes(scan[marks[3]:])
+    damaged = data[:sc.begin] + cut + data[sc.end:]
+    ref = ob.decode(data)
+    assert ref["status"] == 0
+    for mode in (3, 0):
+        planes, coefs = _poisoned_decode(damaged, mode)
+        for c in range(len(planes)):
+            rows = slice(32, 64) if c == 0 else slice(16, 32)  # MCU rows 2 and 3
+            want_c = ref["planes"][c].copy()
+            want_c[rows] = 0
+            want_p = ref["pixels"][c].copy()
+            want_p[rows] = 128
+            assert np.array_equal(coefs[c], want_c), (mode, c)
+            assert np.array_equal(planes[c], want_p), (mode, c)
+
+
+def test_truncated_scan_leaves_zero_coefficients_behind():
+    """A file cut in the middle of the scan: the data units behind the cut are zero (level 128 /
+    the last DC), not what the previous decode left in the scratch."""
+    data = inputs.pillow_jpeg(w=1600, h=1200, seed=108, mode="YCbCr", subsampling=2, quality=92)
+    cut = data[: len(data) * 2 // 3]
+    if cut[-1] == 0xff:
+        cut = cut[:-1]
+    a_planes, a_coefs = _poisoned_decode(cut, 3)
+    # the same decode over a scratch poisoned with another pattern gives the same output
+    import torch
+    from jpeggpu_b200.torch_io import DecodeSession, pinned_bytes
+    sess = DecodeSession()
+    info = sess.parse(pinned_bytes(cut))
+    sess.scratch.fill_(0x5A)
+    sess.transfer()
+    planes = sess.alloc_planes()
+    sess.decode(planes)
+    coefs = sess.decode_coefficients()
+    torch.cuda.synchronize()
+    for c in range(info.num_components):
+        assert np.array_equal(coefs[c].cpu().numpy(), a_coefs[c]), c
+        assert np.array_equal(planes[c].cpu().numpy()[:, : info.sizes_x[c]], a_planes[c]), c
+    # and the tail of the luma coefficient plane holds no AC coefficient (the DC of every data
+    # unit is the last predictor: nothing restarts it)
+    tail = a_coefs[0][-64:].copy()
+    tail[::8, ::8] = 0
+    assert not tail.any()
+    sess.close()
+
+
+def test_writers_clear_their_own_stretches_variant():
+    """Above 80 MB of coefficients (48 MP) huff_write clears the buffer itself, stretch by stretch;
+    below, huff_sync clears it up front.  A library built with the threshold at zero
+    (-DJB2_FILL_IN_WRITE_BYTES=0) runs the first path on the small poisoned inputs of this file."""
+    code = (
+        "import numpy as np, inputs, oracle_bindings as ob\n"
+        "import test_gpu_parity as t\n"
+        "for name, kw in t.POISON_CASES.items():\n"
+        "    data = inputs.pillow_jpeg(**kw)\n"
+        "    ref = ob.decode(data)\n"
+        "    for mode in (3, 0):\n"
+        "        planes, coefs = t._poisoned_decode(data, mode)\n"
+        "        for c in range(len(planes)):\n"
+        "            assert np.array_equal(coefs[c], ref['planes'][c]), (name, mode, c)\n"
+        "            assert np.array_equal(planes[c], ref['pixels'][c]), (name, mode, c)\n"
+        "t.test_restart_segments_without_data_are_cleared()\n"
+        "t.test_truncated_scan_leaves_zero_coefficients_behind()\n"
+        "print('ok')\n")
+    _run_with_variant("lib_fillwrite.so", "-DJB2_FILL_IN_WRITE_BYTES=0", code)
