@@ -375,7 +375,7 @@ def ours_single(sess, host, flush_l2, sample, steps, warmup):
     return dev, e2e, planes
 
 
-def ours_batch(rank, world, device, total_images, chunk, depth):
+def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
     """BASELINE config 5 on this rank: files i with i % world == rank, through fused batches."""
     import numpy as np
     import torch
@@ -451,11 +451,17 @@ def ours_batch(rank, world, device, total_images, chunk, depth):
         dt = time.perf_counter() - t0
         return dt, max(r[0] for r in res), max(r[1] for r in res)
 
-    run(chunks[:depth], False)  # warm-up: allocations, pinned staging, kernel attributes
+    # warm-up: one untimed pass over the whole batch (allocations, pinned staging, kernel attributes,
+    # the threads' CUDA contexts), then `repeats` timed passes - every pass uploads every file again;
+    # the median pass is reported, all of them are listed
+    run(chunks, False)
+    passes = []
+    for _ in range(max(1, repeats)):
+        barrier(world)
+        passes.append(run(chunks, True))
     barrier(world)
-    dt, plan_s, enq_s = run(chunks, True)
+    dt, plan_s, enq_s = sorted(passes, key=lambda r: r[0])[len(passes) // 2]
     host_s = plan_s + enq_s
-    barrier(world)
     info0 = items[0].info
     assert (info0.sizes_y[0], info0.sizes_x[0], info0.sizes_y[1], info0.sizes_x[1]) == ImgInfo0
     # spot check: the last image of the last chunk against the per-image path
@@ -473,7 +479,7 @@ def ours_batch(rank, world, device, total_images, chunk, depth):
         ln["fb"].close()
     total_bytes = sum(len(b) for b in blobs)
     return {"seconds": dt, "images": n, "host_enqueue_seconds": host_s, "plan_seconds": plan_s,
-            "bytes": total_bytes, "matches_per_image_path": ok}
+            "bytes": total_bytes, "matches_per_image_path": ok, "seconds_all_passes": [round(r[0], 5) for r in passes]}
 
 
 def batch_shape(args, world):
@@ -638,7 +644,7 @@ def run_ours(args):
         del flush
         torch.cuda.empty_cache()
         b_chunk, b_depth = batch_shape(args, world)
-        r = ours_batch(rank, world, device, args.batch_images, b_chunk, b_depth)
+        r = ours_batch(rank, world, device, args.batch_images, b_chunk, b_depth, args.batch_repeats)
         if "seconds" in r:
             secs = max_over_ranks(r["seconds"], world)
             host_s = max_over_ranks(r["host_enqueue_seconds"], world)
@@ -651,6 +657,8 @@ def run_ours(args):
                              f"{b_chunk} images per kernel launch, {b_depth} batches in flight per GPU)",
                      "timing": "wall clock, first enqueue to last stream sync, H2D of every file inside; max over ranks",
                      "host_threads_per_gpu": b_depth,
+                     "passes": f"1 untimed + {args.batch_repeats} timed passes over the whole batch, median reported",
+                     "seconds_all_passes_rank0": r["seconds_all_passes"],
                      "host_busy_seconds_slowest_thread": round(host_s, 4),
                      "host_plan_seconds_rank0": round(r["plan_seconds"], 4),
                      "h2d_bytes_rank0": r["bytes"], "nproc": os.cpu_count(),
@@ -964,6 +972,7 @@ def main():
     ap.add_argument("--batch-chunk", type=int, default=0,
                     help="images per fused batch (0: from the images per rank, see batch_shape)")
     ap.add_argument("--batch-depth", type=int, default=0, help="fused batches in flight per GPU (0: auto)")
+    ap.add_argument("--batch-repeats", type=int, default=3, help="timed passes over the batch (median reported)")
     ap.add_argument("--reference-batch-images", type=int, default=1024,
                     help="images of the batch the reference arm's per-image loop decodes (bounded sample)")
     ap.add_argument("--no-configs", action="store_true", help="skip the side configurations and nvJPEG")
