@@ -613,7 +613,7 @@ constexpr size_t kStaticMaxScanBytes = JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES;
 constexpr size_t kStaticMaxTiles = (kStaticMaxScanBytes + kDestuffTile - 1) / kDestuffTile;
 constexpr size_t kStaticHeaderWords = 32; // 256 bytes: word 0 holds the ticket
 constexpr size_t kStaticWords = kStaticHeaderWords + 2 * kStaticMaxTiles;
-constexpr size_t kStaticScratchBytes = kStaticWords * sizeof(unsigned long long); // 262 400
+static_assert(kStaticWords * sizeof(unsigned long long) == 262400, "kStaticScratchBytes: the size the header states");
 constexpr int kStaticMaxDevices = 64;
 
 static __device__ __align__(256) unsigned long long g_destuff_static_scratch[kStaticWords];

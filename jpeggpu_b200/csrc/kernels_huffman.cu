@@ -305,11 +305,7 @@ struct DevMem {
     uint32_t win_addr;
     uint32_t lut_addr; // shared address of the staged LUT pool
     static constexpr uint32_t kWordStep = 4;
-    __device__ __forceinline__ uint32_t lut(uint32_t tbl, uint32_t i) const { return lds32(tbl + i * 4u); }
     __device__ __forceinline__ uint32_t single_of(uint32_t tbl) const { return tbl + (uint32_t)kLut1Size * 4u; }
-    // continuation field: 16-byte units from the start of the staged LUT pool (dynamic shared memory
-    // behind the window; stage_tables<true> re-bases the field for its compact layout)
-    __device__ __forceinline__ uint32_t cont_table(uint32_t e) const { return lut_addr + ((e >> 8) & 0x7fff0u); }
     // generic_step (huff_core.hpp) with every decision as a select: ptxas turns the C++ form into
     // three branches per symbol.  Only the loop's back edge branches, on a predicate that is
     // ready long before it issues.
@@ -395,25 +391,6 @@ struct DevMem {
             : "=r"(addr)
             : "r"(peek & (0xffffffffu << (32 - kLutBits))), "r"(1u << (kLutBits + 2)), "r"(tbl));
         return lds32(addr);
-    }
-    // Both candidate windows are shifted as soon as the new position is known; the "crossed a
-    // word boundary" predicate only selects between the two results, so the dependency chain of
-    // the symbol loop is position -> funnel shift -> select.  The window registers themselves
-    // move by predicated instructions off that chain, with the look-ahead load for the NEXT slide.
-    __device__ __forceinline__ uint32_t slide_peek(uint32_t& w0, uint32_t& w1, uint32_t& w2, uint32_t& wn,
-                                                   uint32_t pp, uint32_t pn) const
-    {
-        uint32_t peek;
-        asm volatile("{\n\t.reg .pred s;\n\t.reg .b32 t, a, b;\n\t"
-                     "shf.l.wrap.b32 a, %2, %1, %5;\n\t"
-                     "shf.l.wrap.b32 b, %3, %2, %5;\n\t"
-                     "xor.b32 t, %5, %6;\n\tand.b32 t, t, 32;\n\tsetp.ne.u32 s, t, 0;\n\t"
-                     "selp.b32 %0, b, a, s;\n\t"
-                     "@s mov.b32 %1, %2;\n\t@s mov.b32 %2, %3;\n\t@s ld.shared.u32 %3, [%4];\n\t"
-                     "@s add.u32 %4, %4, 4;\n\t}"
-                     : "=r"(peek), "+r"(w0), "+r"(w1), "+r"(w2), "+r"(wn)
-                     : "r"(pn), "r"(pp));
-        return peek;
     }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
