@@ -392,7 +392,7 @@ def test_truncated_scan_leaves_zero_coefficients_behind():
 
 
 def test_writers_clear_their_own_stretches_variant():
-    """Above 80 MB of coefficients (48 MP) huff_write clears the buffer itself, stretch by stretch;
+    """Above 100 MB of coefficients (48 MP) huff_write clears the buffer itself, stretch by stretch;
     below, huff_sync clears it up front.  A library built with the threshold at zero
     (-DJB2_FILL_IN_WRITE_BYTES=0) runs the first path on the small poisoned inputs of this file."""
     code = (
