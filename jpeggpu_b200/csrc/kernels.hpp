@@ -13,7 +13,10 @@
 
 namespace jb2 {
 
-constexpr int kHuffThreads = 128;
+#ifndef JB2_SYNC_WARPS
+#define JB2_SYNC_WARPS 4
+#endif
+constexpr int kHuffThreads = JB2_SYNC_WARPS * 32; // decoding threads of a huff_sync CTA (one image)
 constexpr int kDcTile = 256;  // MCUs per CTA in the DC scan
 
 // Device pointers of one scan (all inside the caller's scratch buffer).
