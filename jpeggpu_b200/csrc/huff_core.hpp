@@ -67,6 +67,21 @@ JB2_HD int extend_value(uint32_t bits, uint32_t size)
     return bits < (1u << (size - 1)) ? (int)bits - (int)(1u << size) + 1 : (int)bits;
 }
 
+// WRITE pass, portable form: the coefficient of the symbol whose entry is `e` (window `peek`, slot
+// counter `qq` before the symbol) goes to the policy's put().  DC and AC alike: a zero value needs
+// no store (every sink is pre-zeroed), the coefficient keeps its zig-zag index (the IDCT
+// un-zig-zags in registers); continuations and kEntrySlow have size 0.
+template <class Mem>
+JB2_HD void put_symbol_generic(const Mem& M, uint32_t e, uint32_t peek, uint32_t qq)
+{
+    const uint32_t size = entry_size(e);
+    const uint32_t pos = qq + entry_adv(e) - 1u;
+    if (size != 0 && ((pos ^ qq) & 64u) == 0) {
+        const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
+        M.put(pos, extend_value(bits, size));
+    }
+}
+
 // (hi:lo) << (shift mod 32), upper word
 JB2_HD uint32_t funnel_left_wrap(uint32_t hi, uint32_t lo, uint32_t shift)
 {
@@ -164,17 +179,7 @@ JB2_HD void decode_span(const Mem& M, uint32_t& p, uint32_t end, uint32_t& q, ui
     for (;;) {
         uint32_t flags;
         do {
-            if (WRITE) {
-                // DC and AC alike: a zero value needs no store (every sink is pre-zeroed), the
-                // coefficient keeps its zig-zag index (the IDCT un-zig-zags in registers);
-                // continuations and kEntrySlow have size 0
-                const uint32_t size = entry_size(e);
-                const uint32_t pos = qq + entry_adv(e) - 1u;
-                if (size != 0 && ((pos ^ qq) & 64u) == 0) {
-                    const uint32_t bits = (peek << (entry_skip(e) - size)) >> (32 - size);
-                    M.put(pos, extend_value(bits, size));
-                }
-            }
+            if (WRITE) M.put_symbol(e, peek, qq);
             flags = M.template step<WRITE>(e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
             e = M.probe(tbl, peek); // entry of the next symbol
             r = M.rec(ch);
@@ -238,6 +243,7 @@ struct HostMem {
     }
     int16_t* coef_ = nullptr; // WRITE: first data unit of the restart segment
     int16_t* dc_ = nullptr;
+    JB2_HD void put_symbol(uint32_t e, uint32_t peek, uint32_t qq) const { put_symbol_generic(*this, e, peek, qq); }
     JB2_HD void put(uint32_t slot, int v) const
     {
         if ((slot & 63u) == 0) dc_[slot >> 6] = (int16_t)v;

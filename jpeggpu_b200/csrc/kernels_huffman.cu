@@ -394,6 +394,7 @@ struct DevMem {
     }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
+    __device__ __forceinline__ void put_symbol(uint32_t, uint32_t, uint32_t) const {}
 };
 
 // Policy of huff_write: DevMem + the coefficient sink.  The symbol loop only appends
@@ -417,6 +418,69 @@ struct WriteMem : DevMem {
         } else {
             coef_seg[slot] = (int16_t)v;
         }
+    }
+    // put_symbol_generic without a branch: value extraction, "is there a coefficient", "list or
+    // overflow" and "DC or AC" are predicates of two predicated stores.  The C++ form costs two
+    // data-dependent branches per symbol on predicates that come fresh from the table probe, and
+    // the lanes of a warp take them differently (JB2_WRITE_PTX=0 restores it).
+#ifndef JB2_WRITE_PTX
+#define JB2_WRITE_PTX 1
+#endif
+    __device__ __forceinline__ void put_symbol(uint32_t e, uint32_t peek, uint32_t qq) const
+    {
+#if JB2_WRITE_PTX
+        asm volatile(
+            "{\n\t"
+            ".reg .pred ps, pl, po, pd, pn;\n\t"
+            ".reg .b32 sz, pos, t, u, bits, val, pk;\n\t"
+            ".reg .b64 ad, bs;\n\t"
+            "shr.u32 sz, %1, 8;\n\t"
+            "and.b32 sz, sz, 15;\n\t"
+            "and.b32 t, %1, 127;\n\t"
+            "add.u32 pos, %3, t;\n\t"
+            "sub.u32 pos, pos, 1;\n\t"
+            // a coefficient: size != 0 and inside the data unit
+            "xor.b32 t, pos, %3;\n\t"
+            "and.b32 t, t, 64;\n\t"
+            "setp.eq.u32 ps, t, 0;\n\t"
+            "setp.ne.and.u32 ps, sz, 0, ps;\n\t"
+            // magnitude bits (PTX shifts clamp: size 0 gives 0) and their sign extension
+            "shr.u32 t, %1, 27;\n\t"
+            "sub.u32 t, t, sz;\n\t"
+            "shl.b32 bits, %2, t;\n\t"
+            "sub.u32 t, 32, sz;\n\t"
+            "shr.u32 bits, bits, t;\n\t"
+            "sub.u32 t, sz, 1;\n\t"
+            "shl.b32 u, 1, t;\n\t"
+            "setp.lt.u32 pn, bits, u;\n\t"
+            "shl.b32 t, 1, sz;\n\t"
+            "sub.u32 t, bits, t;\n\t"
+            "add.u32 t, t, 1;\n\t"
+            "selp.b32 val, t, bits, pn;\n\t"
+            // list entry, or straight to global memory when the list is full
+            "setp.ne.and.u32 pl, %0, %4, ps;\n\t"
+            "setp.eq.and.u32 po, %0, %4, ps;\n\t"
+            "sub.u32 t, pos, %5;\n\t"
+            "shl.b32 pk, t, 16;\n\t"
+            "and.b32 t, val, 0xffff;\n\t"
+            "or.b32 pk, pk, t;\n\t"
+            "@pl st.shared.u32 [%0], pk;\n\t"
+            "@pl add.u32 %0, %0, 4;\n\t"
+            "and.b32 t, pos, 63;\n\t"
+            "setp.eq.u32 pd, t, 0;\n\t"
+            "shr.u32 t, pos, 6;\n\t"
+            "selp.b32 t, t, pos, pd;\n\t"
+            "selp.b64 bs, %7, %6, pd;\n\t"
+            "mul.wide.u32 ad, t, 2;\n\t"
+            "add.u64 ad, ad, bs;\n\t"
+            "@po st.global.u16 [ad], val;\n\t"
+            "}"
+            : "+r"(list_ptr)
+            : "r"(e), "r"(peek), "r"(qq), "r"(list_limit), "r"(slot0), "l"(coef_seg), "l"(dc_seg)
+            : "memory");
+#else
+        put_symbol_generic(*this, e, peek, qq);
+#endif
     }
 };
 
@@ -463,6 +527,7 @@ struct GlobalMem {
     }
     __device__ __forceinline__ void note_long_code() const {}
     __device__ __forceinline__ void put(uint32_t, int) const {}
+    __device__ __forceinline__ void put_symbol(uint32_t, uint32_t, uint32_t) const {}
 };
 
 // Slice `block` of `nblocks` of a buffer, cleared by `nthreads` threads of which this is `tid`.

@@ -9,6 +9,7 @@
 using namespace jb2;
 struct CountMem : HostMem {
     mutable int puts = 0;
+    void put_symbol(uint32_t e, uint32_t peek, uint32_t qq) const { put_symbol_generic(*this, e, peek, qq); }
     void put(uint32_t, int) const { ++puts; }
     template <bool WRITE>
     uint32_t step(uint32_t e, uint32_t& pp, uint32_t& qq, uint32_t& ch, uint32_t& tbl, const SlotRec& r,

@@ -51,6 +51,7 @@ struct SimMem {
     {
         return generic_step<WRITE>(*this, e, pp, qq, ch, tbl, r, w0, w1, w2, wn, peek, end, end_fast, q_limit);
     }
+    void put_symbol(uint32_t e, uint32_t peek, uint32_t qq) const { put_symbol_generic(*this, e, peek, qq); }
     void put(uint32_t, int) const {}
     void note_long_code() const { ++g_long; }
 };
