@@ -158,6 +158,16 @@ __device__ __forceinline__ void stage_quantisers(uint32_t (*s_q)[32], const QPai
 #ifndef JB2_IDCT_STAGED
 #define JB2_IDCT_STAGED 1
 #endif
+// Experiment: fetch every data unit with ONE cp.async.bulk of 128 bytes,
+// completed on an mbarrier per warp buffer, into a tile with a 144-byte pitch (conflict-free
+// without a swizzle) instead of eight 16-byte cp.async per lane.  Measured on B200, 12 MP,
+// idct_kernel: 22.5 us with cp.async, 26.7 us with bulk copies (48 MP 67.3 / 79.3, 2 MP 12.3 / 14.2;
+// profiles/r2_r_idct_bulk.txt): 285 768 bulk copies of 128 bytes cost more than they save - the
+// copy engine wants larger pieces, and a warp's 32 data units are 128-byte pieces 768 bytes apart
+// (plane-order threads over an MCU-interleaved buffer).  Same output.  Off by default.
+#ifndef JB2_IDCT_BULK
+#define JB2_IDCT_BULK 0
+#endif
 // Warp-cooperative fetch of the warp's 32 data units.  Thread-per-data-unit loads touch 32
 // different 128-byte lines per instruction; here eight lanes fetch the eight 16-byte chunks of
 // ONE data unit, so an instruction covers four whole data units (4 lines), and the chunks go to
@@ -182,6 +192,7 @@ __device__ __forceinline__ void stage_units(const int16_t* __restrict__ coef, ui
     __syncwarp();
 }
 
+template <bool PITCH144 = false> // layout of `tile`: 144-byte pitch (bulk copies) or XOR swizzle
 __device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
                                           const int16_t* __restrict__ dc, uint32_t du,
                                           const uint32_t* q, int (&v)[8][8], const uint4* tile)
@@ -193,7 +204,7 @@ __device__ __forceinline__ void load_idct(const int16_t* __restrict__ coef,
     // indices are compile-time constants after unrolling)
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
-        const uint4 w = JB2_IDCT_STAGED ? tile[lane * 8 + (r ^ (lane & 7))] : src[r];
+        const uint4 w = PITCH144 ? tile[lane * 9 + r] : JB2_IDCT_STAGED ? tile[lane * 8 + (r ^ (lane & 7))] : src[r];
         const uint4 qq = qsrc[r];
         const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
         const uint32_t qw[4] = {qq.x, qq.y, qq.z, qq.w};
@@ -243,6 +254,36 @@ __device__ __forceinline__ void stage_units_async(const int16_t* __restrict__ co
         }
     }
 }
+// Bulk flavour: lane l copies its own data unit (128 contiguous bytes) to tile + l * 144.
+__device__ __forceinline__ void stage_units_bulk(const int16_t* __restrict__ coef, uint32_t du, bool valid,
+                                                 uint4* tile, unsigned long long* bar)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t bar_addr = (uint32_t)__cvta_generic_to_shared(bar);
+    const uint32_t n = __popc(__ballot_sync(0xffffffffu, valid));
+    if (lane == 0)
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(n * 128u) : "memory");
+    __syncwarp();
+    if (valid) {
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile + lane * 9);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(coef + (size_t)du * 64), "r"(128u), "r"(bar_addr)
+                     : "memory");
+    }
+}
+__device__ __forceinline__ void bulk_wait(unsigned long long* bar, uint32_t parity)
+{
+    const uint32_t bar_addr = (uint32_t)__cvta_generic_to_shared(bar);
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "JB2_IDCT_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra JB2_IDCT_DONE;\n"
+                 "bra JB2_IDCT_WAIT;\n"
+                 "JB2_IDCT_DONE:\n"
+                 "}" ::"r"(bar_addr), "r"(parity)
+                 : "memory");
+}
 __device__ __forceinline__ void async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
@@ -254,7 +295,7 @@ __device__ __forceinline__ void store_unit(const ScanGeom& g, const int16_t* __r
 {
     const int a = pos.comp;
     int v[8][8];
-    load_idct(coef, dc, pos.du, q, v, tile);
+    load_idct<JB2_IDCT_BULK != 0>(coef, dc, pos.du, q, v, tile);
 
     const int x0 = pos.bx * 8, y0 = pos.by * 8;
     const int size_x = g.size_x[a], size_y = g.size_y[a];
@@ -293,26 +334,51 @@ __device__ __forceinline__ void idct_body(const ScanGeom& g, const int16_t* __re
 #if JB2_IDCT_STAGED
     // Software pipeline over kIdctUnits data units per thread: while the IDCT of one unit runs,
     // the cp.async fetch of the next one is in flight (double-buffered tile per warp).
-    __shared__ uint4 s_tile[kIdctThreads / 32][2][256];
+    constexpr int kTileVecs = JB2_IDCT_BULK ? 32 * 9 : 256;
+    __shared__ uint4 s_tile[kIdctThreads / 32][2][kTileVecs];
     uint4* const tiles = s_tile[threadIdx.x >> 5][0];
+#if JB2_IDCT_BULK
+    __shared__ __align__(8) unsigned long long s_bar[kIdctThreads / 32][2];
+    unsigned long long* const bars = s_bar[threadIdx.x >> 5];
+    if ((threadIdx.x & 31) == 0) {
+        const uint32_t b0 = (uint32_t)__cvta_generic_to_shared(bars);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b0) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b0 + 8u) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async;" ::: "memory");
+    }
+    __syncwarp();
+#endif
     const uint32_t first = block * (uint32_t)(kIdctThreads * kIdctUnits) + threadIdx.x;
     DuPos pos, nxt;
     pos.comp = nxt.comp = 0;
     pos.du = nxt.du = 0;
     bool located = locate(g, first, pos);
+#if JB2_IDCT_BULK
+    stage_units_bulk(coef, pos.du, located, tiles, bars);
+#else
     stage_units_async(coef, pos.du, located, tiles);
     async_commit();
+#endif
 #pragma unroll 1
     for (int it = 0; it < kIdctUnits; ++it) {
-        const uint4* tile = tiles + (it & 1) * 256;
+        const uint4* tile = tiles + (it & 1) * kTileVecs;
         bool located_next = false;
+#if JB2_IDCT_BULK
         if (it + 1 < kIdctUnits) {
             located_next = locate(g, first + (uint32_t)(it + 1) * kIdctThreads, nxt);
-            stage_units_async(coef, nxt.du, located_next, tiles + ((it + 1) & 1) * 256);
+            stage_units_bulk(coef, nxt.du, located_next, tiles + ((it + 1) & 1) * kTileVecs, bars + ((it + 1) & 1));
+        }
+        bulk_wait(bars + (it & 1), (uint32_t)(it >> 1) & 1u);
+#else
+        if (it + 1 < kIdctUnits) {
+            located_next = locate(g, first + (uint32_t)(it + 1) * kIdctThreads, nxt);
+            stage_units_async(coef, nxt.du, located_next, tiles + ((it + 1) & 1) * kTileVecs);
         }
         async_commit();
         async_wait_all_but_one();
         __syncwarp();
+#endif
         if (located) store_unit(g, coef, dc, out, pos, s_q[pos.comp], tile);
         __syncwarp(); // the tile is refilled two iterations from now
         pos = nxt;
