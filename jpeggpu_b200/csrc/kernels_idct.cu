@@ -168,6 +168,9 @@ __device__ __forceinline__ void stage_quantisers(uint32_t (*s_q)[32], const QPai
 #ifndef JB2_IDCT_BULK
 #define JB2_IDCT_BULK 0
 #endif
+#ifndef JB2_IDCT_EARLY_FETCH
+#define JB2_IDCT_EARLY_FETCH 1
+#endif
 // Warp-cooperative fetch of the warp's 32 data units.  Thread-per-data-unit loads touch 32
 // different 128-byte lines per instruction; here eight lanes fetch the eight 16-byte chunks of
 // ONE data unit, so an instruction covers four whole data units (4 lines), and the chunks go to
@@ -328,15 +331,27 @@ __device__ __forceinline__ void idct_body(const ScanGeom& g, const int16_t* __re
                                           const int16_t* __restrict__ dc, const PlaneDst& out,
                                           uint32_t (*s_q)[32], const uint32_t block)
 {
-    grid_dependency_wait();
-    grid_dependency_trigger();
-    __syncthreads();
 #if JB2_IDCT_STAGED
     // Software pipeline over kIdctUnits data units per thread: while the IDCT of one unit runs,
     // the cp.async fetch of the next one is in flight (double-buffered tile per warp).
     constexpr int kTileVecs = JB2_IDCT_BULK ? 32 * 9 : 256;
     __shared__ uint4 s_tile[kIdctThreads / 32][2][kTileVecs];
     uint4* const tiles = s_tile[threadIdx.x >> 5][0];
+    const uint32_t first = block * (uint32_t)(kIdctThreads * kIdctUnits) + threadIdx.x;
+    DuPos pos, nxt;
+    pos.comp = nxt.comp = 0;
+    pos.du = nxt.du = 0;
+    bool located = locate(g, first, pos);
+#if !JB2_IDCT_BULK && JB2_IDCT_EARLY_FETCH
+    // The coefficients come from huff_write, the grand-predecessor: it is complete when this CTA
+    // starts (dc_scan triggers its dependents only behind its own dependency wait), so the fetch of
+    // the first data unit can run while dc_scan - which only produces the DC values - is at work.
+    stage_units_async(coef, pos.du, located, tiles);
+    async_commit();
+#endif
+    grid_dependency_wait();
+    grid_dependency_trigger();
+    __syncthreads();
 #if JB2_IDCT_BULK
     __shared__ __align__(8) unsigned long long s_bar[kIdctThreads / 32][2];
     unsigned long long* const bars = s_bar[threadIdx.x >> 5];
@@ -349,14 +364,9 @@ __device__ __forceinline__ void idct_body(const ScanGeom& g, const int16_t* __re
     }
     __syncwarp();
 #endif
-    const uint32_t first = block * (uint32_t)(kIdctThreads * kIdctUnits) + threadIdx.x;
-    DuPos pos, nxt;
-    pos.comp = nxt.comp = 0;
-    pos.du = nxt.du = 0;
-    bool located = locate(g, first, pos);
 #if JB2_IDCT_BULK
     stage_units_bulk(coef, pos.du, located, tiles, bars);
-#else
+#elif !JB2_IDCT_EARLY_FETCH
     stage_units_async(coef, pos.du, located, tiles);
     async_commit();
 #endif
@@ -385,6 +395,9 @@ __device__ __forceinline__ void idct_body(const ScanGeom& g, const int16_t* __re
         located = located_next;
     }
 #else
+    grid_dependency_wait();
+    grid_dependency_trigger();
+    __syncthreads();
     DuPos pos;
     if (!locate(g, block * kIdctThreads + threadIdx.x, pos)) return;
     store_unit(g, coef, dc, out, pos, s_q[pos.comp], nullptr);
@@ -419,6 +432,7 @@ idct_batch_kernel(const BatchImage* __restrict__ images)
             out.pitch[threadIdx.x] = im.pitch[threadIdx.x];
         }
     }
+    __syncthreads(); // idct_body reads the geometry before its own barrier (early fetch)
     idct_body(g, im.b.coef, im.b.dc, out, s_q, blockIdx.x);
 }
 
