@@ -917,14 +917,18 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
     // before huff_sync is done (the control block was cleared two kernels ago): ticket, tables
     if (threadIdx.x == 0) s_cta = atomicAdd(&b.ctrl->write_ticket, 1u);
     stage_tables<true>(g, b, st, win_words);
+    __syncthreads();
+    // The scan itself comes from the destuff kernel, the grand-predecessor: it is complete when this
+    // CTA starts (huff_sync triggers its dependents only behind its own dependency wait), so the
+    // window is staged while huff_sync is still at work; only the records have to wait.
+    const uint32_t num_subs = __ldcg(&b.info->num_subs);
+    const uint32_t cta = s_cta;
+    const uint32_t sub0 = cta * subs_per_cta;
+    stage_window(b, num_subs, (long long)sub0 * kSubWords, win_words, JB2_BULK_STAGE ? smem_addr(&s_bar) : 0u);
     grid_dependency_wait();
     grid_dependency_trigger();
     JB2_TL(b.ctrl, 15, true);
     JB2_TL(b.ctrl, 8, false);
-    __syncthreads();
-    const uint32_t num_subs = __ldcg(&b.info->num_subs);
-    const uint32_t cta = s_cta;
-    const uint32_t sub0 = cta * subs_per_cta;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t j = sub0 + threadIdx.x / kWriteParts, h = threadIdx.x % kWriteParts;
 
@@ -957,7 +961,6 @@ __device__ __forceinline__ void huff_write_body(const ScanGeom& g, const ScanBuf
     q0 = __shfl_sync(0xffffffffu, q0, lane & ~(kWriteParts - 1)); // the sub's first thread has it
     if (h == 0 && j < num_subs) b.qpos[j] = q0; // kept for inspection (jpeggpu_b200_scan_stats)
 
-    stage_window(b, num_subs, (long long)sub0 * kSubWords, win_words, JB2_BULK_STAGE ? smem_addr(&s_bar) : 0u);
     const unsigned long long t1 = now_ns();
 
     // this thread's half subsequence: placement, slot range [qs, qe)
