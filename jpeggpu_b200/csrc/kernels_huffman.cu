@@ -126,17 +126,22 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
 }
+// Bounded: a copy that never completes (it cannot, short of a hardware fault) must not hang the GPU;
+// each try_wait already blocks for a hardware-defined time slice.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
-    asm volatile("{\n"
-                 ".reg .pred p;\n"
-                 "JB2_WAIT:\n"
-                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-                 "@p bra JB2_DONE;\n"
-                 "bra JB2_WAIT;\n"
-                 "JB2_DONE:\n"
-                 "}" ::"r"(bar), "r"(parity)
-                 : "memory");
+    for (int spin = 0; spin < (1 << 20); ++spin) {
+        uint32_t done;
+        asm volatile("{\n"
+                     ".reg .pred p;\n"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+                     "selp.u32 %0, 1, 0, p;\n"
+                     "}"
+                     : "=r"(done)
+                     : "r"(bar), "r"(parity)
+                     : "memory");
+        if (done) return;
+    }
 }
 
 struct __align__(16) SharedTables {

@@ -184,10 +184,9 @@ jpeggpu_status read_dri(Cursor& cur, ImagePlan& plan, const Logger& log)
     const int length = (int)cur.u16() - 2;
     if (length < 2 || cur.left() < (size_t)length) return JPEGGPU_INVALID_JPEG;
     const int rsti = (int)cur.u16();
-    if (plan.restart_interval != 0 && plan.restart_interval != rsti) {
-        log.log("\tredefined restart interval\n");
-        return JPEGGPU_NOT_SUPPORTED;
-    }
+    // The reference refuses a second, different DRI (src/reader.cpp:563-568).  T.81 B.2.4.4 lets
+    // the interval change between scans: every scan takes the value in force at its SOS
+    // (ScanGeom::restart_interval, read_sos).
     plan.restart_interval = rsti;
     log.log("\trestart_interval: %d\n", rsti);
     cur.p += length - 2;

@@ -177,7 +177,8 @@ static int parse_dri(struct parser* ps, struct orc_info* info)
     int length = (int)rd16(ps) - 2;
     if (length < 2 || remaining(ps) < length) return ORC_INVALID_JPEG;
     int rsti = (int)rd16(ps);
-    if (info->restart_interval != 0 && info->restart_interval != rsti) return ORC_NOT_SUPPORTED;
+    /* the reference refuses a second, different DRI (src/reader.cpp:563-568); T.81 B.2.4.4 lets the
+     * interval change between scans, and each scan uses the value in force at its SOS */
     info->restart_interval = rsti;
     ps->p += length - 2;
     return ORC_SUCCESS;
@@ -248,6 +249,7 @@ static int parse_sos(struct parser* ps, struct orc_info* info)
     rd8(ps);
     rd8(ps);
     memcpy(ps->huff[si], ps->cur, sizeof(ps->cur));
+    sc->restart_interval = info->restart_interval;
 
     /* walk the entropy-coded data: reader.cpp:443-489 */
     sc->begin = (int)(ps->p - ps->begin);
@@ -507,7 +509,7 @@ static int decode_scan_stream(const uint8_t* data, const struct orc_info* info,
     const size_t n = (size_t)(sc->end - sc->begin);
     const int K = sc->dus_per_mcu;
     const long total_mcus = (long)sc->mcus_x * sc->mcus_y;
-    const int ri = info->restart_interval;
+    const int ri = sc->restart_interval;
     /* which scan component each DU slot of the MCU belongs to */
     int slot_comp[10];
     {
@@ -588,7 +590,7 @@ static void undo_dc(const struct orc_info* info, int si, int16_t* stream)
     const struct orc_scan_info* sc = &info->scans[si];
     const int K = sc->dus_per_mcu;
     const long total_mcus = (long)sc->mcus_x * sc->mcus_y;
-    const int ri = info->restart_interval;
+    const int ri = sc->restart_interval;
     int off = 0;
     for (int a = 0; a < sc->num_components; ++a) {
         int ci = sc->comp_idx[a];

@@ -45,6 +45,7 @@ struct orc_scan_info {
     int data_size_x[ORC_MAX_COMP]; /* per scan component, rounded up to the MCU */
     int data_size_y[ORC_MAX_COMP];
     int num_segments;
+    int restart_interval;         /* in force at this SOS (T.81 B.2.4.4: DRI may be redefined between scans) */
 };
 
 struct orc_info {

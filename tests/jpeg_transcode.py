@@ -127,7 +127,9 @@ def transcode(data: bytes, planes, scans, restart_interval=0, dht_every_scan=Tru
     least ceil(size/8) blocks in each direction; scans: list of lists of frame component indices,
     e.g. [[0], [1], [2]] or [[0], [1, 2]].  table_map[c] = (dc table id, ac table id); default
     0/0 for component 0 and 1/1 for the others (falls back to 0/0 if the source has one pair).
-    restart_interval in MCUs of each scan (0 = none)."""
+    restart_interval in MCUs of each scan (0 = none), or a list with one value per scan: a DRI
+    segment is then written in front of every scan whose interval differs from the one in force
+    (T.81 B.2.4.4)."""
     dqt, dht, sof = parse_tables(data)
     comps = sof["comps"]
     W, H = sof["width"], sof["height"]
@@ -143,8 +145,8 @@ def transcode(data: bytes, planes, scans, restart_interval=0, dht_every_scan=Tru
     for c in comps:
         sof_body += bytes([c["id"], (c["h"] << 4) | c["v"], c["tq"]])
     out += b"\xff\xc0" + (len(sof_body) + 2).to_bytes(2, "big") + sof_body
-    if restart_interval:
-        out += b"\xff\xdd\x00\x04" + restart_interval.to_bytes(2, "big")
+    per_scan = list(restart_interval) if isinstance(restart_interval, (list, tuple)) else [restart_interval] * len(scans)
+    in_force = 0
 
     def dht_segment():
         body = bytearray()
@@ -156,6 +158,10 @@ def transcode(data: bytes, planes, scans, restart_interval=0, dht_every_scan=Tru
     for si, scan in enumerate(scans):
         if dht_every_scan or si == 0:
             out += dht_segment()
+        restart_interval = per_scan[si]
+        if restart_interval != in_force:
+            out += b"\xff\xdd\x00\x04" + restart_interval.to_bytes(2, "big")
+            in_force = restart_interval
         sos = bytes([len(scan)])
         for c in scan:
             sos += bytes([comps[c]["id"], (table_map[c][0] << 4) | table_map[c][1]])

@@ -24,6 +24,7 @@ class ScanInfo(C.Structure):
         ("data_size_x", C.c_int * 4),
         ("data_size_y", C.c_int * 4),
         ("num_segments", C.c_int),
+        ("restart_interval", C.c_int),
     ]
 
 

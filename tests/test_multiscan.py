@@ -19,6 +19,10 @@ CASES = {
     "444_tables_once": (dict(w=96, h=64, seed=36, mode="YCbCr", subsampling=0), [[0], [1], [2]], 0, False),
     "420_reordered": (dict(w=120, h=88, seed=37, mode="YCbCr", subsampling=2), [[2], [0, 1]], 3, True),
     "gray_single": (dict(w=77, h=50, seed=38, mode="L"), [[0]], 4, True),
+    # the restart interval redefined between the scans (T.81 B.2.4.4; the reference answers
+    # NOT_SUPPORTED, src/reader.cpp:563-568 - SURVEY 8f rank 4), switched off again for the last scan
+    "420_dri_per_scan": (dict(w=203, h=131, seed=39, mode="YCbCr", subsampling=2), [[0], [1], [2]], [7, 3, 0], True),
+    "444_dri_grows": (dict(w=160, h=120, seed=40, mode="YCbCr", subsampling=0), [[0], [1, 2]], [2, 50], True),
 }
 
 
