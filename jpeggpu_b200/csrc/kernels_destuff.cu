@@ -73,9 +73,11 @@ __device__ __forceinline__ void classify(const uint8_t* __restrict__ src, uint32
     ck.term = term;
 }
 
-// Inclusive block scan of a packed (kept | rst << 16) count; returns the exclusive value.
-__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* warp_sums,
-                                                         uint32_t& block_total)
+// Inclusive block scan of a packed (kept | rst << 16) count (< 2^31); returns the exclusive value.
+// any_flag: whether `flag` holds in any thread of the block - it travels in bit 31 of the warp
+// sums, so the question costs no barrier of its own.
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, bool flag, uint32_t* warp_sums,
+                                                         uint32_t& block_total, bool& any_flag)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t inc = v;
@@ -84,16 +86,19 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* w
         const uint32_t up = __shfl_up_sync(0xffffffffu, inc, d);
         if (lane >= d) inc += up;
     }
-    if (lane == 31) warp_sums[warp] = inc;
+    const uint32_t warp_flag = __any_sync(0xffffffffu, flag) ? 0x80000000u : 0u;
+    if (lane == 31) warp_sums[warp] = inc | warp_flag;
     __syncthreads();
-    uint32_t before = 0, total = 0;
+    uint32_t before = 0, total = 0, flags = 0;
 #pragma unroll
     for (int w = 0; w < kDestuffThreads / 32; ++w) {
         const uint32_t s = warp_sums[w];
-        if (w < warp) before += s;
-        total += s;
+        if (w < warp) before += s & 0x7fffffffu;
+        total += s & 0x7fffffffu;
+        flags |= s;
     }
     block_total = total;
+    any_flag = (flags >> 31) != 0u;
     return before + inc - v;
 }
 
@@ -193,7 +198,6 @@ constexpr int kLookK = 4;
 struct LookBackSmem {
     Elem warp_elem[kDestuffThreads / 32];
     uint32_t warp_stop[kDestuffThreads / 32];
-    uint32_t warp_sum[kDestuffThreads / 32];
 };
 
 __device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32_t tile, LookBackSmem& sm)
@@ -245,37 +249,24 @@ __device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32
                     nearest = min(nearest, dist[j]);
                 }
         }
-        // nothing beyond the nearest inclusive prefix matters
+        // Nothing beyond the nearest inclusive prefix matters.  Every warp reduces its own 128
+        // tiles first - cut at ITS nearest prefix, which can only be farther than the block's -
+        // so that ONE barrier suffices: afterwards the warps that lie entirely beyond the block's
+        // nearest prefix are simply left out.
         nearest = __reduce_min_sync(0xffffffffu, nearest);
-        if (lane == 0) sm.warp_stop[warp] = nearest;
-        __syncthreads();
-        uint32_t stop = 0xffffffffu;
-#pragma unroll
-        for (int w = 0; w < kWarps; ++w) stop = min(stop, sm.warp_stop[w]);
-        uint32_t busy = 0;
+        uint32_t busy = 0, heads = 0;
 #pragma unroll
         for (int j = 0; j < kLookK; ++j) {
-            if (dist[j] > stop) e[j] = none;
+            if (dist[j] > nearest) e[j] = none;
             busy |= e[j].nclose | e[j].ended;
+            heads += e[j].head;
         }
-        Elem win;
-        if (!__syncthreads_or((int)busy)) {
-            // no closing in the whole window (every scan without DRI): the heads just add up
-            uint32_t mine = 0;
-#pragma unroll
-            for (int j = 0; j < kLookK; ++j) mine += e[j].head;
-            const uint32_t sum = __reduce_add_sync(0xffffffffu, mine);
-            if (lane == 0) sm.warp_sum[warp] = sum;
-            __syncthreads();
-            uint32_t total = 0;
-#pragma unroll
-            for (int w = 0; w < kWarps; ++w) total += sm.warp_sum[w];
-            win = Elem{0u, total, 0u, 0u, 0u};
-        } else {
-            // ordered reduction (a higher element, lane or warp = a larger distance = an earlier
-            // tile): the thread's own elements, then a tree over the lanes: lane 0 ends with
-            // E[31] o ... o E[0]
-            Elem mine = e[0];
+        Elem mine = Elem{0u, __reduce_add_sync(0xffffffffu, heads), 0u, 0u, 0u};
+        if (__any_sync(0xffffffffu, busy != 0u)) {
+            // a closing among the warp's tiles (restart markers, the end of the scan): ordered
+            // reduction (a higher element, lane or warp = a larger distance = an earlier tile): the
+            // thread's own elements, then a tree over the lanes: lane 0 ends with E[31] o ... o E[0]
+            mine = e[0];
 #pragma unroll
             for (int j = 1; j < kLookK; ++j) mine = combine(e[j], mine);
 #pragma unroll
@@ -283,11 +274,21 @@ __device__ __forceinline__ Elem look_back(const unsigned long long* desc, uint32
                 const Elem far = shfl_down_elem(mine, d);
                 if (lane + d < 32) mine = combine(far, mine);
             }
-            if (lane == 0) sm.warp_elem[warp] = mine;
-            __syncthreads();
-            win = sm.warp_elem[kWarps - 1];
+        }
+        if (lane == 0) {
+            sm.warp_elem[warp] = mine;
+            sm.warp_stop[warp] = nearest;
+        }
+        __syncthreads();
+        uint32_t stop = 0xffffffffu;
 #pragma unroll
-            for (int w = kWarps - 2; w >= 0; --w) win = combine(win, sm.warp_elem[w]);
+        for (int w = 0; w < kWarps; ++w) stop = min(stop, sm.warp_stop[w]);
+        // warps whose first tile lies beyond the stop do not count (the one that holds it cut itself there)
+        Elem win = none;
+#pragma unroll
+        for (int w = kWarps - 1; w >= 0; --w) {
+            const uint32_t warp_first = base + (uint32_t)(w * 32 * kLookK);
+            if (warp_first <= stop) win = combine(win, sm.warp_elem[w]);
         }
         carry = combine(win, carry);
         if (stop != 0xffffffffu) break; // an inclusive prefix was found (the start of the scan counts as one)
@@ -350,7 +351,17 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
     // The scan ends at its first terminating marker or, failing that, with the data: nothing at or
     // behind that position counts.
     const bool last_tile = tile_begin + (uint32_t)kDestuffTile >= n;
-    if (__syncthreads_or(ck.term < 16u || last_tile)) {
+    // Nearly every tile has no terminating marker: scan its counts right away and learn from the
+    // same barrier whether that was true; only a tile that holds one (or the last tile) trims its
+    // masks and scans again.
+    uint32_t tile_total = 0, ex = 0;
+    bool ends = last_tile; // block-uniform
+    if (!ends) {
+        ex = block_exclusive_scan(__popc(ck.keep) | (__popc(ck.rst) << 16), ck.term < 16u, warp_sums, tile_total,
+                                  ends);
+        if (ends) __syncthreads(); // warp_sums is written again below
+    }
+    if (ends) {
         if (ck.term < 16u) atomicMin(&s_term, threadIdx.x * kDestuffBytesPerThread + ck.term);
         __syncthreads();
         uint32_t term = s_term;
@@ -363,10 +374,9 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
         ck.keep &= live;
         ck.rst &= live;
         if (threadIdx.x == 0) s_term = term;
+        bool unused;
+        ex = block_exclusive_scan(__popc(ck.keep) | (__popc(ck.rst) << 16), false, warp_sums, tile_total, unused);
     }
-    uint32_t tile_total;
-    const uint32_t ex = block_exclusive_scan(__popc(ck.keep) | (__popc(ck.rst) << 16), warp_sums,
-                                             tile_total);
     uint32_t pos = ex & 0xffffu, seg = ex >> 16;
     const uint32_t tile_kept = tile_total & 0xffffu;
     const bool ends_here = s_term < (uint32_t)kDestuffTile || (last_tile && s_term == n - tile_begin);
@@ -382,7 +392,7 @@ __device__ __forceinline__ void destuff_body(const DestuffArgs& a, const uint32_
 #pragma unroll
         for (int i = 0; i < 16; ++i)
             if ((ck.keep >> i) & 1u) stage[pos++] = ck.val[i];
-        __syncthreads();
+        if (tile == 0) __syncthreads(); // (the look-back of every other tile has a barrier)
     } else {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {

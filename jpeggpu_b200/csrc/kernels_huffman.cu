@@ -398,7 +398,6 @@ struct DevMem {
         return lds32(addr);
     }
     __device__ __forceinline__ void note_long_code() const {}
-    __device__ __forceinline__ void put(uint32_t, int) const {}
     __device__ __forceinline__ void put_symbol(uint32_t, uint32_t, uint32_t) const {}
 };
 
@@ -412,6 +411,14 @@ struct WriteMem : DevMem {
     uint32_t slot0;            // first slot of this thread's half subsequence (segment relative)
     int16_t* coef_seg;         // overflow: coefficient buffer / DC array at the first data unit of
     int16_t* dc_seg;           // the restart segment
+    // put_symbol_generic without a branch: value extraction, "is there a coefficient", "list or
+    // overflow" and "DC or AC" are predicates of two predicated stores.  The C++ form costs two
+    // data-dependent branches per symbol on predicates that come fresh from the table probe, and
+    // the lanes of a warp take them differently (JB2_WRITE_PTX=0 restores it).
+#ifndef JB2_WRITE_PTX
+#define JB2_WRITE_PTX 1
+#endif
+#if !JB2_WRITE_PTX
     __device__ __forceinline__ void put(uint32_t slot, int v) const
     {
         if (list_ptr != list_limit) {
@@ -424,12 +431,6 @@ struct WriteMem : DevMem {
             coef_seg[slot] = (int16_t)v;
         }
     }
-    // put_symbol_generic without a branch: value extraction, "is there a coefficient", "list or
-    // overflow" and "DC or AC" are predicates of two predicated stores.  The C++ form costs two
-    // data-dependent branches per symbol on predicates that come fresh from the table probe, and
-    // the lanes of a warp take them differently (JB2_WRITE_PTX=0 restores it).
-#ifndef JB2_WRITE_PTX
-#define JB2_WRITE_PTX 1
 #endif
     __device__ __forceinline__ void put_symbol(uint32_t e, uint32_t peek, uint32_t qq) const
     {
@@ -531,7 +532,6 @@ struct GlobalMem {
         return funnel_left_wrap(w0, w1, pn);
     }
     __device__ __forceinline__ void note_long_code() const {}
-    __device__ __forceinline__ void put(uint32_t, int) const {}
     __device__ __forceinline__ void put_symbol(uint32_t, uint32_t, uint32_t) const {}
 };
 

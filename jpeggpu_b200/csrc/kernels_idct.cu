@@ -257,6 +257,7 @@ __device__ __forceinline__ void stage_units_async(const int16_t* __restrict__ co
         }
     }
 }
+#if JB2_IDCT_BULK
 // Bulk flavour: lane l copies its own data unit (128 contiguous bytes) to tile + l * 144.
 __device__ __forceinline__ void stage_units_bulk(const int16_t* __restrict__ coef, uint32_t du, bool valid,
                                                  uint4* tile, unsigned long long* bar)
@@ -287,6 +288,7 @@ __device__ __forceinline__ void bulk_wait(unsigned long long* bar, uint32_t pari
                  "}" ::"r"(bar_addr), "r"(parity)
                  : "memory");
 }
+#endif
 __device__ __forceinline__ void async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
