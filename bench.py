@@ -397,7 +397,27 @@ def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
         hv[o:o + len(b)] = np.frombuffer(b, dtype=np.uint8)
     items = make_items([(host.data_ptr() + o, len(b)) for o, b in zip(offs, blobs)])
     n = len(blobs)
-    chunks = [(i, min(chunk, n - i)) for i in range(0, n, chunk)]
+    # Batches of `chunk` images, with a short ramp at both ends when a rank has few batches: the
+    # first kernels start after planning and uploading 8 images instead of `chunk`, and the last
+    # batch that the pipeline has to drain is a small one.
+    sizes = []
+    if chunk <= 8 or n < 4 * chunk:
+        sizes = [chunk] * (n // chunk) + ([n % chunk] if n % chunk else [])
+    else:
+        head, c = [], max(8, chunk // 4)
+        while c < chunk:
+            head.append(c)
+            c *= 2
+        tail = head[::-1]
+        body = n - sum(head) - sum(tail)
+        if body < 0:
+            head, tail, body = [], [], n
+        sizes = head + [chunk] * (body // chunk) + ([body % chunk] if body % chunk else []) + tail
+    chunks, at0 = [], 0
+    for c in sizes:
+        chunks.append((at0, c))
+        at0 += c
+    assert at0 == n
     lanes = []
     for _ in range(depth):
         fb = FusedBatch()
@@ -485,15 +505,14 @@ def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
 def batch_shape(args, world):
     """Images per fused batch and batches in flight.  Large batches amortise launches and the
     descriptor upload; small ones shorten the fill and drain of the pipeline, which is what counts
-    when a rank has few images (measured on B200s, 4096 files: 1 GPU 128 x 3 -> 82 k images/s,
-    64 x 3 -> 81 k; 8 GPUs, 512 files per rank: 128 x 3 -> 487 k, 64 x 4 -> 554 k, 32 x 4 -> 578 k;
-    profiles/r2_k_batch_scale_8gpu.txt)."""
+    when a rank has few images (ours_batch also ramps the batch size at both ends).  Measured on
+    B200s, 4096 files: 1 GPU 128 x 3 -> 88 k images/s, 64 x 4 -> 87 k; 512 files on one GPU (a
+    rank's share on 8): 64 x 4 -> 81.4 k, 32 x 4 -> 80.0 k, 16 x 4 -> 75.9 k
+    (profiles/r2_final_batch_scale_*.txt)."""
     per_rank = max(1, args.batch_images // world)
     chunk = args.batch_chunk
     if chunk <= 0:
-        chunk = 32
-        while chunk < 128 and chunk * 16 < per_rank:
-            chunk *= 2
+        chunk = 128 if per_rank >= 2048 else 64
     depth = args.batch_depth if args.batch_depth > 0 else (3 if chunk >= 128 else 4)
     return chunk, depth
 

@@ -11,5 +11,5 @@ $TR --master-port 29512 bench.py --impl reference --gpus $N --steps 20 --warmup 
 tail -2 gpurun_out/${TAG}_m2.err
 python tools/show_bench.py gpurun_out/${TAG}_bench_ours_${N}gpu.json gpurun_out/${TAG}_bench_reference_${N}gpu.json
 echo host cores: $(nproc)
-$TR --master-port 29513 tools/batch_scale.py 4096 128:3 64:3 64:4 32:4 > gpurun_out/${TAG}_batch_scale_${N}gpu.txt 2> gpurun_out/${TAG}_m3.err
+$TR --master-port 29513 tools/batch_scale.py 4096 128:3 64:4 32:4 > gpurun_out/${TAG}_batch_scale_${N}gpu.txt 2> gpurun_out/${TAG}_m3.err
 cat gpurun_out/${TAG}_batch_scale_${N}gpu.txt; tail -2 gpurun_out/${TAG}_m3.err
