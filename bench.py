@@ -454,7 +454,10 @@ def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
             h0 = time.perf_counter()
             need, _ = ln["fb"].plan(sub, count=count)
             h1 = time.perf_counter()
-            if ln["arena"] is None or ln["arena"].numel() < need:
+            if ln["arena"].numel() < need:
+                # (never with one geometry: the arenas are sized for the largest batch up front.  A
+                # new arena must not replace one that batches in flight still use.)
+                ln["stream"].synchronize()
                 ln["arena"] = torch.empty(need + need // 8, dtype=torch.uint8, device=device)
             ln["fb"].decode(sub, ln["arena"].data_ptr(), ln["arena"].numel(), ln["stream"].cuda_stream,
                             count=count)
@@ -464,6 +467,11 @@ def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
         return plan_s, enq_s
 
     pool = concurrent.futures.ThreadPoolExecutor(max_workers=depth)
+    # every lane's arena, sized for the largest batch before anything runs
+    largest = max(chunks, key=lambda fc: fc[1])
+    for ln in lanes:
+        need, _ = ln["fb"].plan(C_slice(items, largest[0], isz), count=largest[1])
+        ln["arena"] = torch.empty(need + need // 8, dtype=torch.uint8, device=device)
 
     def run(which, timed):
         t0 = time.perf_counter()
@@ -507,12 +515,13 @@ def batch_shape(args, world):
     descriptor upload; small ones shorten the fill and drain of the pipeline, which is what counts
     when a rank has few images (ours_batch also ramps the batch size at both ends).  Measured on
     B200s, 4096 files: 1 GPU 128 x 3 -> 88 k images/s, 64 x 4 -> 87 k; 512 files on one GPU (a
-    rank's share on 8): 64 x 4 -> 81.4 k, 32 x 4 -> 80.0 k, 16 x 4 -> 75.9 k
+    rank's share on 8): 64 x 4 -> 81.4 k, 32 x 4 -> 80.0 k, 16 x 4 -> 75.9 k; on 8 GPUs, where eight
+    processes share 32 host cores, 32 x 4 -> 575-585 k, 64 x 4 -> 550-562 k, 128 x 3 -> 490-510 k
     (profiles/r2_final_batch_scale_*.txt)."""
     per_rank = max(1, args.batch_images // world)
     chunk = args.batch_chunk
     if chunk <= 0:
-        chunk = 128 if per_rank >= 2048 else 64
+        chunk = 128 if per_rank >= 2048 else 64 if per_rank >= 1024 else 32
     depth = args.batch_depth if args.batch_depth > 0 else (3 if chunk >= 128 else 4)
     return chunk, depth
 
