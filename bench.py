@@ -397,22 +397,7 @@ def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
         hv[o:o + len(b)] = np.frombuffer(b, dtype=np.uint8)
     items = make_items([(host.data_ptr() + o, len(b)) for o, b in zip(offs, blobs)])
     n = len(blobs)
-    # Batches of `chunk` images, with a short ramp at both ends when a rank has few batches: the
-    # first kernels start after planning and uploading 8 images instead of `chunk`, and the last
-    # batch that the pipeline has to drain is a small one.
-    sizes = []
-    if chunk <= 8 or n < 4 * chunk:
-        sizes = [chunk] * (n // chunk) + ([n % chunk] if n % chunk else [])
-    else:
-        head, c = [], max(8, chunk // 4)
-        while c < chunk:
-            head.append(c)
-            c *= 2
-        tail = head[::-1]
-        body = n - sum(head) - sum(tail)
-        if body < 0:
-            head, tail, body = [], [], n
-        sizes = head + [chunk] * (body // chunk) + ([body % chunk] if body % chunk else []) + tail
+    sizes = batch_sizes(n, chunk)
     chunks, at0 = [], 0
     for c in sizes:
         chunks.append((at0, c))
@@ -508,6 +493,22 @@ def ours_batch(rank, world, device, total_images, chunk, depth, repeats=3):
     total_bytes = sum(len(b) for b in blobs)
     return {"seconds": dt, "images": n, "host_enqueue_seconds": host_s, "plan_seconds": plan_s,
             "bytes": total_bytes, "matches_per_image_path": ok, "seconds_all_passes": [round(r[0], 5) for r in passes]}
+
+
+def batch_sizes(n, chunk):
+    """Sizes of the fused batches of one rank's n files: `chunk` images each, with a short ramp at
+    both ends (a quarter of `chunk`, at least 8, doubling) - the first kernels start after planning
+    and uploading a few files instead of `chunk`, and the last batch the pipeline has to drain is
+    a small one."""
+    if chunk <= 8 or n < 4 * chunk:
+        return [chunk] * (n // chunk) + ([n % chunk] if n % chunk else [])
+    head, c = [], max(8, chunk // 4)
+    while c < chunk:
+        head.append(c)
+        c *= 2
+    tail = head[::-1]
+    body = n - sum(head) - sum(tail)
+    return head + [chunk] * (body // chunk) + ([body % chunk] if body % chunk else []) + tail
 
 
 def batch_shape(args, world):

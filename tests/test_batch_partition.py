@@ -161,3 +161,23 @@ def test_one_decoder_many_images_in_flight():
         ref = ob.decode(data)
         for c, p in enumerate(planes):
             assert np.array_equal(p[:, :info.sizes_x[c]].cpu().numpy(), ref["pixels"][c]), name
+
+
+def test_batch_sizes_cover_every_file_once():
+    """bench.py's batch leg: the sizes of a rank's fused batches (ramp at both ends) add up to the
+    rank's files, none exceeds the batch size, and the shape follows the files per rank."""
+    import argparse
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    for n in (0, 1, 7, 100, 511, 512, 513, 1024, 2048, 4096, 4097):
+        for chunk in (8, 16, 32, 64, 128, 256):
+            sizes = bench.batch_sizes(n, chunk)
+            assert sum(sizes) == n and all(0 < x <= chunk for x in sizes), (n, chunk, sizes)
+            if n >= 4 * chunk and chunk > 8:
+                assert sizes[0] == max(8, chunk // 4) and sizes[-1] == sizes[0]
+    shapes = [bench.batch_shape(argparse.Namespace(batch_images=4096, batch_chunk=0, batch_depth=0), w)
+              for w in (1, 2, 4, 8)]
+    assert shapes == [(128, 3), (128, 3), (64, 4), (32, 4)]
+    assert bench.batch_shape(argparse.Namespace(batch_images=4096, batch_chunk=16, batch_depth=2), 8) == (16, 2)
