@@ -133,6 +133,10 @@ enum jpeggpu_status jpeggpu_b200_parse_batch(
 // ---- fused batches (include/jpeggpu_b200.h): several images per kernel launch ------------------
 #include "plan.hpp"
 
+#ifndef JB2_BATCH_FILL_IN_WRITE
+#define JB2_BATCH_FILL_IN_WRITE 1
+#endif
+
 #include <algorithm>
 #include <cstring>
 #include <memory>
@@ -366,6 +370,9 @@ jpeggpu_status decode_batch(jpeggpu_b200_batch& B, jpeggpu_b200_batch_item* item
     bl.lut_compact_words_max = B.max_compact_words;
     const int write_warps = batch_write_warps(B.max_compact_words);
     jpeggpu_status first = JPEGGPU_SUCCESS;
+    size_t batch_coef_bytes = 0;
+    for (int i = 0; i < n; ++i)
+        if (B.images[i]->ok) batch_coef_bytes += B.images[i]->layout.coef_bytes;
     for (int i = 0; i < n; ++i) {
         jpeggpu_b200_batch::Image& im = *B.images[i];
         BatchImage& d = desc[i];
@@ -383,6 +390,9 @@ jpeggpu_status decode_batch(jpeggpu_b200_batch& B, jpeggpu_b200_batch_item* item
         }
         d.g = sp.geom;
         d.b = make_bufs(im.layout, base);
+        // the coefficient buffers of a batch are written and read together: what counts for "fits
+        // L2" is their sum (64 files of 2 MP: 397 MB)
+        if (JB2_BATCH_FILL_IN_WRITE && batch_coef_bytes > kFillInWriteBytes) d.b.fill_in_write = 1u;
         d.b.scan_lead = im.lead;
         uint8_t q[kMaxComp][64];
         memset(q, 0, sizeof(q));
