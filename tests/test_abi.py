@@ -161,3 +161,25 @@ def test_deferred_walk_reports_late_errors(lib):
     assert lib.jpeggpu_decoder_get_buffer_size(lazy.handle, C.byref(n)) == jb.INVALID_ARGUMENT
     eager.cleanup()
     lazy.cleanup()
+
+
+def test_destuff_static_rejects_bad_arguments_without_touching_the_device(capfd):
+    """jpeggpu_b200_destuff_static checks its arguments before any CUDA call: NULL pointers, sizes of
+    zero, pointers that are not 16-byte aligned and scans beyond the static scratch's maximum are
+    JPEGGPU_INVALID_ARGUMENT (the last one with a line on stderr that names the limit)."""
+    import jpeggpu_b200 as jb
+    lib = jb.load_library()
+    call = lib.jpeggpu_b200_destuff_static
+    a = 0x10000  # never dereferenced
+    assert call(None, 4096, a, 64, a, 16, a, None) == jb.INVALID_ARGUMENT
+    assert call(a, 4096, None, 64, a, 16, a, None) == jb.INVALID_ARGUMENT
+    assert call(a, 4096, a, 64, None, 16, a, None) == jb.INVALID_ARGUMENT
+    assert call(a, 4096, a, 64, a, 16, None, None) == jb.INVALID_ARGUMENT
+    assert call(a, 0, a, 64, a, 16, a, None) == jb.INVALID_ARGUMENT
+    assert call(a, 4096, a, 0, a, 16, a, None) == jb.INVALID_ARGUMENT
+    assert call(a, 4096, a, 64, a, 0, a, None) == jb.INVALID_ARGUMENT
+    assert call(a + 8, 4096, a, 64, a, 16, a, None) == jb.INVALID_ARGUMENT
+    assert call(a, 4096, a + 4, 64, a, 16, a, None) == jb.INVALID_ARGUMENT
+    capfd.readouterr()
+    assert call(a, jb.DESTUFF_STATIC_MAX_BYTES + 1, a, 64, a, 16, a, None) == jb.INVALID_ARGUMENT
+    assert "JPEGGPU_B200_DESTUFF_STATIC_MAX_BYTES" in capfd.readouterr().err
