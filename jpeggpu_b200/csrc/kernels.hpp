@@ -38,10 +38,10 @@ struct ScanBufs {
     unsigned long long* write_agg; // zeroed by destuff: slot aggregate per huff_write CTA
     uint32_t clear_words;      // Control + mailboxes + DC flags + write aggregates, contiguous
     uint32_t* destuffed;       // big-endian words, segment k at sub_off * kSubWords
-    int16_t* coef;             // zeroed by huff_sync; DU-major coded order, 64 zig-zag-order int16 per DU (slot 0 unused)
+    int16_t* coef;             // zeroed by huff_sync (or by huff_write, fill_in_write); DU-major coded order, 64 zig-zag-order int16 per DU (slot 0 unused)
     uint32_t fill_in_write;    // huff_write clears the coefficient buffer stretch by stretch (else huff_sync clears it)
     size_t coef_bytes;         // multiple of 16
-    int16_t* dc;               // zeroed by huff_sync; one DC value per DU, coded order: differences
+    int16_t* dc;               // zeroed like coef; one DC value per DU, coded order: differences
                                // after huff_write, absolute values after dc_scan
     size_t dc_bytes;           // multiple of 16
     SubEntry* entries;         // N

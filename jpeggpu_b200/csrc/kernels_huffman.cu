@@ -15,19 +15,24 @@
 //               the cold start of lane 0.  The warp then publishes the exit state of its last
 //               subsequence in a one-word mailbox, reads its left neighbour's mailbox, and if that
 //               disagrees with the entry state it had assumed it re-runs the iteration from the
-//               corrected state (rare).  One 8-byte record {entry, exit, slots} per subsequence.
-//               The kernel also zero-fills the coefficient buffer (its load/store units are idle
-//               while the warps decode).
-//               The CTA that finishes last verifies every chunk boundary (exit of the left
-//               record == entry of the right one); if all agree, every record is exact by
-//               induction from the segment starts, otherwise it repairs sequentially.
+//               corrected state (rare).  A lane keeps the evaluation it held before the current
+//               one (one-entry memo), so flipping back to an earlier entry state costs nothing.
+//               One 16-byte record {entry, exit, slots, mid state} per subsequence.
+//               An extra warp per CTA zero-fills the coefficient buffer in the prologue (buffers
+//               that fit L2; larger ones are cleared by huff_write, stretch by stretch).
+//               Tables and scan window arrive by cp.async.bulk + mbarrier.
+//               Only when a chunk re-published a different exit state (or a mailbox wait timed
+//               out) does the CTA that finishes last verify every chunk boundary (exit of the left
+//               record == entry of the right one) and repair sequentially from each break;
+//               otherwise every record is exact by induction from the segment starts.
 //   huff_write  decode from the verified entry states, kWriteParts (2) threads per subsequence (the record
 //               holds the state at its middle).  The first output slot of every subsequence is
 //               a segmented prefix sum of the records' slot counts, computed inside this kernel
 //               with a look-back over per-CTA aggregates (replaces the reference's CUB
 //               ExclusiveScanByKey + assign_sinfo_n, src/decode_huffman.cu:827-869).  Non-zero
-//               coefficients are collected in per-thread lists in shared memory and scattered
-//               afterwards into the zero-filled buffer, zig-zag index kept (the IDCT un-zig-zags
+//               coefficients are collected in bounded per-thread lists in shared memory (what
+//               does not fit goes straight to global memory) and scattered afterwards into the
+//               zero-filled buffer, zig-zag index kept (the IDCT un-zig-zags
 //               in registers); DC differences go to a compact per-DU array
 //               (src/decode_huffman.cu:627-682).
 #include "huff_threads.hpp"
